@@ -114,7 +114,7 @@ typedef struct lsmc_problem {
 
 typedef struct lsmc_rng {
     int32_t mode;             /* LSMC_RNG_* */
-    int32_t antithetic;       /* Philox mode: path n >= ceil(Nglobal/2) reuses the negated draws of path n - ceil(Nglobal/2) */
+    int32_t antithetic;       /* Philox mode: global paths 2m and 2m+1 share draw m with opposite signs */
     uint64_t seed;            /* Philox key */
     const double* normals;    /* LSMC_RNG_NORMALS: [S][F][N] standard normals, S = simulated periods */
     const double* spot;       /* LSMC_RNG_PANELS: [S][N] */
@@ -196,6 +196,7 @@ int lsmc_calculate(lsmc_ctx* ctx, const lsmc_problem* problem,
 /* Staged entry points (same work, separately callable; used by the benchmark and the tests). */
 int lsmc_set_problem(lsmc_ctx* ctx, const lsmc_problem* problem);       /* host set-up (SH.cs:39-107, grids, decision tables) + H2D */
 int lsmc_get_layout(const lsmc_ctx* ctx, lsmc_layout* out);
+int lsmc_request_outputs(lsmc_ctx* ctx, uint32_t mask);                 /* before lsmc_set_problem: bit0 per-sim [P][N] panels, bit1 decision_index */
 int lsmc_simulate(lsmc_ctx* ctx, int set /*0 regression, 1 valuation*/, const lsmc_rng* rng);
 int lsmc_backward(lsmc_ctx* ctx, lsmc_progress_cb progress, void* progress_user);
 int lsmc_forward(lsmc_ctx* ctx, lsmc_progress_cb progress, void* progress_user);

@@ -569,8 +569,6 @@ void simulate(const lsmc_problem& pb, const SimTables& t, const lsmc_rng& rng, S
         return;
     }
     if (rng.mode == LSMC_RNG_NORMALS && !rng.normals) throw OracleError(LSMC_EINVAL, "normals mode needs normals");
-    int64_t Ng = pb.n_sims_global > 0 ? pb.n_sims_global : N;
-    int64_t half = (Ng + 1) / 2;
 #pragma omp parallel for schedule(static)
     for (int64_t n = 0; n < N; n++) {
         double x[LSMC_MAX_FACTORS] = {0};
@@ -578,7 +576,7 @@ void simulate(const lsmc_problem& pb, const SimTables& t, const lsmc_rng& rng, S
         int64_t gn = pb.sim_offset + n;
         double sign = 1.0;
         uint64_t draw = (uint64_t)gn;
-        if (rng.mode == LSMC_RNG_PHILOX && rng.antithetic && gn >= half) { draw = (uint64_t)(gn - half); sign = -1.0; }
+        if (rng.mode == LSMC_RNG_PHILOX && rng.antithetic) { draw = (uint64_t)(gn >> 1); sign = (gn & 1) ? -1.0 : 1.0; }   // partners are adjacent paths
         for (int j = 0; j < S; j++) {
             if (rng.mode == LSMC_RNG_NORMALS) {
                 for (int f = 0; f < F; f++) z[f] = rng.normals[((size_t)j * F + f) * N + n];
@@ -1147,12 +1145,11 @@ void calculate(const lsmc_problem& pb, const lsmc_rng& regRng, const lsmc_rng& v
     res.npv = average(pvBySim.data(), N);   // LSV.cs:584
     res.backward_npv = backwardNpv;
     {   // standard error from antithetic pair means when the draws are paired, else plain
-        bool paired = valRng.mode == LSMC_RNG_PHILOX && valRng.antithetic && (N % 2 == 0) && pb.sim_offset == 0 &&
-                      (pb.n_sims_global == 0 || pb.n_sims_global == N);
+        bool paired = valRng.mode == LSMC_RNG_PHILOX && valRng.antithetic && (N % 2 == 0) && (pb.sim_offset % 2 == 0);
         int64_t m = paired ? N / 2 : N;
         double mean = 0.0, m2 = 0.0;
         for (int64_t i = 0; i < m; i++) {
-            double v = paired ? 0.5 * (pvBySim[i] + pvBySim[i + m]) : pvBySim[i];
+            double v = paired ? 0.5 * (pvBySim[2 * i] + pvBySim[2 * i + 1]) : pvBySim[i];
             double dlt = v - mean;
             mean += dlt / (double)(i + 1);
             m2 += dlt * (v - mean);

@@ -1,0 +1,84 @@
+// host_plan.h — host-side set-up of one valuation: everything the reference computes per (period, grid point)
+// before touching a simulation path (LSV.cs:86-143,209-223,237-300; SH.cs:39-204).  Product code; the CPU
+// oracle has its own independent restatement under oracle/.
+#pragma once
+#include <cstdint>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/lsmc_b200.h"
+
+namespace lsmc {
+
+struct Error : std::runtime_error {
+    int status;
+    Error(int s, const std::string& m) : std::runtime_error(m), status(s) {}
+};
+
+// One multiplication of the basis "program": node[dst] = node[a] * node[b].
+struct BasisOp { int16_t dst, a, b, pad; };
+
+// Basis functions compiled to a prefix-sharing product chain (left-to-right, spot first, factors ascending).
+// Node 0 = zero row, node 1 = ones, node 2 = spot, node 3+f = factor f, then product nodes.
+struct BasisProgram {
+    int n_nodes = 0;
+    std::vector<BasisOp> ops;
+    std::vector<int16_t> node_of_basis;   // [K]
+};
+
+// Decision table entry for one (period, grid point, decision): LSV.cs:249-300.
+struct DecisionTables {
+    // per (period p < P-1, grid index i): offsets via row_offset[p] + i
+    std::vector<int32_t> row_offset;      // [P]  first row of period p (rows = grid points)
+    std::vector<int32_t> n_dec;           // [rows]
+    std::vector<double>  inv_cost_npv;    // [rows]
+    // per (row, d), stride max_dec
+    std::vector<double> vol, cost_npv, consumed, w_lo, w_hi;
+    std::vector<int32_t> lo, hi;
+};
+
+struct SimCoefficients {
+    int S = 0;
+    std::vector<double> decay;   // [S][F]
+    std::vector<double> chol;    // [S][F][F]
+    std::vector<double> vol;     // [S][F]
+    std::vector<double> drift;   // [S]
+    std::vector<double> fwd;     // [S]
+};
+
+// Deep copy of the caller's problem so no host pointer outlives the call (ownership rule).
+struct ProblemCopy {
+    lsmc_problem pb{};
+    std::vector<double> sim_time, mean_reversion, factor_vol, factor_corr, forward, min_inventory, max_inventory,
+        inject_cost, inject_cost_df, withdraw_cost, withdraw_cost_df, consumed_inject, consumed_withdraw, inventory_loss,
+        inventory_cost, inventory_cost_df, settle_df, pillar_inventory, pillar_min_rate, pillar_max_rate;
+    std::vector<int32_t> spot_power, factor_power, constraint_id, constraint_kind, constraint_first, constraint_count;
+    void assign(const lsmc_problem& src);
+};
+
+struct Plan {
+    ProblemCopy problem;
+    int P = 0, F = 0, K = 0, S = 0, s0 = 0, max_dec = 0, max_grid = 0;
+    std::vector<double> space_min, space_max;   // [P]; entry 0 is the start inventory
+    std::vector<int32_t> grid_offset;           // [P+1]
+    std::vector<double> grid;                   // concatenated grids
+    DecisionTables tables;
+    SimCoefficients sim;
+    BasisProgram basis;
+
+    int grid_size(int p) const { return grid_offset[p + 1] - grid_offset[p]; }
+    const double* grid_of(int p) const { return grid.data() + grid_offset[p]; }
+};
+
+void build_plan(const lsmc_problem& problem, Plan& plan);
+
+// Storage queries at arbitrary inventory, used by the trigger-price post-processing (LSV.cs:494-497).
+void inject_withdraw_range(const lsmc_problem& pb, int period, double inventory, double& rmin, double& rmax);
+int bang_bang_decisions(double rmin, double rmax, double inventory, double loss, double next_min, double next_max,
+                        double tol, int extra, double* out);
+double decision_cost_npv(const lsmc_problem& pb, int period, double volume);
+double decision_consumed(const lsmc_problem& pb, int period, double volume);
+void bisect_grid(const double* grid, int n, double inventory, double tol, int& lo, int& hi);
+
+}  // namespace lsmc

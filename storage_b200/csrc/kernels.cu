@@ -1,0 +1,696 @@
+// kernels.cu — hand-written sm_100a kernels of the LSMC hot path.
+//   K1 simulate_kernel       multi-factor OU simulation (LVP.cs:160-178 -> Cmdty.Core simulator)
+//   K3 sweep_kernel          backward decision sweep of one period fused with the design-matrix build and the
+//                            X^T X / X^T Y normal-equation accumulation of the previous period on FP64 tensor
+//                            cores (DMMA) (LSV.cs:185-205, 234-332, 753-770)
+//   K2 reduce/solve kernels  partial reduction + scaled Cholesky solve of the K x K system for all grid points
+//   K4 forward_kernel        forward inventory / cash-flow simulation of one period (LSV.cs:426-480)
+#include "kernels.h"
+
+namespace lsmc {
+
+// =================================================================================================
+// K1: simulation.  One thread per path, the time loop runs in registers; stores are coalesced across the warp
+// (path-major rows).  HBM-bound on 8(F+1) bytes per path-step written (+8F read with injected normals).
+// =================================================================================================
+template <int F>
+__global__ void __launch_bounds__(256) simulate_kernel(SimParams sp) {
+    const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= sp.N) return;
+    double x[F];
+#pragma unroll
+    for (int f = 0; f < F; f++) x[f] = 0.0;
+    const int64_t gn = sp.sim_offset + n;
+    double sign = 1.0;
+    uint64_t draw = (uint64_t)gn;
+    if (sp.mode == LSMC_RNG_PHILOX && sp.antithetic) { draw = (uint64_t)(gn >> 1); sign = (gn & 1) ? -1.0 : 1.0; }   // partners are adjacent paths
+    for (int j = 0; j < sp.S; j++) {
+        double z[F + 1];
+        if (sp.mode == LSMC_RNG_NORMALS) {
+#pragma unroll
+            for (int f = 0; f < F; f++) z[f] = __ldcs(sp.normals + ((size_t)j * F + f) * sp.N + n);
+        } else {
+#pragma unroll
+            for (int f = 0; f < F; f += 2) {
+                double a, b;
+                philox_normal_pair(sp.seed, draw, (uint32_t)j, (uint32_t)(f / 2), a, b);
+                z[f] = sign * a;
+                z[f + 1] = sign * b;
+            }
+        }
+        const double* L = sp.chol + (size_t)j * F * F;
+        double acc = 0.0;
+#pragma unroll
+        for (int f = 0; f < F; f++) {
+            double eps = mul_rn(__ldg(L + f * F), z[0]);
+#pragma unroll
+            for (int b = 1; b <= f; b++) eps = add_rn(eps, mul_rn(__ldg(L + f * F + b), z[b]));
+            x[f] = add_rn(mul_rn(__ldg(sp.decay + (size_t)j * F + f), x[f]), eps);
+        }
+#pragma unroll
+        for (int f = 0; f < F; f++) {
+            double term = mul_rn(__ldg(sp.vol + (size_t)j * F + f), x[f]);
+            acc = (f == 0) ? term : add_rn(acc, term);
+            __stcs(sp.fac + ((size_t)j * F + f) * sp.Npad + n, x[f]);
+        }
+        double s = mul_rn(__ldg(sp.fwd + j), det_exp(sub_rn(acc, __ldg(sp.drift + j))));
+        __stcs(sp.spot + (size_t)j * sp.Npad + n, s);
+    }
+}
+
+void launch_simulate(const SimParams& sp, cudaStream_t stream) {
+    const int threads = 256;
+    const int blocks = (int)((sp.N + threads - 1) / threads);
+    switch (sp.F) {
+#define CASE(f) case f: simulate_kernel<f><<<blocks, threads, 0, stream>>>(sp); break;
+        CASE(1) CASE(2) CASE(3) CASE(4) CASE(5) CASE(6) CASE(7) CASE(8)
+#undef CASE
+    }
+}
+
+// =================================================================================================
+// K3: fused backward sweep.
+//
+// A CTA walks path tiles of TP paths.  Per tile:
+//   stage   V_next[Gn][TP] -> smem (coalesced 16 B per lane), design-matrix nodes of period p and p-1 -> smem
+//   fit     C^[l][n] = sum_k beta[l][k] X_p[n][k]  for all next-grid rows l: DMMA, A = beta, B = X_p^T -> smem
+//   decide  lane (g,t) of warp w owns grid row i = 8*ntile + g and paths 4*ks + t: max over the bang-bang
+//           decisions of immediate + interpolated C^, realised value from interpolated V_next -> store V[i][n];
+//           the value just computed is the B operand of the DMMA that accumulates X_{p-1}^T V (and, on the
+//           trailing "basis" n-tiles, X_{p-1}^T X_{p-1}) without ever touching shared memory again.
+// The accumulators live in registers for the whole kernel and are written once per CTA.
+// =================================================================================================
+template <int TP, int MT, int NTW>
+__global__ void __launch_bounds__(512, 1) sweep_kernel(SweepParams q) {
+    constexpr int LD = TP + 8;   // row stride in doubles: rows 8 banks apart -> conflict-free 8-row x 4-path reads
+    extern __shared__ double smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, W = blockDim.x >> 5;
+    const int g = lane >> 2, t = lane & 3;
+    const BasisDev* __restrict__ bd = q.basis;
+    const int n_nodes = bd->n_nodes;
+    const int GnP = (q.Gn + 7) & ~7;
+    const int NT = (q.G + 7) >> 3;            // decision n-tiles
+    const int NTaug = q.accum_mode ? NT + MT : NT;
+    const int Kp4 = q.ldb;
+
+    double* sVn = smem;                           // [GnP][LD]
+    double* sC = sVn + (size_t)GnP * LD;          // [GnP][LD]
+    double* sNP = sC + (size_t)GnP * LD;          // [n_nodes][LD]
+    double* sNM = sNP + (size_t)n_nodes * LD;     // [n_nodes][LD]
+    double* sBeta = sNM + (size_t)n_nodes * LD;   // [GnP][Kp4]
+    __shared__ int16_t sNodeP[64 + 8], sNodeM[64 + 8];
+    __shared__ BasisOpDev sOps[kMaxOps];
+
+    // one-time staging: basis program, coefficients
+    for (int i = tid; i < bd->n_ops; i += blockDim.x) sOps[i] = bd->ops[i];
+    for (int k = tid; k < 72; k += blockDim.x) {
+        int16_t node = (k < q.K) ? bd->node_of_basis[k] : (int16_t)0;
+        sNodeP[k] = node;
+        sNodeM[k] = (q.accum_mode == 1) ? node : (int16_t)((q.accum_mode == 2 && k == 0) ? 1 : 0);
+    }
+    if (q.mode == 0) {
+        for (int i = tid; i < GnP * Kp4; i += blockDim.x) {
+            int l = i / Kp4;
+            sBeta[i] = (l < q.Gn) ? __ldg(q.beta + i) : 0.0;
+        }
+    }
+    // zero the padded rows of the staged value tile once (never overwritten by the loads)
+    for (int i = q.Gn * LD + tid; i < GnP * LD; i += blockDim.x) { sVn[i] = 0.0; sC[i] = 0.0; }
+
+    double acc[NTW][MT][2];
+#pragma unroll
+    for (int a = 0; a < NTW; a++)
+#pragma unroll
+        for (int m = 0; m < MT; m++) acc[a][m][0] = acc[a][m][1] = 0.0;
+
+    const int64_t n_tiles = q.Npad / TP;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int64_t n0 = tile * TP;
+        __syncthreads();   // previous tile fully consumed
+        // ---- stage V_next tile ----
+        if (q.mode == 0) {
+            constexpr int LPR = TP / 2;          // lanes per row (16 B each)
+            constexpr int RPW = 32 / LPR;        // rows per warp pass
+            const int sub = lane / LPR, col = (lane % LPR) * 2;
+            for (int r = warp * RPW + sub; r < q.Gn; r += W * RPW) {
+                const double2 v = __ldcs(reinterpret_cast<const double2*>(q.Vnext + (size_t)r * q.Npad + n0 + col));
+                *reinterpret_cast<double2*>(sVn + (size_t)r * LD + col) = v;
+            }
+        }
+        // ---- design-matrix nodes for period p (threads [0,TP)) and p-1 (threads [TP,2TP)) ----
+        if (tid < 2 * TP) {
+            const bool isM = tid >= TP;
+            const int path = isM ? tid - TP : tid;
+            const int64_t n = n0 + path;
+            double* nodes = isM ? sNM : sNP;
+            const bool live = n < q.N;
+            bool skip = isM ? (q.accum_mode != 1) : false;
+            const double* spot = isM ? q.spot_m : q.spot_p;
+            const double* fac = isM ? q.fac_m : q.fac_p;
+            nodes[0 * LD + path] = 0.0;
+            nodes[1 * LD + path] = (live && (!isM || q.accum_mode)) ? 1.0 : 0.0;
+            if (!skip) {
+                double s = (!isM && q.spot_is_const) ? q.spot_const : __ldcs(spot + n);
+                nodes[2 * LD + path] = live ? s : 0.0;
+                const bool need_fac = isM || (q.mode == 0 && q.cont_mode == 0);
+                if (need_fac) {
+                    for (int f = 0; f < q.F; f++) nodes[(3 + f) * LD + path] = live ? __ldcs(fac + (size_t)f * q.Npad + n) : 0.0;
+                    for (int o = 0; o < bd->n_ops; o++) {
+                        const BasisOpDev op = sOps[o];
+                        nodes[op.dst * LD + path] = mul_rn(nodes[op.a * LD + path], nodes[op.b * LD + path]);
+                    }
+                }
+            }
+        }
+        __syncthreads();
+        // ---- fitted continuation values for every next-grid row ----
+        if (q.mode == 0) {
+            const int NTn = GnP >> 3;
+            if (q.cont_mode == 0) {
+                for (int mt = warp; mt < NTn; mt += W) {
+                    const double* brow = sBeta + (size_t)(8 * mt + g) * Kp4;
+#pragma unroll 1
+                    for (int nt = 0; nt < TP / 8; nt++) {
+                        double c0 = 0.0, c1 = 0.0;
+                        for (int ks = 0; ks < Kp4; ks += 4) {
+                            const double a = brow[ks + t];
+                            const double b = sNP[(size_t)sNodeP[ks + t] * LD + 8 * nt + g];
+                            dmma8x8x4(c0, c1, a, b);
+                        }
+                        *reinterpret_cast<double2*>(sC + (size_t)(8 * mt + g) * LD + 8 * nt + 2 * t) = make_double2(c0, c1);
+                    }
+                }
+            } else {
+                for (int i = tid; i < q.Gn * TP; i += blockDim.x) {
+                    int l = i / TP, c = i % TP;
+                    sC[(size_t)l * LD + c] = __ldg(q.beta + (size_t)l * q.ldb);
+                }
+            }
+            __syncthreads();
+        }
+        // ---- decisions + normal-equation accumulation ----
+#pragma unroll
+        for (int jj = 0; jj < NTW; jj++) {
+            const int j = warp + jj * W;
+            if (j >= NTaug) break;
+            if (j < NT) {
+                const int i = 8 * j + g;
+                const bool row_ok = i < q.G;
+                // decision table of this lane's grid row -> registers (specialised for up to 3 decisions; more
+                // decisions re-read the table from L1 inside the loop)
+                int nd = 0; double invc = 0.0, gridv = 0.0;
+                double dv[3], dc[3], dm[3], wl[3], wh[3]; int lo[3], hi[3];
+                const size_t trow = (size_t)(row_ok ? i : 0) * q.max_dec;
+                if (q.mode == 0) {
+                    if (row_ok) { nd = __ldg(q.t_ndec + i); invc = __ldg(q.t_invcost + i); }
+#pragma unroll
+                    for (int d = 0; d < 3; d++) {
+                        const bool on = d < nd;
+                        dv[d] = on ? __ldg(q.t_vol + trow + d) : 0.0;
+                        dc[d] = on ? __ldg(q.t_cost + trow + d) : 0.0;
+                        dm[d] = on ? __ldg(q.t_cons + trow + d) : 0.0;
+                        wl[d] = on ? __ldg(q.t_wlo + trow + d) : 0.0;
+                        wh[d] = on ? __ldg(q.t_whi + trow + d) : 0.0;
+                        lo[d] = on ? __ldg(q.t_lo + trow + d) : 0;
+                        hi[d] = on ? __ldg(q.t_hi + trow + d) : 0;
+                    }
+                } else if (row_ok) gridv = __ldg(q.grid + i);
+#pragma unroll 2
+                for (int ks = 0; ks < TP / 4; ks++) {
+                    const int path = 4 * ks + t;
+                    double v = 0.0;
+                    if (row_ok) {
+                        const double s = sNP[2 * LD + path];
+                        if (q.mode == 1) {
+                            v = q.must_be_empty ? 0.0
+                                : add_rn(add_rn(add_rn(q.tc0, mul_rn(q.tc1, s)), mul_rn(q.tc2, gridv)), mul_rn(q.tc3, mul_rn(s, gridv)));
+                        } else {
+                            double best = 0.0, bestC = 0.0; int bl = 0, bh = 0; double bwl = 1.0, bwh = 0.0;
+                            auto consider = [&](int d, double vol, double cost, double cons, double wlo, double whi, int l, int h) {
+                                const double a = mul_rn(mul_rn(-vol, s), q.df);
+                                const double c = mul_rn(mul_rn(-cons, s), q.df);
+                                const double imm = add_rn(sub_rn(a, cost), c);
+                                const double cl = sC[(size_t)l * LD + path];
+                                double cont = cl;
+                                if (h != l) cont = add_rn(mul_rn(sC[(size_t)h * LD + path], whi), mul_rn(cl, wlo));
+                                const double tot = sub_rn(add_rn(imm, cont), invc);
+                                if (d == 0 || tot > best) { best = tot; bestC = cont; bl = l; bh = h; bwl = wlo; bwh = whi; }
+                            };
+                            if (nd <= 3) {
+#pragma unroll
+                                for (int d = 0; d < 3; d++)
+                                    if (d < nd) consider(d, dv[d], dc[d], dm[d], wl[d], wh[d], lo[d], hi[d]);
+                            } else {
+                                for (int d = 0; d < nd; d++)
+                                    consider(d, __ldg(q.t_vol + trow + d), __ldg(q.t_cost + trow + d), __ldg(q.t_cons + trow + d),
+                                             __ldg(q.t_wlo + trow + d), __ldg(q.t_whi + trow + d), __ldg(q.t_lo + trow + d), __ldg(q.t_hi + trow + d));
+                            }
+                            const double al = sVn[(size_t)bl * LD + path];
+                            double act = al;
+                            if (bh != bl) act = add_rn(mul_rn(sVn[(size_t)bh * LD + path], bwh), mul_rn(al, bwl));
+                            v = add_rn(best, add_rn(-bestC, act));
+                        }
+                        __stcs(q.Vout + (size_t)i * q.Npad + n0 + path, v);
+                    }
+                    if (q.accum_mode) {
+#pragma unroll
+                        for (int m = 0; m < MT; m++) {
+                            const double a = sNM[(size_t)sNodeM[8 * m + g] * LD + path];
+                            dmma8x8x4(acc[jj][m][0], acc[jj][m][1], a, v);
+                        }
+                    }
+                }
+            } else {
+                // trailing n-tiles: B = X_{p-1} itself -> X^T X
+                const int kb = 8 * (j - NT) + g;
+                const int16_t bnode = sNodeM[kb];
+                for (int ks = 0; ks < TP / 4; ks++) {
+                    const int path = 4 * ks + t;
+                    const double b = sNM[(size_t)bnode * LD + path];
+#pragma unroll
+                    for (int m = 0; m < MT; m++) {
+                        const double a = sNM[(size_t)sNodeM[8 * m + g] * LD + path];
+                        dmma8x8x4(acc[jj][m][0], acc[jj][m][1], a, b);
+                    }
+                }
+            }
+        }
+    }
+    // ---- per-CTA partial: partial[cta][k][col], k = 8m+g, col = 8j+2t ----
+    if (q.accum_mode) {
+        double* out = q.partial + (size_t)blockIdx.x * (8 * MT) * q.ncols;
+#pragma unroll
+        for (int jj = 0; jj < NTW; jj++) {
+            const int j = warp + jj * W;
+            if (j >= NTaug) break;
+#pragma unroll
+            for (int m = 0; m < MT; m++)
+                *reinterpret_cast<double2*>(out + (size_t)(8 * m + g) * q.ncols + 8 * j + 2 * t) = make_double2(acc[jj][m][0], acc[jj][m][1]);
+        }
+    }
+}
+
+size_t sweep_smem_bytes(int TP, int Gn, int n_nodes, int ldb) {
+    const int LD = TP + 8, GnP = (Gn + 7) & ~7;
+    return sizeof(double) * ((size_t)2 * GnP * LD + (size_t)2 * n_nodes * LD + (size_t)GnP * ldb);
+}
+
+template <int TP, int MT, int NTW>
+static cudaError_t launch_sweep_t(const SweepParams& q, int blocks, int warps, size_t smem, cudaStream_t stream) {
+    auto kern = sweep_kernel<TP, MT, NTW>;
+    static size_t configured = 0;
+    if (smem > configured) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        configured = smem;
+    }
+    kern<<<blocks, warps * 32, smem, stream>>>(q);
+    return cudaGetLastError();
+}
+
+template <int TP>
+static cudaError_t launch_sweep_tp(const SweepParams& q, int MT, int NTW, int blocks, int warps, size_t smem, cudaStream_t s) {
+#define ROW(mt) \
+    if (MT == mt) { \
+        if (NTW == 1) return launch_sweep_t<TP, mt, 1>(q, blocks, warps, smem, s); \
+        if (NTW == 2) return launch_sweep_t<TP, mt, 2>(q, blocks, warps, smem, s); \
+        return launch_sweep_t<TP, mt, 4>(q, blocks, warps, smem, s); \
+    }
+    ROW(1) ROW(2) ROW(4) ROW(8)
+#undef ROW
+    return cudaErrorInvalidValue;
+}
+
+// Chooses the launch shape: one warp per 8-row n-tile (decision tiles + basis tiles), at most 16 warps.
+cudaError_t launch_sweep(SweepParams& q, const SweepConfig& cfg, cudaStream_t stream) {
+    const int MT = cfg.MT;
+    const int NT = (q.G + 7) / 8;
+    const int NTaug = q.accum_mode ? NT + MT : NT;
+    const int NTn = (q.Gn + 7) / 8;
+    int warps = std::max(std::max(NTaug, NTn), (2 * cfg.TP + 31) / 32);
+    warps = std::min(std::max(warps, 4), 16);
+    int ntw = (NTaug + warps - 1) / warps;
+    int NTW = ntw <= 1 ? 1 : (ntw <= 2 ? 2 : 4);
+    if (ntw > 4) return cudaErrorInvalidValue;
+    q.ncols = 8 * (NT + MT);
+    const size_t smem = sweep_smem_bytes(cfg.TP, q.Gn, cfg.n_nodes, q.ldb);
+    if (cfg.TP == 64) return launch_sweep_tp<64>(q, MT, NTW, cfg.blocks, warps, smem, stream);
+    return launch_sweep_tp<32>(q, MT, NTW, cfg.blocks, warps, smem, stream);
+}
+
+// =================================================================================================
+// K2a: deterministic reduction of the per-CTA partials: one warp per element, fixed lane/CTA order.
+// =================================================================================================
+__global__ void __launch_bounds__(256) reduce_partials_kernel(const double* __restrict__ partial, int n_parts, int n_elem,
+                                                              double* __restrict__ out) {
+    const int e = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (e >= n_elem) return;
+    double s = 0.0;
+    for (int c = lane; c < n_parts; c += 32) s += partial[(size_t)c * n_elem + e];
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
+    if (lane == 0) out[e] = s;
+}
+
+void launch_reduce_partials(const double* partial, int n_parts, int n_elem, double* out, cudaStream_t stream) {
+    const int wpb = 8;
+    reduce_partials_kernel<<<(n_elem + wpb - 1) / wpb, wpb * 32, 0, stream>>>(partial, n_parts, n_elem, out);
+}
+
+// =================================================================================================
+// K2b: solve the normal equations for all grid points of one period.
+//   reduced[k][col]: col < G -> X^T V_i ; col = 8*NT + k' -> X^T X.
+// Column-equilibrated Cholesky (G~ = D G D, D = diag(G)^-1/2) with a pivot guard that drops numerically dependent
+// columns, one step of iterative refinement against the unscaled system, beta = D x.
+// =================================================================================================
+__global__ void __launch_bounds__(256) solve_kernel(SolveParams sp) {
+    extern __shared__ double sm[];
+    const int K = sp.K, G = sp.G, ld = sp.ncols, tid = threadIdx.x;
+    const double* red = sp.reduced;
+    if (sp.accum_mode == 2) {   // current period: continuation = mean over sims (LSV.cs:171-182)
+        for (int i = tid; i < G; i += blockDim.x) {
+            double* b = sp.beta + (size_t)i * sp.ldb;
+            b[0] = red[i] / (double)sp.n_global;
+            for (int k = 1; k < sp.ldb; k++) b[k] = 0.0;
+        }
+        return;
+    }
+    double* A = sm;                 // [K][K] scaled Gram -> Cholesky factor (lower)
+    double* Graw = A + K * K;       // [K][K] unscaled Gram
+    double* dscale = Graw + K * K;  // [K]
+    __shared__ int dropped[64];
+    const int gcol = 8 * sp.NT;
+    for (int k = tid; k < K; k += blockDim.x) {
+        double gkk = red[(size_t)k * ld + gcol + k];
+        dscale[k] = gkk > 0.0 ? rsqrt(gkk) : 0.0;
+        dropped[k] = gkk > 0.0 ? 0 : 1;
+    }
+    __syncthreads();
+    for (int e = tid; e < K * K; e += blockDim.x) {
+        int r = e / K, c = e % K;
+        // symmetrise: the two triangles come from different DMMA tiles and may differ in the last bit
+        double gv = 0.5 * (red[(size_t)r * ld + gcol + c] + red[(size_t)c * ld + gcol + r]);
+        Graw[e] = gv;
+        A[e] = gv * dscale[r] * dscale[c];
+    }
+    __syncthreads();
+    for (int j = 0; j < K; j++) {
+        if (tid == 0) {
+            double piv = A[j * K + j];
+            if (dropped[j] || !(piv > sp.pivot_tol)) { dropped[j] = 1; A[j * K + j] = 1.0; }
+            else A[j * K + j] = sqrt(piv);
+        }
+        __syncthreads();
+        const bool dj = dropped[j];
+        const double ljj = A[j * K + j];
+        for (int i = j + 1 + tid; i < K; i += blockDim.x) A[i * K + j] = dj ? 0.0 : A[i * K + j] / ljj;
+        __syncthreads();
+        const int rem = K - j - 1;
+        for (int e = tid; e < rem * rem; e += blockDim.x) {
+            int i = j + 1 + e / rem, k = j + 1 + e % rem;
+            if (k <= i) A[i * K + k] -= A[i * K + j] * A[k * K + j];
+        }
+        __syncthreads();
+    }
+    // each thread: one right-hand side at a time
+    for (int i = tid; i < G; i += blockDim.x) {
+        double x[64], r[64];
+        for (int k = 0; k < K; k++) { r[k] = red[(size_t)k * ld + i]; x[k] = 0.0; }
+        for (int pass = 0; pass < 2; pass++) {
+            double y[64];
+            for (int k = 0; k < K; k++) {   // L y = D r
+                double s = r[k] * dscale[k];
+                for (int m = 0; m < k; m++) s -= A[k * K + m] * y[m];
+                y[k] = dropped[k] ? 0.0 : s / A[k * K + k];
+            }
+            for (int k = K - 1; k >= 0; k--) {   // L^T z = y
+                double s = y[k];
+                for (int m = k + 1; m < K; m++) s -= A[m * K + k] * y[m];
+                y[k] = dropped[k] ? 0.0 : s / A[k * K + k];
+            }
+            for (int k = 0; k < K; k++) x[k] += y[k] * dscale[k];
+            if (pass == 0) {   // residual of the unscaled system
+                for (int k = 0; k < K; k++) {
+                    double s = red[(size_t)k * ld + i];
+                    for (int m = 0; m < K; m++) s = fma(-Graw[k * K + m], x[m], s);
+                    r[k] = dropped[k] ? 0.0 : s;
+                }
+            }
+        }
+        double* b = sp.beta + (size_t)i * sp.ldb;
+        for (int k = 0; k < sp.ldb; k++) b[k] = k < K ? x[k] : 0.0;
+    }
+}
+
+void launch_solve(const SolveParams& sp, cudaStream_t stream) {
+    size_t smem = sizeof(double) * ((size_t)2 * sp.K * sp.K + sp.K);
+    solve_kernel<<<1, 256, smem, stream>>>(sp);
+}
+
+// =================================================================================================
+// K4: forward simulation of one period (LSV.cs:426-480).  One thread per path (grid-stride), state = inventory and
+// accumulated PV; only the <= 2 fitted values per decision that are actually needed are evaluated (x.beta_l on
+// demand) instead of the reference's full N x G product (LSV.cs:395-401).  Block-level sums feed the expected
+// profile, deltas and trigger prices.
+// =================================================================================================
+__device__ __forceinline__ int last_at_or_below(const double* x, int n, double v) {
+    int lo = 0, hi = n;   // first index with x > v
+    while (lo < hi) { int mid = (lo + hi) >> 1; if (__ldg(x + mid) <= v) lo = mid + 1; else hi = mid; }
+    return lo - 1;
+}
+
+__device__ __forceinline__ double spline_dev(const double* x, const double* y, int n, double v) {
+    int k = min(max(last_at_or_below(x, n, v), 0), n - 2);
+    double x0 = __ldg(x + k), y0 = __ldg(y + k);
+    double slope = (__ldg(y + k + 1) - y0) / (__ldg(x + k + 1) - x0);
+    return add_rn(y0, mul_rn(sub_rn(v, x0), slope));
+}
+
+// StorageHelper.BisectInventorySpace (SH.cs:280-314); returns false when outside the grid.
+__device__ __forceinline__ bool bisect_dev(const double* grid, int n, double inv, double tol, int& lo, int& hi) {
+    if (n == 1 && fabs(inv - __ldg(grid)) <= tol) { lo = hi = 0; return true; }
+    int left = 0, right = n - 1;
+    const int top = right;
+    while (right > left) {
+        int mid = (left + right) >> 1;
+        double gm = __ldg(grid + mid);
+        if (fabs(inv - gm) <= tol) { lo = hi = mid; return true; }
+        if (gm > inv) { right = mid; continue; }
+        double gn = __ldg(grid + mid + 1);
+        if (inv <= gn) { lo = mid; hi = mid + 1; return true; }
+        if (fabs(inv - gn) <= tol) { lo = hi = mid + 1; return true; }
+        if (mid + 1 == top) return false;
+        left = mid;
+    }
+    return false;
+}
+
+constexpr int kFwdMaxDec = 16;
+
+__global__ void __launch_bounds__(256) forward_kernel(ForwardParams q) {
+    const BasisDev* __restrict__ bd = q.basis;
+    const int K = q.K, nsum = kFwdSums + K;
+    extern __shared__ double fsm[];   // [warps][nsum]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    double sums[kFwdSums];
+#pragma unroll
+    for (int i = 0; i < kFwdSums; i++) sums[i] = 0.0;
+    double xsum[64];
+    for (int k = 0; k < K; k++) xsum[k] = 0.0;
+
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; n < q.N; n += stride) {
+        const double s = q.spot_is_const ? q.spot_const : __ldcs(q.spot + n);
+        const double v = q.inventory[n];
+        double xrow[64];
+        if (q.cont_mode == 0) {
+            double nodes[kMaxNodes];
+            nodes[0] = 0.0; nodes[1] = 1.0; nodes[2] = s;
+            for (int f = 0; f < q.F; f++) nodes[3 + f] = __ldcs(q.fac + (size_t)f * q.Npad + n);
+            for (int o = 0; o < bd->n_ops; o++) {
+                const BasisOpDev op = bd->ops[o];
+                nodes[op.dst] = mul_rn(nodes[op.a], nodes[op.b]);
+            }
+            for (int k = 0; k < K; k++) { xrow[k] = nodes[bd->node_of_basis[k]]; xsum[k] += xrow[k]; }
+        }
+        // CmdtyStorage.GetInjectWithdrawRange (CmdtyStorage.cs:86-100)
+        if (v < q.min_inv || v > q.max_inv) atomicExch(q.error_flag, 1);
+        double rmin, rmax;
+        if (q.c_kind == LSMC_CONSTRAINT_CONSTANT) { rmin = __ldg(q.c_lo); rmax = __ldg(q.c_hi); }
+        else if (q.c_kind == LSMC_CONSTRAINT_PIECEWISE_LINEAR) { rmax = spline_dev(q.c_x, q.c_hi, q.c_n, v); rmin = spline_dev(q.c_x, q.c_lo, q.c_n, v); }
+        else {
+            if (v < __ldg(q.c_x) || v > __ldg(q.c_x + q.c_n - 1)) atomicExch(q.error_flag, 2);
+            int idx = min(max(last_at_or_below(q.c_x, q.c_n, v), 0), q.c_n - 1);
+            rmin = __ldg(q.c_lo + idx); rmax = __ldg(q.c_hi + idx);
+        }
+        const double loss = mul_rn(q.loss_pct, v);
+        // bang-bang decision set (SH.cs:109-197)
+        double dec[kFwdMaxDec];
+        int nd;
+        {
+            const double base = sub_rn(v, loss);
+            const double afterW = add_rn(rmin, base), afterJ = add_rn(rmax, base);
+            double w, jn;
+            if (afterW > q.next_max) { if (!(sub_rn(afterW, q.next_max) < q.tol)) atomicExch(q.error_flag, 3); w = sub_rn(q.next_max, base); }
+            else w = afterW > q.next_min ? rmin : sub_rn(q.next_min, base);
+            if (afterJ < q.next_min) { if (!(sub_rn(q.next_min, afterJ) < q.tol)) atomicExch(q.error_flag, 3); jn = sub_rn(q.next_min, base); }
+            else jn = afterJ < q.next_max ? rmax : sub_rn(q.next_max, base);
+            const int ex = q.extra;
+            if (w >= 0.0 || jn <= 0.0) {
+                nd = ex + 2;
+                dec[0] = w;
+                const double step = (jn - w) / (ex + 1);
+                for (int i = 0; i < ex; i++) dec[1 + i] = add_rn(mul_rn((double)(i + 1), step), w);
+                dec[nd - 1] = jn;
+            } else {
+                nd = 2 * ex + 3;
+                dec[0] = w;
+                const double stepw = (0.0 - w) / (ex + 1), stepj = (jn - 0.0) / (ex + 1);
+                for (int i = 0; i < ex; i++) { dec[1 + i] = add_rn(mul_rn((double)(i + 1), stepw), w); dec[ex + 2 + i] = add_rn(mul_rn((double)(i + 1), stepj), 0.0); }
+                dec[ex + 1] = 0.0;
+                dec[nd - 1] = jn;
+            }
+        }
+        const double inv_cost_npv = q.inv_cost == 0.0 ? 0.0 : mul_rn(mul_rn(v, q.inv_cost), q.inv_cost_df);
+        double best = 0.0, best_imm = 0.0, best_cons = 0.0, best_vol = 0.0;
+        int best_d = 0;
+        for (int d = 0; d < nd; d++) {
+            const double vol = dec[d];
+            const double after = sub_rn(add_rn(v, vol), loss);
+            const double cons = vol > 0.0 ? mul_rn(q.cons_inj, fabs(vol)) : mul_rn(q.cons_wd, fabs(-vol));
+            const double a = mul_rn(mul_rn(-vol, s), q.df);
+            const double c = mul_rn(mul_rn(-cons, s), q.df);
+            const double cost = vol > 0.0 ? mul_rn(mul_rn(q.inj_cost, vol), q.inj_df) : mul_rn(mul_rn(q.wd_cost, fabs(-vol)), q.wd_df);
+            const double imm = sub_rn(add_rn(sub_rn(a, cost), c), inv_cost_npv);
+            int lo, hi;
+            if (!bisect_dev(q.next_grid, q.Gn, after, q.tol, lo, hi)) { atomicExch(q.error_flag, 4); lo = hi = 0; }
+            auto fitted = [&](int l) {
+                const double* b = q.beta + (size_t)l * q.ldb;
+                if (q.cont_mode == 1) return __ldg(b);
+                double acc = 0.0;
+                for (int k = 0; k < K; k++) acc = fma(xrow[k], __ldg(b + k), acc);
+                return acc;
+            };
+            double cont;
+            if (lo == hi) cont = fitted(lo);
+            else {
+                const double gl = __ldg(q.next_grid + lo), gu = __ldg(q.next_grid + hi);
+                const double wl = sub_rn(gu, after) / sub_rn(gu, gl);
+                const double wu = sub_rn(1.0, wl);
+                cont = add_rn(mul_rn(fitted(lo), wl), mul_rn(fitted(hi), wu));
+            }
+            const double tot = add_rn(imm, cont);
+            if (d == 0 || tot > best) { best = tot; best_imm = imm; best_cons = cons; best_vol = vol; best_d = d; }
+        }
+        const double next_inv = sub_rn(add_rn(v, best_vol), loss);
+        q.inventory[n] = next_inv;
+        q.pv_by_sim[n] = add_rn(q.pv_by_sim[n], best_imm);
+        const double net = sub_rn(-best_vol, best_cons);
+        sums[0] += v; sums[1] += best_vol; sums[2] += best_cons; sums[3] += loss; sums[4] += net; sums[5] += best_imm;
+        sums[6] += mul_rn(-(add_rn(best_vol, best_cons)), s);
+        if (q.o_inventory) __stcs(q.o_inventory + n, v);
+        if (q.o_volume) __stcs(q.o_volume + n, best_vol);
+        if (q.o_consumed) __stcs(q.o_consumed + n, best_cons);
+        if (q.o_loss) __stcs(q.o_loss + n, loss);
+        if (q.o_net) __stcs(q.o_net + n, net);
+        if (q.o_pv) __stcs(q.o_pv + n, best_imm);
+        if (q.o_decision) q.o_decision[n] = (int8_t)best_d;
+    }
+    // block reduction (fixed order)
+    for (int i = 0; i < nsum; i++) {
+        double val = i < kFwdSums ? sums[i] : xsum[i - kFwdSums];
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) val += __shfl_xor_sync(0xffffffffu, val, off);
+        if (lane == 0) fsm[warp * nsum + i] = val;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < nsum; i += blockDim.x) {
+        double tot = 0.0;
+        for (int w = 0; w < nwarps; w++) tot += fsm[w * nsum + i];
+        q.sums[(size_t)blockIdx.x * nsum + i] = tot;
+    }
+}
+
+void launch_forward(const ForwardParams& q, int blocks, cudaStream_t stream) {
+    const int threads = 256;
+    size_t smem = sizeof(double) * (threads / 32) * (kFwdSums + q.K);
+    forward_kernel<<<blocks, threads, smem, stream>>>(q);
+}
+
+// Column reduction of block partials: out[r][c] = sum_b in[r][b][c]; one warp per (r, c).
+__global__ void __launch_bounds__(256) reduce_rows_kernel(const double* __restrict__ in, int n_rows, int n_blocks, int n_cols,
+                                                          double* __restrict__ out) {
+    const int e = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (e >= n_rows * n_cols) return;
+    const int r = e / n_cols, c = e % n_cols;
+    double s = 0.0;
+    for (int b = lane; b < n_blocks; b += 32) s += in[((size_t)r * n_blocks + b) * n_cols + c];
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
+    if (lane == 0) out[e] = s;
+}
+
+void launch_reduce_rows(const double* in, int n_rows, int n_blocks, int n_cols, double* out, cudaStream_t stream) {
+    const int wpb = 8, n = n_rows * n_cols;
+    reduce_rows_kernel<<<(n + wpb - 1) / wpb, wpb * 32, 0, stream>>>(in, n_rows, n_blocks, n_cols, out);
+}
+
+// Final period (LSV.cs:563-579) + sums for NPV / final inventory / standard error.
+//   pass 0: pv += terminal value on the regression sims' end prices; block sums {final inventory, terminal pv, pv}
+//   pass 1: sum of squared deviations of (pair means of) pv from the mean
+__global__ void __launch_bounds__(256) final_kernel(FinalParams q) {
+    __shared__ double sm[8][3];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double a0 = 0.0, a1 = 0.0, a2 = 0.0;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    if (q.pass == 0) {
+        for (int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; n < q.N; n += stride) {
+            const double inv = q.inventory[n];
+            double tpv = 0.0;
+            if (!q.must_be_empty) {
+                const double s = q.spot_end[n];
+                tpv = add_rn(add_rn(add_rn(q.tc0, mul_rn(q.tc1, s)), mul_rn(q.tc2, inv)), mul_rn(q.tc3, mul_rn(s, inv)));
+                q.pv_by_sim[n] = add_rn(q.pv_by_sim[n], tpv);
+            }
+            if (q.o_inventory) q.o_inventory[n] = inv;
+            if (q.o_pv) q.o_pv[n] = tpv;
+            a0 += inv; a1 += tpv; a2 += q.pv_by_sim[n];
+        }
+    } else {
+        const int64_t m = q.paired ? q.N / 2 : q.N;
+        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < m; i += stride) {
+            const double v = q.paired ? 0.5 * (q.pv_by_sim[2 * i] + q.pv_by_sim[2 * i + 1]) : q.pv_by_sim[i];
+            const double dlt = v - q.mean;
+            a0 += dlt * dlt;
+        }
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        a0 += __shfl_xor_sync(0xffffffffu, a0, off);
+        a1 += __shfl_xor_sync(0xffffffffu, a1, off);
+        a2 += __shfl_xor_sync(0xffffffffu, a2, off);
+    }
+    if (lane == 0) { sm[warp][0] = a0; sm[warp][1] = a1; sm[warp][2] = a2; }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+        double tot = 0.0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); w++) tot += sm[w][threadIdx.x];
+        q.sums[(size_t)blockIdx.x * 3 + threadIdx.x] = tot;
+    }
+}
+
+void launch_final(const FinalParams& q, int blocks, cudaStream_t stream) { final_kernel<<<blocks, 256, 0, stream>>>(q); }
+
+__global__ void fill_kernel(double* p, int64_t n, double v) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) p[i] = v;
+}
+
+void launch_fill(double* p, int64_t n, double v, cudaStream_t stream) {
+    int blocks = (int)std::min<int64_t>((n + 255) / 256, 148 * 8);
+    fill_kernel<<<blocks, 256, 0, stream>>>(p, n, v);
+}
+
+}  // namespace lsmc

@@ -1,0 +1,46 @@
+// kernels.h — launchers of the sm_100a kernels (kernels.cu).
+#pragma once
+#include <algorithm>
+#include <cstddef>
+#include "../../include/lsmc_b200.h"
+#include "lsmc_device.cuh"
+
+namespace lsmc {
+
+struct SweepConfig {
+    int TP;        // paths per tile (32 or 64)
+    int MT;        // basis m-tiles: 1, 2, 4 or 8 (8*MT >= K)
+    int blocks;    // persistent CTAs
+    int n_nodes;   // basis-program nodes
+};
+
+struct SolveParams {
+    const double* reduced;   // [8*MT][ncols]
+    int ncols, K, G, NT, ldb, accum_mode;
+    int64_t n_global;
+    double pivot_tol;
+    double* beta;            // [G][ldb]
+};
+
+struct FinalParams {
+    int64_t N;
+    int pass, must_be_empty, paired;
+    double tc0, tc1, tc2, tc3, mean;
+    const double* spot_end;
+    const double* inventory;
+    double* pv_by_sim;
+    double* sums;            // [gridDim.x][3]
+    double* o_inventory; double* o_pv;
+};
+
+size_t sweep_smem_bytes(int TP, int Gn, int n_nodes, int ldb);
+void launch_simulate(const SimParams& sp, cudaStream_t stream);
+cudaError_t launch_sweep(SweepParams& q, const SweepConfig& cfg, cudaStream_t stream);
+void launch_reduce_partials(const double* partial, int n_parts, int n_elem, double* out, cudaStream_t stream);
+void launch_solve(const SolveParams& sp, cudaStream_t stream);
+void launch_forward(const ForwardParams& q, int blocks, cudaStream_t stream);
+void launch_reduce_rows(const double* in, int n_rows, int n_blocks, int n_cols, double* out, cudaStream_t stream);
+void launch_final(const FinalParams& q, int blocks, cudaStream_t stream);
+void launch_fill(double* p, int64_t n, double v, cudaStream_t stream);
+
+}  // namespace lsmc

@@ -1,0 +1,786 @@
+// lsmc_api.cu — the C ABI (include/lsmc_b200.h): context, device memory, per-period orchestration.
+// Replaces the body of LsmcStorageValuation.Calculate<T> (LSV.cs:97-616) behind plain pointers and sizes.
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <dlfcn.h>
+#include <limits>
+#include <string>
+#include <vector>
+
+#include "host_plan.h"
+#include "kernels.h"
+
+using namespace lsmc;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+#define CUDA_CHECK(expr)                                                                              \
+    do {                                                                                              \
+        cudaError_t _e = (expr);                                                                      \
+        if (_e != cudaSuccess)                                                                        \
+            throw Error(LSMC_ECUDA, std::string(#expr) + ": " + cudaGetErrorString(_e));              \
+    } while (0)
+
+template <typename T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t n = 0;
+    void alloc(size_t count) {
+        if (count <= n && p) return;
+        release();
+        CUDA_CHECK(cudaMalloc(&p, std::max<size_t>(count, 1) * sizeof(T)));
+        n = count;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+    void upload(const std::vector<T>& h, cudaStream_t s) {
+        alloc(h.size());
+        if (!h.empty()) CUDA_CHECK(cudaMemcpyAsync(p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice, s));
+    }
+    ~DevBuf() { release(); }
+};
+
+// ---- NCCL through dlopen: the library has no link-time dependency on it --------------------------------------
+struct NcclApi {
+    void* handle = nullptr;
+    int (*GetUniqueId)(void*) = nullptr;
+    int (*CommInitRank)(void**, int, char[128], int) = nullptr;   // ncclUniqueId is a 128-byte struct passed by value
+    int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*CommDestroy)(void*) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+    bool load(std::string& err) {
+        if (handle) return true;
+        const char* names[] = {"libnccl.so.2", "libnccl.so"};
+        for (const char* nm : names) { handle = dlopen(nm, RTLD_NOW | RTLD_GLOBAL); if (handle) break; }
+        if (!handle) { err = "cannot dlopen libnccl.so.2"; return false; }
+        GetUniqueId = (int (*)(void*))dlsym(handle, "ncclGetUniqueId");
+        CommInitRank = (int (*)(void**, int, char[128], int))dlsym(handle, "ncclCommInitRank");
+        AllReduce = (int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t))dlsym(handle, "ncclAllReduce");
+        CommDestroy = (int (*)(void*))dlsym(handle, "ncclCommDestroy");
+        GetErrorString = (const char* (*)(int))dlsym(handle, "ncclGetErrorString");
+        if (!GetUniqueId || !CommInitRank || !AllReduce || !CommDestroy) { err = "libnccl is missing symbols"; return false; }
+        return true;
+    }
+};
+NcclApi g_nccl;
+struct NcclId { char bytes[128]; };
+
+}  // namespace
+
+struct lsmc_ctx {
+    int device = 0, num_sms = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    bool has_problem = false, sims_ready[2] = {false, false}, backward_done = false, forward_done = false;
+    Plan plan;
+    int64_t N = 0, Npad = 0, Nglobal = 0;
+    int TP = 64, MT = 1, ldb = 4, sweep_blocks = 0, fwd_blocks = 0, ncols_max = 0;
+    uint32_t outputs = 0;       // bit0 per-sim panels, bit1 decision index
+    bool keep_values = false;
+    int valuation_antithetic = 0;
+
+    DevBuf<double> spot[2], fac, Vbuf, Vall, beta_all, grid, partial, reduced, inventory, pv_by_sim, fwd_sums, fwd_red, fin_sums;
+    DevBuf<double> t_invcost, t_vol, t_cost, t_cons, t_wlo, t_whi, c_x, c_lo, c_hi;
+    DevBuf<int32_t> t_ndec, t_lo, t_hi;
+    DevBuf<double> s_decay, s_chol, s_vol, s_drift, s_fwd, normals_stage;
+    DevBuf<BasisDev> basis;
+    DevBuf<int> error_flag;
+    DevBuf<double> panels[6];
+    DevBuf<int8_t> decisions;
+    std::vector<char> beta_override_set;   // [P-1]
+    std::vector<double> beta_override;     // [P-1][max_grid][ldb]
+
+    // multi-GPU
+    void* comm = nullptr;
+    int rank = 0, world = 1;
+
+    // results staged on host
+    double backward_npv = 0.0, npv = 0.0, npv_se = 0.0, final_inventory_sum = 0.0, terminal_pv_sum = 0.0;
+    std::vector<double> h_fwd;   // [P-1][nsum]
+
+    // timings
+    lsmc_timings tm{};
+    std::vector<cudaEvent_t> ev;
+
+    ~lsmc_ctx() {
+        for (auto e : ev) cudaEventDestroy(e);
+        if (comm && g_nccl.CommDestroy) g_nccl.CommDestroy(comm);
+        if (stream) cudaStreamDestroy(stream);
+    }
+    size_t beta_stride() const { return (size_t)(plan.max_grid + 8) * ldb; }
+    double* V(int which) { return Vbuf.p + (size_t)which * plan.max_grid * Npad; }
+    cudaEvent_t event(size_t i) {
+        while (ev.size() <= i) { cudaEvent_t e; CUDA_CHECK(cudaEventCreate(&e)); ev.push_back(e); }
+        return ev[i];
+    }
+    void allreduce(double* buf, size_t count) {
+        if (world <= 1) return;
+        int rc = g_nccl.AllReduce(buf, buf, count, /*ncclFloat64*/ 8, /*ncclSum*/ 0, comm, stream);
+        if (rc != 0) throw Error(LSMC_ECUDA, std::string("ncclAllReduce: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "error"));
+    }
+};
+
+namespace {
+
+template <typename Fn>
+int guarded(lsmc_ctx* ctx, Fn&& fn) {
+    try {
+        if (ctx) CUDA_CHECK(cudaSetDevice(ctx->device));
+        fn();
+        return LSMC_OK;
+    } catch (const Error& e) {
+        if (ctx) ctx->err = e.what(); else g_create_error = e.what();
+        return e.status;
+    } catch (const std::exception& e) {
+        if (ctx) ctx->err = e.what(); else g_create_error = e.what();
+        return LSMC_EINVAL;
+    }
+}
+
+void require(bool ok, int status, const char* msg) { if (!ok) throw Error(status, msg); }
+
+void check_device_error_flag(lsmc_ctx* c) {
+    int flag = 0;
+    CUDA_CHECK(cudaMemcpyAsync(&flag, c->error_flag.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    switch (flag) {
+        case 0: return;
+        case 1: case 2: throw Error(LSMC_EINVAL, "A simulated inventory is outside the storage's allowed inventory range (CmdtyStorage.GetInjectWithdrawRange).");
+        case 3: throw Error(LSMC_EINVAL, "Inventory constraints cannot be fulfilled. This could potentially be fixed by increasing the numerical tolerance.");
+        default: throw Error(LSMC_EINVAL, "Inventory is outside of inventoryGrid bounds.");
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+void set_problem(lsmc_ctx* c, const lsmc_problem* problem) {
+    require(problem != nullptr, LSMC_EINVAL, "problem is null");
+    c->has_problem = false;
+    build_plan(*problem, c->plan);
+    Plan& pl = c->plan;
+    const lsmc_problem& pb = pl.problem.pb;
+    c->N = pb.n_sims;
+    c->Nglobal = pb.n_sims_global > 0 ? pb.n_sims_global : pb.n_sims;
+    c->MT = pl.K <= 8 ? 1 : (pl.K <= 16 ? 2 : (pl.K <= 32 ? 4 : 8));
+    c->ldb = (pl.K + 3) & ~3;
+    require(pl.basis.n_nodes <= kMaxNodes && (int)pl.basis.ops.size() <= kMaxOps, LSMC_EUNSUPPORTED, "basis functions need too many product nodes");
+    require(pl.max_dec <= 16, LSMC_EUNSUPPORTED, "extra_decisions above 6 is not supported on the device path");
+    c->TP = sweep_smem_bytes(64, pl.max_grid, pl.basis.n_nodes, c->ldb) <= 200 * 1024 ? 64 : 32;
+    require(sweep_smem_bytes(c->TP, pl.max_grid, pl.basis.n_nodes, c->ldb) <= 220 * 1024, LSMC_EUNSUPPORTED, "inventory grid / basis too large for the sweep kernel's shared memory");
+    require((pl.max_grid + 7) / 8 + c->MT <= 64, LSMC_EUNSUPPORTED, "inventory grid has too many points for the sweep kernel (max 448)");
+    c->Npad = (c->N + 63) / 64 * 64;
+    c->sweep_blocks = (int)std::min<int64_t>(c->num_sms, c->Npad / c->TP);
+    c->fwd_blocks = (int)std::min<int64_t>((int64_t)c->num_sms * 4, (c->N + 255) / 256);
+    c->ncols_max = 8 * ((pl.max_grid + 7) / 8 + c->MT);
+
+    cudaStream_t s = c->stream;
+    const size_t S = pl.S, F = pl.F, Np = (size_t)c->Npad;
+    for (int set = 0; set < 2; set++) { c->spot[set].alloc(S * Np); CUDA_CHECK(cudaMemsetAsync(c->spot[set].p, 0, S * Np * sizeof(double), s)); }
+    c->fac.alloc(S * F * Np); CUDA_CHECK(cudaMemsetAsync(c->fac.p, 0, S * F * Np * sizeof(double), s));
+    c->Vbuf.alloc((size_t)2 * pl.max_grid * Np);
+    CUDA_CHECK(cudaMemsetAsync(c->Vbuf.p, 0, (size_t)2 * pl.max_grid * Np * sizeof(double), s));
+    if (c->keep_values) c->Vall.alloc((size_t)pl.P * pl.max_grid * Np);
+    c->beta_all.alloc((size_t)(pl.P - 1) * c->beta_stride());
+    CUDA_CHECK(cudaMemsetAsync(c->beta_all.p, 0, c->beta_all.n * sizeof(double), s));
+    c->grid.upload(pl.grid, s);
+    c->partial.alloc((size_t)c->sweep_blocks * 8 * c->MT * c->ncols_max);
+    c->reduced.alloc((size_t)8 * c->MT * c->ncols_max);
+    c->inventory.alloc(Np); c->pv_by_sim.alloc(Np);
+    const int nsum = kFwdSums + pl.K;
+    c->fwd_sums.alloc((size_t)(pl.P - 1) * c->fwd_blocks * nsum);
+    c->fwd_red.alloc((size_t)(pl.P - 1) * nsum);
+    c->fin_sums.alloc((size_t)c->fwd_blocks * 3);
+    c->t_ndec.upload(pl.tables.n_dec, s); c->t_invcost.upload(pl.tables.inv_cost_npv, s);
+    c->t_vol.upload(pl.tables.vol, s); c->t_cost.upload(pl.tables.cost_npv, s); c->t_cons.upload(pl.tables.consumed, s);
+    c->t_wlo.upload(pl.tables.w_lo, s); c->t_whi.upload(pl.tables.w_hi, s);
+    c->t_lo.upload(pl.tables.lo, s); c->t_hi.upload(pl.tables.hi, s);
+    c->c_x.upload(pl.problem.pillar_inventory, s); c->c_lo.upload(pl.problem.pillar_min_rate, s); c->c_hi.upload(pl.problem.pillar_max_rate, s);
+    c->s_decay.upload(pl.sim.decay, s); c->s_chol.upload(pl.sim.chol, s); c->s_vol.upload(pl.sim.vol, s);
+    c->s_drift.upload(pl.sim.drift, s); c->s_fwd.upload(pl.sim.fwd, s);
+    {
+        std::vector<BasisDev> hb(1);
+        BasisDev& b = hb[0];
+        std::memset(&b, 0, sizeof(b));
+        b.n_nodes = pl.basis.n_nodes; b.n_ops = (int)pl.basis.ops.size(); b.K = pl.K; b.F = pl.F;
+        for (size_t i = 0; i < pl.basis.ops.size(); i++) b.ops[i] = BasisOpDev{pl.basis.ops[i].dst, pl.basis.ops[i].a, pl.basis.ops[i].b, 0};
+        for (int k = 0; k < pl.K; k++) b.node_of_basis[k] = pl.basis.node_of_basis[k];
+        c->basis.upload(hb, s);
+        CUDA_CHECK(cudaStreamSynchronize(s));   // hb goes out of scope
+    }
+    c->error_flag.alloc(1);
+    CUDA_CHECK(cudaMemsetAsync(c->error_flag.p, 0, sizeof(int), s));
+    if (c->outputs & 1) for (auto& pbuf : c->panels) pbuf.alloc((size_t)pl.P * Np);
+    if (c->outputs & 2) c->decisions.alloc((size_t)(pl.P - 1) * Np);
+    c->beta_override_set.assign(pl.P - 1, 0);
+    c->beta_override.clear();
+    c->sims_ready[0] = c->sims_ready[1] = c->backward_done = c->forward_done = false;
+    std::memset(&c->tm, 0, sizeof(c->tm));
+    CUDA_CHECK(cudaStreamSynchronize(s));
+    c->has_problem = true;
+}
+
+void simulate(lsmc_ctx* c, int set, const lsmc_rng* rng) {
+    require(c->has_problem, LSMC_EINVAL, "lsmc_set_problem has not been called");
+    require(set == 0 || set == 1, LSMC_EINVAL, "set must be 0 or 1");
+    require(rng != nullptr, LSMC_EINVAL, "rng is null");
+    Plan& pl = c->plan;
+    const size_t S = pl.S, F = pl.F, N = (size_t)c->N, Np = (size_t)c->Npad;
+    cudaStream_t s = c->stream;
+    CUDA_CHECK(cudaEventRecord(c->event(set == 0 ? 0 : 4), s));
+    // the factor panel is shared by both sets: the valuation set is generated after the backward pass has
+    // consumed the regression set, exactly as the reference orders them (LSV.cs:100 vs :346)
+    if (set == 1) require(c->backward_done, LSMC_EINVAL, "simulate the valuation set after lsmc_backward");
+    if (rng->mode == LSMC_RNG_PANELS) {
+        require(rng->spot && rng->factors, LSMC_EINVAL, "LSMC_RNG_PANELS needs spot and factors");
+        CUDA_CHECK(cudaMemcpy2DAsync(c->spot[set].p, Np * sizeof(double), rng->spot, N * sizeof(double), N * sizeof(double), S, cudaMemcpyHostToDevice, s));
+        CUDA_CHECK(cudaMemcpy2DAsync(c->fac.p, Np * sizeof(double), rng->factors, N * sizeof(double), N * sizeof(double), S * F, cudaMemcpyHostToDevice, s));
+    } else {
+        SimParams sp{};
+        sp.N = c->N; sp.Npad = c->Npad; sp.sim_offset = pl.problem.pb.sim_offset;
+        sp.S = pl.S; sp.F = pl.F; sp.mode = rng->mode; sp.antithetic = rng->antithetic; sp.seed = rng->seed;
+        if (rng->mode == LSMC_RNG_NORMALS) {
+            require(rng->normals != nullptr, LSMC_EINVAL, "LSMC_RNG_NORMALS needs normals");
+            c->normals_stage.alloc(S * F * N);
+            CUDA_CHECK(cudaMemcpyAsync(c->normals_stage.p, rng->normals, S * F * N * sizeof(double), cudaMemcpyHostToDevice, s));
+            sp.normals = c->normals_stage.p;
+        } else require(rng->mode == LSMC_RNG_PHILOX, LSMC_EINVAL, "unknown rng mode");
+        sp.decay = c->s_decay.p; sp.chol = c->s_chol.p; sp.vol = c->s_vol.p; sp.drift = c->s_drift.p; sp.fwd = c->s_fwd.p;
+        sp.spot = c->spot[set].p; sp.fac = c->fac.p;
+        launch_simulate(sp, s);
+        CUDA_CHECK(cudaGetLastError());
+        c->tm.kernel_launches++;
+    }
+    if (set == 1) c->valuation_antithetic = (rng->mode == LSMC_RNG_PHILOX && rng->antithetic) ? 1 : 0;
+    CUDA_CHECK(cudaEventRecord(c->event(set == 0 ? 1 : 5), s));
+    c->sims_ready[set] = true;
+    if (set == 0) { c->backward_done = false; }
+    c->forward_done = false;
+}
+
+// Backward induction (LSV.cs:104-341): terminal values, then one fused sweep + reduce + solve per period.
+void backward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
+    require(c->has_problem && c->sims_ready[0], LSMC_EINVAL, "simulate the regression set before lsmc_backward");
+    Plan& pl = c->plan;
+    const lsmc_problem& pb = pl.problem.pb;
+    const int P = pl.P, s0 = pl.s0, F = pl.F, D = pl.max_dec;
+    const size_t Np = (size_t)c->Npad;
+    cudaStream_t s = c->stream;
+    SweepConfig cfg{c->TP, c->MT, c->sweep_blocks, pl.basis.n_nodes};
+    CUDA_CHECK(cudaEventRecord(c->event(2), s));
+    c->tm.backward_sweep_launches = 0;
+    c->tm.sweep_bytes = 0.0;
+    size_t ev_base = 8;
+    int cur = 0;
+    double progress = 0.0;
+    const double back_step = 0.66 / (P - 1);   // BackwardPcntTime (LSV.cs:46,161)
+
+    auto regressors = [&](int period, const double*& spot, const double*& fac) {
+        const int j = period - s0;
+        spot = (j >= 0) ? c->spot[0].p + (size_t)j * Np : nullptr;
+        fac = (j >= 0) ? c->fac.p + (size_t)j * F * Np : nullptr;
+    };
+
+    for (int p = P - 1; p >= 0; p--) {
+        SweepParams q{};
+        q.N = c->N; q.Npad = c->Npad;
+        q.G = pl.grid_size(p);
+        q.K = pl.K; q.F = F; q.max_dec = D;
+        q.ldb = c->ldb;
+        q.basis = c->basis.p;
+        q.partial = c->partial.p;
+        const bool is_current = (p == 0 && s0 == 1);
+        double* vout = c->keep_values ? c->Vall.p + (size_t)p * pl.max_grid * Np : c->V(cur ^ 1);
+        const double* vnext = c->keep_values ? c->Vall.p + (size_t)(p + 1) * pl.max_grid * Np : c->V(cur);
+        q.Vout = vout;
+        if (p == P - 1) {
+            q.mode = 1; q.Gn = 0;
+            q.grid = c->grid.p + pl.grid_offset[p];
+            q.must_be_empty = pb.must_be_empty_at_end;
+            q.tc0 = pb.terminal_coef[0]; q.tc1 = pb.terminal_coef[1]; q.tc2 = pb.terminal_coef[2]; q.tc3 = pb.terminal_coef[3];
+        } else {
+            q.mode = 0; q.Gn = pl.grid_size(p + 1);
+            q.Vnext = vnext;
+            q.cont_mode = is_current ? 1 : 0;
+            q.beta = c->beta_all.p + (size_t)p * c->beta_stride();
+            q.df = pb.settle_df[p];
+            const size_t row = pl.tables.row_offset[p];
+            q.t_ndec = c->t_ndec.p + row; q.t_invcost = c->t_invcost.p + row;
+            q.t_vol = c->t_vol.p + row * D; q.t_cost = c->t_cost.p + row * D; q.t_cons = c->t_cons.p + row * D;
+            q.t_wlo = c->t_wlo.p + row * D; q.t_whi = c->t_whi.p + row * D; q.t_lo = c->t_lo.p + row * D; q.t_hi = c->t_hi.p + row * D;
+        }
+        q.spot_is_const = is_current ? 1 : 0;
+        q.spot_const = pb.forward[p];
+        regressors(p, q.spot_p, q.fac_p);
+        // normal equations for the regression of period p-1 (ones-only when p-1 is the deterministic current period;
+        // at p == 0 the ones column yields the backward NPV, LSV.cs:589)
+        if (p == 0) q.accum_mode = 2;
+        else {
+            q.accum_mode = (p - 1 == 0 && s0 == 1) ? 2 : 1;
+            regressors(p - 1, q.spot_m, q.fac_m);
+        }
+        CUDA_CHECK(cudaEventRecord(c->event(ev_base), s));
+        CUDA_CHECK(launch_sweep(q, cfg, s));
+        CUDA_CHECK(cudaEventRecord(c->event(ev_base + 1), s));
+        ev_base += 2;
+        c->tm.backward_sweep_launches++;
+        c->tm.kernel_launches++;
+        c->tm.sweep_bytes += (double)c->N * 8.0 * ((double)q.G + q.Gn + (q.mode == 0 && !is_current ? F + 1 : (q.mode == 1 ? 1 : 0)) + (q.accum_mode == 1 ? F + 1 : 0));
+
+        const int n_elem = 8 * c->MT * q.ncols;
+        launch_reduce_partials(c->partial.p, c->sweep_blocks, n_elem, c->reduced.p, s);
+        c->tm.kernel_launches++;
+        c->allreduce(c->reduced.p, (size_t)n_elem);
+        if (p > 0) {
+            SolveParams sp{};
+            sp.reduced = c->reduced.p; sp.ncols = q.ncols; sp.K = pl.K; sp.G = q.G; sp.NT = (q.G + 7) / 8; sp.ldb = c->ldb;
+            sp.accum_mode = q.accum_mode; sp.n_global = c->Nglobal; sp.pivot_tol = 1e-13;
+            sp.beta = c->beta_all.p + (size_t)(p - 1) * c->beta_stride();
+            launch_solve(sp, s);
+            c->tm.kernel_launches++;
+            if (c->beta_override_set[p - 1])
+                CUDA_CHECK(cudaMemcpyAsync(sp.beta, c->beta_override.data() + (size_t)(p - 1) * c->beta_stride(),
+                                           c->beta_stride() * sizeof(double), cudaMemcpyHostToDevice, s));
+        } else {
+            double sum = 0.0;
+            CUDA_CHECK(cudaMemcpyAsync(&sum, c->reduced.p, sizeof(double), cudaMemcpyDeviceToHost, s));
+            CUDA_CHECK(cudaStreamSynchronize(s));
+            c->backward_npv = sum / (double)c->Nglobal;
+        }
+        CUDA_CHECK(cudaGetLastError());
+        cur ^= 1;
+        if (p < P - 1) {   // one progress tick per decision period (LSV.cs:337-339)
+            progress += back_step;
+            if (cb) {
+                CUDA_CHECK(cudaStreamSynchronize(s));
+                if (cb(user, progress) != 0) throw Error(LSMC_ECANCELLED, "The operation was canceled.");
+            }
+        }
+    }
+    CUDA_CHECK(cudaEventRecord(c->event(3), s));
+    CUDA_CHECK(cudaStreamSynchronize(s));
+    float ms = 0.f;
+    c->tm.backward_sweep_kernel_ms = 0.0;
+    for (size_t e = 8; e < ev_base; e += 2) { CUDA_CHECK(cudaEventElapsedTime(&ms, c->ev[e], c->ev[e + 1])); c->tm.backward_sweep_kernel_ms += ms; }
+    CUDA_CHECK(cudaEventElapsedTime(&ms, c->ev[2], c->ev[3])); c->tm.backward_ms = ms;
+    CUDA_CHECK(cudaEventElapsedTime(&ms, c->ev[0], c->ev[1])); c->tm.regression_sim_ms = ms;
+    c->backward_done = true;
+}
+
+// Forward simulation (LSV.cs:344-579).
+void forward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
+    require(c->backward_done && c->sims_ready[1], LSMC_EINVAL, "run lsmc_backward and simulate the valuation set before lsmc_forward");
+    Plan& pl = c->plan;
+    const lsmc_problem& pb = pl.problem.pb;
+    const int P = pl.P, s0 = pl.s0, F = pl.F, K = pl.K, nsum = kFwdSums + K;
+    const size_t Np = (size_t)c->Npad;
+    cudaStream_t s = c->stream;
+    CUDA_CHECK(cudaEventRecord(c->event(6), s));
+    launch_fill(c->inventory.p, c->Npad, pb.start_inventory, s);   // LSV.cs:362-364
+    CUDA_CHECK(cudaMemsetAsync(c->pv_by_sim.p, 0, Np * sizeof(double), s));
+    CUDA_CHECK(cudaMemsetAsync(c->error_flag.p, 0, sizeof(int), s));
+    const bool panels = (c->outputs & 1) != 0;
+    double progress = 0.66;
+    const double fwd_step = (1.0 - 0.66) / P;   // LSV.cs:371
+    for (int p = 0; p < P - 1; p++) {
+        ForwardParams q{};
+        q.N = c->N; q.Npad = c->Npad; q.p = p; q.Gn = pl.grid_size(p + 1); q.K = K; q.F = F; q.max_dec = pl.max_dec; q.extra = pb.extra_decisions;
+        const bool is_current = (p == 0 && s0 == 1);
+        q.cont_mode = is_current ? 1 : 0; q.spot_is_const = is_current ? 1 : 0; q.spot_const = pb.forward[p];
+        q.df = pb.settle_df[p]; q.tol = pb.numerical_tolerance;
+        q.loss_pct = pb.inventory_loss[p]; q.inv_cost = pb.inventory_cost[p]; q.inv_cost_df = pb.inventory_cost_df[p];
+        q.inj_cost = pb.inject_cost[p]; q.inj_df = pb.inject_cost_df[p]; q.wd_cost = pb.withdraw_cost[p]; q.wd_df = pb.withdraw_cost_df[p];
+        q.cons_inj = pb.consumed_inject[p]; q.cons_wd = pb.consumed_withdraw[p];
+        q.min_inv = pb.min_inventory[p]; q.max_inv = pb.max_inventory[p];
+        q.next_min = pl.space_min[p + 1]; q.next_max = pl.space_max[p + 1];
+        const int cid = pb.constraint_id[p], first = pb.constraint_first[cid];
+        q.c_kind = pb.constraint_kind[cid]; q.c_n = pb.constraint_count[cid];
+        q.c_x = c->c_x.p + first; q.c_lo = c->c_lo.p + first; q.c_hi = c->c_hi.p + first;
+        if (!is_current) { q.spot = c->spot[1].p + (size_t)(p - s0) * Np; q.fac = c->fac.p + (size_t)(p - s0) * F * Np; }
+        q.beta = c->beta_all.p + (size_t)p * c->beta_stride(); q.ldb = c->ldb;
+        q.next_grid = c->grid.p + pl.grid_offset[p + 1];
+        q.basis = c->basis.p;
+        q.inventory = c->inventory.p; q.pv_by_sim = c->pv_by_sim.p;
+        q.sums = c->fwd_sums.p + (size_t)p * c->fwd_blocks * nsum;
+        q.error_flag = c->error_flag.p;
+        if (panels) {
+            q.o_inventory = c->panels[0].p + (size_t)p * Np; q.o_volume = c->panels[1].p + (size_t)p * Np; q.o_consumed = c->panels[2].p + (size_t)p * Np;
+            q.o_loss = c->panels[3].p + (size_t)p * Np; q.o_net = c->panels[4].p + (size_t)p * Np; q.o_pv = c->panels[5].p + (size_t)p * Np;
+        }
+        if (c->outputs & 2) q.o_decision = c->decisions.p + (size_t)p * Np;
+        launch_forward(q, c->fwd_blocks, s);
+        c->tm.kernel_launches++;
+        progress += fwd_step;
+        if (cb) {
+            CUDA_CHECK(cudaStreamSynchronize(s));
+            check_device_error_flag(c);
+            if (cb(user, progress) != 0) throw Error(LSMC_ECANCELLED, "The operation was canceled.");
+        }
+    }
+    launch_reduce_rows(c->fwd_sums.p, P - 1, c->fwd_blocks, nsum, c->fwd_red.p, s);
+    c->tm.kernel_launches++;
+    c->allreduce(c->fwd_red.p, (size_t)(P - 1) * nsum);
+    // final period + NPV
+    FinalParams fq{};
+    fq.N = c->N; fq.pass = 0; fq.must_be_empty = pb.must_be_empty_at_end;
+    fq.tc0 = pb.terminal_coef[0]; fq.tc1 = pb.terminal_coef[1]; fq.tc2 = pb.terminal_coef[2]; fq.tc3 = pb.terminal_coef[3];
+    fq.spot_end = c->spot[0].p + (size_t)(pl.S - 1) * Np;   // regression sims' end prices (LSV.cs:567)
+    fq.inventory = c->inventory.p; fq.pv_by_sim = c->pv_by_sim.p; fq.sums = c->fin_sums.p;
+    if (panels) {
+        fq.o_inventory = c->panels[0].p + (size_t)(P - 1) * Np; fq.o_pv = c->panels[5].p + (size_t)(P - 1) * Np;
+        for (int k = 1; k <= 4; k++) CUDA_CHECK(cudaMemsetAsync(c->panels[k].p + (size_t)(P - 1) * Np, 0, Np * sizeof(double), s));
+    }
+    launch_final(fq, c->fwd_blocks, s);
+    launch_reduce_rows(c->fin_sums.p, 1, c->fwd_blocks, 3, c->reduced.p, s);
+    c->tm.kernel_launches += 2;
+    c->allreduce(c->reduced.p, 3);
+    double fin[3];
+    CUDA_CHECK(cudaMemcpyAsync(fin, c->reduced.p, sizeof(fin), cudaMemcpyDeviceToHost, s));
+    c->h_fwd.resize((size_t)(P - 1) * nsum);
+    CUDA_CHECK(cudaMemcpyAsync(c->h_fwd.data(), c->fwd_red.p, c->h_fwd.size() * sizeof(double), cudaMemcpyDeviceToHost, s));
+    CUDA_CHECK(cudaStreamSynchronize(s));
+    check_device_error_flag(c);
+    c->final_inventory_sum = fin[0]; c->terminal_pv_sum = fin[1];
+    c->npv = fin[2] / (double)c->Nglobal;   // LSV.cs:584
+    // standard error of the NPV (pair means when the valuation draws are antithetic)
+    const bool paired = c->valuation_antithetic && (c->N % 2 == 0) && (pb.sim_offset % 2 == 0);
+    fq.pass = 1; fq.paired = paired ? 1 : 0; fq.mean = c->npv;
+    launch_final(fq, c->fwd_blocks, s);
+    launch_reduce_rows(c->fin_sums.p, 1, c->fwd_blocks, 3, c->reduced.p, s);
+    c->tm.kernel_launches += 2;
+    c->allreduce(c->reduced.p, 3);
+    double ss[3];
+    CUDA_CHECK(cudaMemcpyAsync(ss, c->reduced.p, sizeof(ss), cudaMemcpyDeviceToHost, s));
+    CUDA_CHECK(cudaEventRecord(c->event(7), s));
+    CUDA_CHECK(cudaStreamSynchronize(s));
+    const double m = (double)(paired ? c->Nglobal / 2 : c->Nglobal);
+    c->npv_se = m > 1 ? std::sqrt(ss[0] / (m - 1) / m) : 0.0;
+    float ms = 0.f;
+    CUDA_CHECK(cudaEventElapsedTime(&ms, c->ev[4], c->ev[5])); c->tm.valuation_sim_ms = ms;
+    CUDA_CHECK(cudaEventElapsedTime(&ms, c->ev[6], c->ev[7])); c->tm.forward_ms = ms;
+    c->tm.total_ms = c->tm.regression_sim_ms + c->tm.backward_ms + c->tm.valuation_sim_ms + c->tm.forward_ms;
+    c->forward_done = true;
+    if (cb) cb(user, 1.0);   // LSV.cs:604
+}
+
+// Expected profile, deltas (LSV.cs:482-487,593-597) and trigger prices (LSV.cs:492-561) from the per-period sums.
+void assemble_summary(lsmc_ctx* c, lsmc_results* r) {
+    Plan& pl = c->plan;
+    const lsmc_problem& pb = pl.problem.pb;
+    const int P = pl.P, K = pl.K, nsum = kFwdSums + K, s0 = pl.s0;
+    const double Ng = (double)c->Nglobal;
+    const double NaN = std::numeric_limits<double>::quiet_NaN();
+    r->npv = c->npv; r->npv_std_error = c->npv_se; r->backward_npv = c->backward_npv;
+    if (r->deltas) {
+        for (int p = 0; p < P - 1; p++) {
+            const double* sm = &c->h_fwd[(size_t)p * nsum];
+            const double disc = pb.discount_deltas ? pb.settle_df[p] : 1.0;
+            r->deltas[p] = (sm[6] / pb.forward[p] / Ng) * disc;
+        }
+        r->deltas[P - 1] = 0.0;
+    }
+    if (r->profile) {
+        for (int p = 0; p < P - 1; p++)
+            for (int k = 0; k < 6; k++) r->profile[(size_t)p * 6 + k] = c->h_fwd[(size_t)p * nsum + k] / Ng;
+        double* last = r->profile + (size_t)(P - 1) * 6;
+        last[0] = c->final_inventory_sum / Ng; last[1] = last[2] = last[3] = last[4] = 0.0;
+        last[5] = pb.must_be_empty_at_end ? 0.0 : c->terminal_pv_sum / Ng;
+    }
+    const bool want_trig = r->trigger_summary || r->trigger_inject || r->trigger_withdraw;
+    if (!want_trig) return;
+    const int nv = LSMC_NUM_TRIGGER_VOLUMES;
+    if (r->trigger_summary) std::fill(r->trigger_summary, r->trigger_summary + (size_t)(P - 1) * 4, NaN);
+    if (r->trigger_inject) std::fill(r->trigger_inject, r->trigger_inject + (size_t)(P - 1) * nv * 2, NaN);
+    if (r->trigger_withdraw) std::fill(r->trigger_withdraw, r->trigger_withdraw + (size_t)(P - 1) * nv * 2, NaN);
+    std::vector<double> beta(c->beta_all.n);
+    CUDA_CHECK(cudaMemcpy(beta.data(), c->beta_all.p, beta.size() * sizeof(double), cudaMemcpyDeviceToHost));
+    std::vector<double> ds(pl.max_dec), xbar(K);
+    for (int p = 0; p < P - 1; p++) {
+        const double* sm = &c->h_fwd[(size_t)p * nsum];
+        const bool is_current = (p == 0 && s0 == 1);
+        const double inv = sm[0] / Ng;   // expected inventory
+        for (int k = 0; k < K; k++) xbar[k] = sm[kFwdSums + k] / Ng;
+        const double* bp = beta.data() + (size_t)p * c->beta_stride();
+        const double* next = pl.grid_of(p + 1);
+        const int Gn = pl.grid_size(p + 1);
+        // mean over sims of the fitted continuation value at grid row l = xbar . beta_l
+        auto mean_fit = [&](int l) {
+            if (is_current) return bp[(size_t)l * c->ldb];
+            double acc = 0.0;
+            for (int k = 0; k < K; k++) acc += xbar[k] * bp[(size_t)l * c->ldb + k];
+            return acc;
+        };
+        auto avg_cont = [&](double after) {   // AverageContinuationValue (LSV.cs:700-720)
+            int lo, hi;
+            bisect_grid(next, Gn, after, pb.numerical_tolerance, lo, hi);
+            if (lo == hi) return mean_fit(lo);
+            const double wl = (next[hi] - after) / (next[hi] - next[lo]);
+            return mean_fit(lo) * wl + mean_fit(hi) * (1.0 - wl);
+        };
+        const double loss = pb.inventory_loss[p] * inv;
+        double rmin, rmax;
+        inject_withdraw_range(pb, p, inv, rmin, rmax);
+        const int nd = bang_bang_decisions(rmin, rmax, inv, loss, pl.space_min[p + 1], pl.space_max[p + 1], pb.numerical_tolerance, pb.extra_decisions, ds.data());
+        const double df = pb.settle_df[p];
+        auto price_of = [&](double vol, double alt_cont, double alt_vol, double alt_cost, double alt_cons) {   // CalcTriggerPrice (LSV.cs:619-638)
+            const double cont_change = avg_cont(inv + vol - loss) - alt_cont;
+            const double cost_change = decision_cost_npv(pb, p, vol) - alt_cost;
+            const double cons_change = decision_consumed(pb, p, vol) - alt_cons;
+            return (cont_change - cost_change) / (df * ((vol - alt_vol) + cons_change));
+        };
+        double max_inj = ds[0], max_wd = ds[0];
+        for (int d = 1; d < nd; d++) { max_inj = std::max(max_inj, ds[d]); max_wd = std::min(max_wd, ds[d]); }
+        if (max_inj > 0) {
+            double alt = std::numeric_limits<double>::infinity();
+            for (int d = 0; d < nd; d++) if (ds[d] >= 0 && ds[d] < alt) alt = ds[d];
+            if (max_inj > alt) {
+                const double alt_cont = avg_cont(inv + alt - loss), alt_cost = decision_cost_npv(pb, p, alt), alt_cons = decision_consumed(pb, p, alt);
+                const double inc = (max_inj - alt) / nv;
+                double last_price = NaN;
+                for (int i = 0; i < nv; i++) {
+                    const double vol = (i == nv - 1) ? max_inj : alt + (i + 1) * inc;   // LSV.cs:640-649
+                    last_price = price_of(vol, alt_cont, alt, alt_cost, alt_cons);
+                    if (r->trigger_inject) { r->trigger_inject[((size_t)p * nv + i) * 2] = vol; r->trigger_inject[((size_t)p * nv + i) * 2 + 1] = last_price; }
+                }
+                if (r->trigger_summary) { r->trigger_summary[(size_t)p * 4] = max_inj; r->trigger_summary[(size_t)p * 4 + 1] = last_price; }
+            }
+        }
+        if (max_wd < 0) {
+            double alt = -std::numeric_limits<double>::infinity();
+            for (int d = 0; d < nd; d++) if (ds[d] <= 0 && ds[d] > alt) alt = ds[d];
+            if (max_wd < alt) {
+                const double alt_cont = avg_cont(inv + alt - loss), alt_cost = decision_cost_npv(pb, p, alt), alt_cons = decision_consumed(pb, p, alt);
+                const double inc = (alt - max_wd) / nv;
+                for (int out = 0; out < nv; out++) {   // volumes max_wd + i*inc, listed in reverse (LSV.cs:545,651-659)
+                    const int i = nv - 1 - out;
+                    const double vol = max_wd + i * inc;
+                    const double price = price_of(vol, alt_cont, alt, alt_cost, alt_cons);
+                    if (r->trigger_withdraw) { r->trigger_withdraw[((size_t)p * nv + out) * 2] = vol; r->trigger_withdraw[((size_t)p * nv + out) * 2 + 1] = price; }
+                    if (out == 0 && r->trigger_summary) { r->trigger_summary[(size_t)p * 4 + 2] = max_wd; r->trigger_summary[(size_t)p * 4 + 3] = price; }
+                }
+            }
+        }
+    }
+}
+
+void copy_panel(lsmc_ctx* c, double* dst, const double* src, size_t rows) {
+    if (!dst) return;
+    CUDA_CHECK(cudaMemcpy2D(dst, (size_t)c->N * sizeof(double), src, (size_t)c->Npad * sizeof(double), (size_t)c->N * sizeof(double), rows, cudaMemcpyDeviceToHost));
+}
+
+void get_results(lsmc_ctx* c, lsmc_results* r) {
+    require(r != nullptr, LSMC_EINVAL, "results is null");
+    require(r->struct_size == (int32_t)sizeof(lsmc_results), LSMC_EINVAL, "lsmc_results.struct_size mismatch");
+    require(c->forward_done, LSMC_EINVAL, "lsmc_forward has not completed");
+    Plan& pl = c->plan;
+    assemble_summary(c, r);
+    copy_panel(c, r->pv_by_sim, c->pv_by_sim.p, 1);
+    copy_panel(c, r->spot_regress, c->spot[0].p, pl.S);
+    copy_panel(c, r->spot_valuation, c->spot[1].p, pl.S);
+    double* outs[6] = {r->inventory, r->inject_withdraw, r->consumed, r->loss, r->net_volume, r->pv};
+    for (int k = 0; k < 6; k++) {
+        if (!outs[k]) continue;
+        require((c->outputs & 1) != 0, LSMC_EINVAL, "per-sim panels were not requested before lsmc_forward (lsmc_request_outputs)");
+        copy_panel(c, outs[k], c->panels[k].p, pl.P);
+    }
+    if (r->decision_index) {
+        require((c->outputs & 2) != 0, LSMC_EINVAL, "decision_index was not requested before lsmc_forward (lsmc_request_outputs)");
+        CUDA_CHECK(cudaMemcpy2D(r->decision_index, (size_t)c->N, c->decisions.p, (size_t)c->Npad, (size_t)c->N, pl.P - 1, cudaMemcpyDeviceToHost));
+    }
+}
+
+}  // namespace
+
+// ================================================================================================================
+extern "C" {
+
+const char* lsmc_version(void) { return "lsmc_b200 0.1.0 (sm_100a)"; }
+
+int lsmc_create(int device, lsmc_ctx** out) {
+    if (!out) { g_create_error = "out is null"; return LSMC_EINVAL; }
+    *out = nullptr;
+    lsmc_ctx* c = nullptr;
+    int rc = guarded(nullptr, [&] {
+        int count = 0;
+        CUDA_CHECK(cudaGetDeviceCount(&count));
+        require(device >= 0 && device < count, LSMC_ECUDA, "no such CUDA device");
+        CUDA_CHECK(cudaSetDevice(device));
+        cudaDeviceProp prop;
+        CUDA_CHECK(cudaGetDeviceProperties(&prop, device));
+        require(prop.major >= 10, LSMC_ECUDA, "this library is built for sm_100a (B200) only");
+        c = new lsmc_ctx();
+        c->device = device;
+        c->num_sms = prop.multiProcessorCount;
+        CUDA_CHECK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    });
+    if (rc != LSMC_OK) { delete c; return rc; }
+    *out = c;
+    return LSMC_OK;
+}
+
+void lsmc_destroy(lsmc_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    delete ctx;
+}
+
+const char* lsmc_last_error(const lsmc_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int lsmc_comm_unique_id(void* out128) {
+    return guarded(nullptr, [&] {
+        std::string err;
+        require(out128 != nullptr, LSMC_EINVAL, "out128 is null");
+        if (!g_nccl.load(err)) throw Error(LSMC_ECUDA, err);
+        int rc = g_nccl.GetUniqueId(out128);
+        if (rc != 0) throw Error(LSMC_ECUDA, "ncclGetUniqueId failed");
+    });
+}
+
+int lsmc_comm_init(lsmc_ctx* ctx, int rank, int world, const void* unique_id128) {
+    if (!ctx) return LSMC_EINVAL;
+    return guarded(ctx, [&] {
+        require(world >= 1 && rank >= 0 && rank < world, LSMC_EINVAL, "bad rank/world");
+        ctx->rank = rank; ctx->world = world;
+        if (world == 1) return;
+        require(unique_id128 != nullptr, LSMC_EINVAL, "unique id is null");
+        std::string err;
+        if (!g_nccl.load(err)) throw Error(LSMC_ECUDA, err);
+        NcclId id;
+        std::memcpy(id.bytes, unique_id128, 128);
+        typedef int (*init_fn)(void**, int, NcclId, int);
+        int rc = ((init_fn)g_nccl.CommInitRank)(&ctx->comm, world, id, rank);
+        if (rc != 0) throw Error(LSMC_ECUDA, std::string("ncclCommInitRank: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "error"));
+    });
+}
+
+int lsmc_request_outputs(lsmc_ctx* ctx, uint32_t mask) {
+    if (!ctx) return LSMC_EINVAL;
+    ctx->outputs = mask;
+    return LSMC_OK;
+}
+
+int lsmc_set_problem(lsmc_ctx* ctx, const lsmc_problem* problem) {
+    if (!ctx) return LSMC_EINVAL;
+    return guarded(ctx, [&] { set_problem(ctx, problem); });
+}
+
+int lsmc_get_layout(const lsmc_ctx* ctx, lsmc_layout* out) {
+    if (!ctx || !out || !ctx->has_problem) return LSMC_EINVAL;
+    out->n_periods = ctx->plan.P; out->n_sim_periods = ctx->plan.S; out->max_grid = ctx->plan.max_grid;
+    out->max_decisions = ctx->plan.max_dec; out->n_sims = ctx->N;
+    return LSMC_OK;
+}
+
+int lsmc_simulate(lsmc_ctx* ctx, int set, const lsmc_rng* rng) {
+    if (!ctx) return LSMC_EINVAL;
+    return guarded(ctx, [&] { simulate(ctx, set, rng); });
+}
+
+int lsmc_backward(lsmc_ctx* ctx, lsmc_progress_cb progress, void* user) {
+    if (!ctx) return LSMC_EINVAL;
+    return guarded(ctx, [&] { backward(ctx, progress, user); });
+}
+
+int lsmc_forward(lsmc_ctx* ctx, lsmc_progress_cb progress, void* user) {
+    if (!ctx) return LSMC_EINVAL;
+    return guarded(ctx, [&] { forward(ctx, progress, user); });
+}
+
+int lsmc_get_results(lsmc_ctx* ctx, lsmc_results* results) {
+    if (!ctx) return LSMC_EINVAL;
+    return guarded(ctx, [&] { get_results(ctx, results); });
+}
+
+int lsmc_calculate(lsmc_ctx* ctx, const lsmc_problem* problem, const lsmc_rng* regression_rng, const lsmc_rng* valuation_rng,
+                   lsmc_progress_cb progress, void* user, lsmc_results* results) {
+    if (!ctx) return LSMC_EINVAL;
+    return guarded(ctx, [&] {
+        require(results != nullptr, LSMC_EINVAL, "results is null");
+        uint32_t mask = 0;
+        if (results->inventory || results->inject_withdraw || results->consumed || results->loss || results->net_volume || results->pv) mask |= 1;
+        if (results->decision_index) mask |= 2;
+        ctx->outputs = mask;
+        set_problem(ctx, problem);
+        simulate(ctx, 0, regression_rng);
+        backward(ctx, progress, user);
+        simulate(ctx, 1, valuation_rng);
+        forward(ctx, progress, user);
+        get_results(ctx, results);
+    });
+}
+
+int lsmc_get_timings(const lsmc_ctx* ctx, lsmc_timings* out) {
+    if (!ctx || !out) return LSMC_EINVAL;
+    *out = ctx->tm;
+    return LSMC_OK;
+}
+
+int lsmc_get_grid(const lsmc_ctx* ctx, int period, double* out, int32_t* count) {
+    if (!ctx || !ctx->has_problem || period < 0 || period >= ctx->plan.P || !count) return LSMC_EINVAL;
+    const int n = ctx->plan.grid_size(period);
+    *count = n;
+    if (out) std::memcpy(out, ctx->plan.grid_of(period), sizeof(double) * n);
+    return LSMC_OK;
+}
+
+int lsmc_get_inventory_space(const lsmc_ctx* ctx, double* min_out, double* max_out) {
+    if (!ctx || !ctx->has_problem || !min_out || !max_out) return LSMC_EINVAL;
+    std::memcpy(min_out, ctx->plan.space_min.data(), sizeof(double) * ctx->plan.P);
+    std::memcpy(max_out, ctx->plan.space_max.data(), sizeof(double) * ctx->plan.P);
+    return LSMC_OK;
+}
+
+int lsmc_get_regression_coeffs(lsmc_ctx* ctx, int period, double* out) {
+    if (!ctx) return LSMC_EINVAL;
+    return guarded(ctx, [&] {
+        require(ctx->backward_done && period >= 0 && period < ctx->plan.P - 1 && out, LSMC_EINVAL, "bad period or backward not run");
+        const int Gn = ctx->plan.grid_size(period + 1), K = ctx->plan.K;
+        std::vector<double> tmp((size_t)Gn * ctx->ldb);
+        CUDA_CHECK(cudaMemcpy(tmp.data(), ctx->beta_all.p + (size_t)period * ctx->beta_stride(), tmp.size() * sizeof(double), cudaMemcpyDeviceToHost));
+        for (int i = 0; i < Gn; i++) for (int k = 0; k < K; k++) out[(size_t)i * K + k] = tmp[(size_t)i * ctx->ldb + k];
+    });
+}
+
+int lsmc_get_sim_panel(lsmc_ctx* ctx, int set, int factor, double* out) {
+    if (!ctx) return LSMC_EINVAL;
+    return guarded(ctx, [&] {
+        require(ctx->has_problem && (set == 0 || set == 1) && ctx->sims_ready[set] && out, LSMC_EINVAL, "simulation set not available");
+        const Plan& pl = ctx->plan;
+        require(factor >= -1 && factor < pl.F, LSMC_EINVAL, "bad factor index");
+        CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+        if (factor < 0) { copy_panel(ctx, out, ctx->spot[set].p, pl.S); return; }
+        require(set == 1 || !ctx->sims_ready[1], LSMC_EINVAL, "regression factors were overwritten by the valuation set");
+        for (int j = 0; j < pl.S; j++)
+            copy_panel(ctx, out + (size_t)j * ctx->N, ctx->fac.p + ((size_t)j * pl.F + factor) * ctx->Npad, 1);
+    });
+}
+
+int lsmc_debug_set_regression_coeffs(lsmc_ctx* ctx, int period, const double* coeffs) {
+    if (!ctx) return LSMC_EINVAL;
+    return guarded(ctx, [&] {
+        require(ctx->has_problem && period >= 0 && period < ctx->plan.P - 1 && coeffs, LSMC_EINVAL, "bad period");
+        if (ctx->beta_override.empty()) ctx->beta_override.assign((size_t)(ctx->plan.P - 1) * ctx->beta_stride(), 0.0);
+        const int Gn = ctx->plan.grid_size(period + 1), K = ctx->plan.K;
+        double* dst = ctx->beta_override.data() + (size_t)period * ctx->beta_stride();
+        std::fill(dst, dst + ctx->beta_stride(), 0.0);
+        for (int i = 0; i < Gn; i++) for (int k = 0; k < K; k++) dst[(size_t)i * ctx->ldb + k] = coeffs[(size_t)i * K + k];
+        ctx->beta_override_set[period] = 1;
+    });
+}
+
+int lsmc_debug_keep_values(lsmc_ctx* ctx, int keep) {
+    if (!ctx) return LSMC_EINVAL;
+    ctx->keep_values = keep != 0;
+    return LSMC_OK;
+}
+
+int lsmc_debug_get_values(lsmc_ctx* ctx, int period, double* out) {
+    if (!ctx) return LSMC_EINVAL;
+    return guarded(ctx, [&] {
+        require(ctx->backward_done && ctx->keep_values && ctx->Vall.p && period >= 0 && period < ctx->plan.P && out, LSMC_EINVAL, "values were not kept");
+        copy_panel(ctx, out, ctx->Vall.p + (size_t)period * ctx->plan.max_grid * ctx->Npad, ctx->plan.grid_size(period));
+    });
+}
+
+}  // extern "C"

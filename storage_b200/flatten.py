@@ -69,8 +69,8 @@ def flatten_problem(cmdty_storage: CmdtyStorage,
         return TrivialResult(cmdty_storage.terminal_storage_npv(spot, inventory), False)
 
     start_active = max(cmdty_storage.start, current)    # SH.cs:45
-    P = (cmdty_storage.end - start_active).n + 1
-    periods = pd.period_range(start=start_active, periods=P, freq=start_active.freq)
+    periods = pd.period_range(start=start_active, end=cmdty_storage.end, freq=start_active.freq)
+    P = len(periods)
     first_is_current = int(start_active == current)
 
     # forward curve coverage (LSV.cs:91-95)
