@@ -1,0 +1,276 @@
+#!/usr/bin/env python
+"""bench.py — LSMC path-steps/sec on B200 (BASELINE.json metric), one JSON line on rank 0.
+
+A "step" is one complete valuation pass of the hot path over the workload: regression-set simulation, backward
+induction (fused sweep + normal equations + solve per period), valuation-set simulation, forward simulation and
+the reductions to NPV / deltas / trigger-price inputs.  path-steps = paths x decision periods.
+
+  value     device-resident throughput: problem tables already on the GPU, device RNG, summary left on device
+  e2e       the same pass through the one-call C ABI (`lsmc_calculate`) with HOST buffers: problem tables H2D and the
+            results (NPV, deltas, profile, trigger prices, PV by sim) D2H inside the timed region
+  roofline  the dominant kernel (fused backward sweep): algorithmic HBM bytes / CUDA-event time vs measured copy peak
+  cpu_baseline  the CPU oracle (port of the reference algorithm) on a bounded sample of the same workload
+
+`--impl reference` times the reference's CPU algorithm (the oracle port: the C# reference cannot be built in this
+image — no dotnet, NuGet dependencies absent) on all host threads on a bounded sample of the same config.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+CONFIG_TEXT = {
+    "c1": "README CmdtyStorage simple, three_factor_seasonal_value, daily 1y",
+    "c2": "one-factor multi_factor_value, constant-rate storage, daily 1y",
+    "c3": "three-factor seasonal, inventory ratchets + losses, daily 1y",
+    "c4": "five-factor multi_factor_value, degree-3 polynomial basis (K=56), 2y daily",
+    "c5": "battery-style storage, 2-factor, half-hourly 1 month",
+}
+DEFAULT_PATHS = {"c1": 1000, "c2": 100_000, "c3": 1_000_000, "c4": 500_000, "c5": 2_000_000}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--config", default="c3", choices=sorted(CONFIG_TEXT))
+    ap.add_argument("--paths-per-gpu", type=int, default=0, help="paths owned by each GPU (weak scaling); default = the config's path count")
+    ap.add_argument("--cpu-paths", type=int, default=0, help="paths of the bounded CPU sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    QUERY = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.stop_flag = index, [], threading.Event()
+
+    def run(self):
+        while not self.stop_flag.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.QUERY, "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.samples.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            self.stop_flag.wait(0.2)
+
+    def summary(self):
+        self.stop_flag.set()
+        self.join(timeout=6)
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        sm = sorted(float(s[0]) for s in self.samples if s[0].replace(".", "").isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(s) > 2 + i and s[2 + i].lower().startswith("active") for s in self.samples)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": float(self.samples[0][1]), "reasons": reasons,
+                "samples": len(self.samples)}
+
+
+def measured_peak_gbs():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def problem_h2d_bytes(pb):
+    total = 0
+    for name in pb._F64 + pb._I32:
+        total += getattr(pb, name).nbytes
+    return int(total)
+
+
+def results_d2h_bytes(res):
+    total = 24
+    for name in ("deltas", "profile", "trigger_summary", "trigger_inject", "trigger_withdraw", "pv_by_sim"):
+        a = getattr(res, name)
+        if a is not None:
+            total += a.nbytes
+    return int(total)
+
+
+def cpu_sample(config, cpu_paths, kind_note=""):
+    """The oracle on a bounded sample of the workload with all host threads; returns the cpu_baseline object."""
+    from oracle import oracle
+    from storage_b200._abi import Rng
+    from storage_b200.configs import build_config
+    pb = build_config(config, num_sims=cpu_paths)
+    t0 = time.perf_counter()
+    out = oracle.calculate(pb, Rng.philox(11), Rng.philox(22), decision_index=False, triggers=True)
+    dt = time.perf_counter() - t0
+    T = pb.n_periods - 1
+    return {"value": cpu_paths * T / dt, "unit": "path-steps/s", "cores": oracle.num_threads(), "kind": "port",
+            "sample": "%s at %d paths x %d periods, one full valuation in %.2f s on %d OpenMP threads%s" % (
+                config, cpu_paths, T, dt, oracle.num_threads(), kind_note),
+            "npv": out.results.npv}, dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cpu_paths = args.cpu_paths or {"c1": 1000, "c2": 20000, "c3": 8192, "c4": 2048, "c5": 4096}[args.config]
+    from storage_b200.configs import build_config
+    for _ in range(min(args.warmup, 1)):
+        cpu_sample(args.config, max(256, cpu_paths // 8))
+    times, base = [], None
+    for _ in range(args.steps):
+        base, dt = cpu_sample(args.config, cpu_paths)
+        times.append(dt)
+    pb = build_config(args.config, num_sims=cpu_paths)
+    T = pb.n_periods - 1
+    ms = 1e3 * sum(times) / len(times)
+    value = cpu_paths * T / (ms / 1e3)
+    base["value"] = value
+    line = {"impl": "reference", "metric": "lsmc_path_steps_per_sec", "value": value, "unit": "path-steps/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": CONFIG_TEXT[args.config], "config": args.config, "paths_sample": cpu_paths, "periods": T,
+                       "note": "reference C# cannot be built here (no dotnet/NuGet); this is the CPU oracle port of its algorithm, OpenMP on all host threads, bounded sample"},
+            "cpu_baseline": base,
+            "e2e": {"value": value, "unit": "path-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch   # plumbing only: process group, device selection, barriers
+    import torch.distributed as dist
+    from storage_b200 import _native, _abi
+    from storage_b200._abi import Rng
+    from storage_b200.configs import build_config
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a B200: the LSMC path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    n_local = args.paths_per_gpu or DEFAULT_PATHS[args.config]
+    n_global = n_local * world
+    pb = build_config(args.config, num_sims=n_local)
+    pb.n_sims_global = n_global
+    pb.sim_offset = rank * n_local
+    T = pb.n_periods - 1
+
+    ctx = _native.Context(local_rank)
+    if world > 1:
+        uid = [_native.Context.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        ctx.comm_init(rank, world, uid[0])
+    reg, val = Rng.philox(11), Rng.philox(22)
+
+    def device_step():
+        ctx.simulate(0, reg)
+        ctx.backward()
+        ctx.simulate(1, val)
+        ctx.forward()
+
+    # ---- device-resident throughput ----
+    ctx.set_problem(pb)
+    for _ in range(args.warmup):
+        device_step()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    t0 = time.perf_counter()
+    sweep_ms = sweep_launches = launches = sweep_bytes = dev_ms = 0.0
+    for _ in range(args.steps):
+        launches0 = ctx.timings()["kernel_launches"]
+        device_step()
+        tm = ctx.timings()
+        sweep_ms += tm["backward_sweep_kernel_ms"]; sweep_launches += tm["backward_sweep_launches"]
+        sweep_bytes += tm["sweep_bytes"]; dev_ms += tm["total_ms"]; launches += tm["kernel_launches"] - launches0
+    barrier()
+    elapsed = time.perf_counter() - t0
+    clocks = sampler.summary()
+    res_dev = ctx.get_results(_abi.Results(pb.n_periods, pb.n_sim_periods, n_local, pv_by_sim=False))
+    phase = ctx.timings()
+
+    # ---- end to end through the one-call C ABI with host buffers ----
+    e2e_res = _abi.Results(pb.n_periods, pb.n_sim_periods, n_local, pv_by_sim=True)
+    for _ in range(min(args.warmup, 2)):
+        ctx.calculate(pb, reg, val, results=e2e_res)
+    barrier()
+    t1 = time.perf_counter()
+    for _ in range(args.steps):
+        ctx.calculate(pb, reg, val, results=e2e_res)
+    barrier()
+    e2e_elapsed = time.perf_counter() - t1
+
+    times = torch.tensor([elapsed, e2e_elapsed], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(times, op=dist.ReduceOp.MAX)
+    elapsed, e2e_elapsed = float(times[0]), float(times[1])
+
+    if rank == 0:
+        ms_per_step = 1e3 * elapsed / args.steps
+        value = n_global * T / (ms_per_step / 1e3)
+        peak, peak_src = measured_peak_gbs()
+        achieved = (sweep_bytes / 1e9) / (sweep_ms / 1e3) if sweep_ms > 0 else 0.0
+        line = {
+            "metric": "lsmc_path_steps_per_sec", "value": value, "unit": "path-steps/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": CONFIG_TEXT[args.config], "config": args.config, "paths_per_gpu": n_local, "paths_total": n_global,
+                       "periods": T, "factors": pb.n_factors, "basis_functions": pb.n_basis, "inventory_grid_points": 100,
+                       "rng": "device Philox4x32-10, antithetic", "timing": "wall clock between device synchronisations + barrier, max over ranks",
+                       "l2": "inputs larger than L2 (sim panels %.1f GB, value surfaces %.1f GB per GPU)" % (
+                           8e-9 * n_local * pb.n_sim_periods * (pb.n_factors + 2), 16e-9 * n_local * 101)},
+            "npv": res_dev.npv, "npv_std_error": res_dev.npv_std_error,
+            "device_ms_per_step": dev_ms / args.steps,
+            "phase_ms": {k: phase[k] for k in ("regression_sim_ms", "backward_ms", "valuation_sim_ms", "forward_ms")},
+            "e2e": {"value": n_global * T / (e2e_elapsed / args.steps), "unit": "path-steps/s",
+                    "h2d_bytes_per_step": problem_h2d_bytes(pb), "d2h_bytes_per_step": results_d2h_bytes(e2e_res),
+                    "ms_per_step": 1e3 * e2e_elapsed / args.steps, "api": "lsmc_calculate (include/lsmc_b200.h) with host buffers"},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": {"kernel": "sweep_kernel (fused decision sweep + DMMA normal equations)", "bound": "hbm", "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "launches": int(sweep_launches), "avg_launch_ms": sweep_ms / max(1.0, sweep_launches),
+                         "share_of_step": sweep_ms / max(1e-9, dev_ms)},
+        }
+        if not args.no_cpu_baseline:
+            cpu_paths = args.cpu_paths or {"c1": 1000, "c2": 20000, "c3": 8192, "c4": 2048, "c5": 4096}[args.config]
+            try:
+                base, _ = cpu_sample(args.config, cpu_paths)
+                line["cpu_baseline"] = base
+            except Exception as e:   # the oracle is a checker; its absence must not hide the GPU number
+                line["cpu_baseline"] = {"value": None, "unit": "path-steps/s", "cores": 0, "kind": "port", "sample": "failed: %s" % e}
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

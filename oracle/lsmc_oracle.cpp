@@ -168,10 +168,12 @@ void constraint_range(const Constraint& c, double inventory, double& rmin, doubl
             rmin = linear_spline(c.inv, c.rmin, c.n, inventory);
             return;
         case LSMC_CONSTRAINT_STEP: {
-            if (inventory < c.inv[0] || inventory > c.inv[c.n - 1])
+            const double slack = 64.0 * 2.220446049250313e-16 * std::max(1.0, std::fabs(c.inv[c.n - 1]));
+            if (inventory < c.inv[0] - slack || inventory > c.inv[c.n - 1] + slack)
                 throw OracleError(LSMC_EINVAL, "Value of inventory is outside of the step ratchet interval.");
             int s = array_binary_search(c.inv, c.n, inventory);
             int idx = s >= 0 ? s : ~s - 1;
+            idx = std::min(std::max(idx, 0), c.n - 1);
             rmin = c.rmin[idx]; rmax = c.rmax[idx];
             return;
         }
@@ -180,12 +182,19 @@ void constraint_range(const Constraint& c, double inventory, double& rmin, doubl
     }
 }
 
+inline double range_slack(const lsmc_problem& pb, double bound) {
+    return std::max(pb.numerical_tolerance, 64.0 * 2.220446049250313e-16 * std::max(1.0, std::fabs(bound)));
+}
+
 // CmdtyStorage<T>.GetInjectWithdrawRange (CmdtyStorage.cs:86-100).
 void storage_range(const lsmc_problem& pb, int p, double inventory, double& rmin, double& rmax) {
+    // DEVIATION (documented in DESIGN.md §6): the reference compares with no tolerance (CmdtyStorage.cs:88-94), so a
+    // path whose inventory lands a few ulps outside the bound after `inventory + volume - loss` makes it throw.
+    // Both the oracle and the CUDA path accept a breach of at most range_slack(); larger breaches still throw.
     double minInv = pb.min_inventory[p];
-    if (inventory < minInv) throw OracleError(LSMC_EINVAL, "Inventory is below minimum allowed value.");
+    if (inventory < minInv - range_slack(pb, minInv)) throw OracleError(LSMC_EINVAL, "Inventory is below minimum allowed value.");
     double maxInv = pb.max_inventory[p];
-    if (inventory > maxInv) throw OracleError(LSMC_EINVAL, "Inventory above maximum allowed value.");
+    if (inventory > maxInv + range_slack(pb, maxInv)) throw OracleError(LSMC_EINVAL, "Inventory above maximum allowed value.");
     if (p >= pb.n_periods - 1) { rmin = 0.0; rmax = 0.0; return; }
     constraint_range(get_constraint(pb, p), inventory, rmin, rmax);
 }

@@ -73,7 +73,17 @@ def check(cfg, N, seed=7):
         r.npv, orr.npv, abs(r.npv / orr.npv - 1), abs(r.backward_npv / orr.backward_npv - 1), r.npv_std_error, orr.npv_std_error))
     print("valuation spot bit-exact:", np.array_equal(r.spot_valuation, orr.spot_valuation))
     mism = int(np.sum(r.decision_index != orr.decision_index))
-    print("forward decision mismatches:", mism, "of", r.decision_index.size)
+    vol_scale = np.max(np.abs(orr.inject_withdraw))
+    material = int(np.sum(np.abs(r.inject_withdraw - orr.inject_withdraw) > 1e-9 * vol_scale))
+    print("forward decision index mismatches:", mism, "of", r.decision_index.size, "| material (volume differs):", material)
+    if mism:
+        pp, nn = np.nonzero(r.decision_index != orr.decision_index)
+        print("  mismatch periods histogram (first 10):", np.unique(pp, return_counts=True)[0][:10], np.unique(pp, return_counts=True)[1][:10])
+        for k in range(min(5, len(pp))):
+            p_, n_ = pp[k], nn[k]
+            print("   p=%d n=%d gpu idx %d vol %.6f inv %.6f | oracle idx %d vol %.6f inv %.6f" % (p_, n_, r.decision_index[p_, n_], r.inject_withdraw[p_, n_], r.inventory[p_, n_],
+                  orr.decision_index[p_, n_], orr.inject_withdraw[p_, n_], orr.inventory[p_, n_]))
+        print("  volume panel max abs diff", np.max(np.abs(r.inject_withdraw - orr.inject_withdraw)), "inventory panel max abs diff", np.max(np.abs(r.inventory - orr.inventory)))
     dscale = np.max(np.abs(orr.deltas))
     print("deltas max err / max|delta|: %.3e" % (np.max(np.abs(r.deltas - orr.deltas)) / dscale))
     print("profile max rel err: %.3e" % np.max(np.abs(r.profile - orr.profile) / np.maximum(1e-9, np.max(np.abs(orr.profile), axis=0))))

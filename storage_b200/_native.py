@@ -105,6 +105,7 @@ class Context:
                                    decision_index=decision_index)
         cp, cr, cv, cres = problem.c_struct(), regression_rng.c_struct(), valuation_rng.c_struct(), results.c_struct()
         cb = _make_cb(on_progress)
+        self._problem = problem
         self._check(lib().lsmc_calculate(self._h, C.byref(cp), C.byref(cr), C.byref(cv), cb, None, C.byref(cres)))
         return results.sync_scalars()
 

@@ -95,8 +95,9 @@ void rate_range(const Pillars& c, double v, double& rmin, double& rmax) {
         rmin = spline_eval(c.x, c.lo, c.n, v);
         return;
     }
-    if (v < c.x[0] || v > c.x[c.n - 1]) throw Error(LSMC_EINVAL, "Value of inventory is outside of the ratchet interval.");
-    int idx = last_pillar_at_or_below(c.x, c.n, v);
+    const double slack = range_slack(0.0, c.x[c.n - 1]);
+    if (v < c.x[0] - slack || v > c.x[c.n - 1] + slack) throw Error(LSMC_EINVAL, "Value of inventory is outside of the ratchet interval.");
+    int idx = std::min(std::max(last_pillar_at_or_below(c.x, c.n, v), 0), c.n - 1);
     rmin = c.lo[idx]; rmax = c.hi[idx];
 }
 
@@ -164,8 +165,11 @@ double lower_bound_of_space(const Pillars& c, double nextLo, double nextHi, doub
 }  // namespace
 
 void inject_withdraw_range(const lsmc_problem& pb, int period, double inventory, double& rmin, double& rmax) {
-    if (inventory < pb.min_inventory[period]) throw Error(LSMC_EINVAL, "Inventory is below minimum allowed value.");
-    if (inventory > pb.max_inventory[period]) throw Error(LSMC_EINVAL, "Inventory above maximum allowed value.");
+    // a breach of a few ulps (rounding of inventory + volume - loss) is accepted, see range_slack()
+    if (inventory < pb.min_inventory[period] - range_slack(pb.numerical_tolerance, pb.min_inventory[period]))
+        throw Error(LSMC_EINVAL, "Inventory is below minimum allowed value.");
+    if (inventory > pb.max_inventory[period] + range_slack(pb.numerical_tolerance, pb.max_inventory[period]))
+        throw Error(LSMC_EINVAL, "Inventory above maximum allowed value.");
     if (period >= pb.n_periods - 1) { rmin = 0.0; rmax = 0.0; return; }
     rate_range(pillars_of(pb, period), inventory, rmin, rmax);
 }

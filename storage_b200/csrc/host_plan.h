@@ -71,6 +71,14 @@ struct Plan {
     const double* grid_of(int p) const { return grid.data() + grid_offset[p]; }
 };
 
+// Tolerated breach of an inventory bound: the reference checks with none (CmdtyStorage.cs:88-94) and throws on
+// rounding noise of `inventory + volume - loss`; see DESIGN.md §6.
+inline double range_slack(double tol, double bound) {
+    double a = bound < 0 ? -bound : bound;
+    double ulps = 64.0 * 2.220446049250313e-16 * (a > 1.0 ? a : 1.0);
+    return tol > ulps ? tol : ulps;
+}
+
 void build_plan(const lsmc_problem& problem, Plan& plan);
 
 // Storage queries at arbitrary inventory, used by the trigger-price post-processing (LSV.cs:494-497).

@@ -82,7 +82,7 @@ void launch_simulate(const SimParams& sp, cudaStream_t stream) {
 // =================================================================================================
 template <int TP, int MT, int NTW>
 __global__ void __launch_bounds__(512, 1) sweep_kernel(SweepParams q) {
-    constexpr int LD = TP + 8;   // row stride in doubles: rows 8 banks apart -> conflict-free 8-row x 4-path reads
+    constexpr int LD = TP + 4;   // row stride in doubles: consecutive rows 8 banks apart -> a half-warp's 4 rows x 4 paths hit 32 distinct banks
     extern __shared__ double smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, W = blockDim.x >> 5;
     const int g = lane >> 2, t = lane & 3;
@@ -291,7 +291,7 @@ __global__ void __launch_bounds__(512, 1) sweep_kernel(SweepParams q) {
 }
 
 size_t sweep_smem_bytes(int TP, int Gn, int n_nodes, int ldb) {
-    const int LD = TP + 8, GnP = (Gn + 7) & ~7;
+    const int LD = TP + 4, GnP = (Gn + 7) & ~7;
     return sizeof(double) * ((size_t)2 * GnP * LD + (size_t)2 * n_nodes * LD + (size_t)GnP * ldb);
 }
 
@@ -515,12 +515,12 @@ __global__ void __launch_bounds__(256) forward_kernel(ForwardParams q) {
             for (int k = 0; k < K; k++) { xrow[k] = nodes[bd->node_of_basis[k]]; xsum[k] += xrow[k]; }
         }
         // CmdtyStorage.GetInjectWithdrawRange (CmdtyStorage.cs:86-100)
-        if (v < q.min_inv || v > q.max_inv) atomicExch(q.error_flag, 1);
+        if (v < q.min_inv - q.slack_lo || v > q.max_inv + q.slack_hi) atomicExch(q.error_flag, 1);
         double rmin, rmax;
         if (q.c_kind == LSMC_CONSTRAINT_CONSTANT) { rmin = __ldg(q.c_lo); rmax = __ldg(q.c_hi); }
         else if (q.c_kind == LSMC_CONSTRAINT_PIECEWISE_LINEAR) { rmax = spline_dev(q.c_x, q.c_hi, q.c_n, v); rmin = spline_dev(q.c_x, q.c_lo, q.c_n, v); }
         else {
-            if (v < __ldg(q.c_x) || v > __ldg(q.c_x + q.c_n - 1)) atomicExch(q.error_flag, 2);
+            if (v < __ldg(q.c_x) - q.slack_hi || v > __ldg(q.c_x + q.c_n - 1) + q.slack_hi) atomicExch(q.error_flag, 2);
             int idx = min(max(last_at_or_below(q.c_x, q.c_n, v), 0), q.c_n - 1);
             rmin = __ldg(q.c_lo + idx); rmax = __ldg(q.c_hi + idx);
         }

@@ -392,6 +392,7 @@ void forward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
         q.inj_cost = pb.inject_cost[p]; q.inj_df = pb.inject_cost_df[p]; q.wd_cost = pb.withdraw_cost[p]; q.wd_df = pb.withdraw_cost_df[p];
         q.cons_inj = pb.consumed_inject[p]; q.cons_wd = pb.consumed_withdraw[p];
         q.min_inv = pb.min_inventory[p]; q.max_inv = pb.max_inventory[p];
+        q.slack_lo = range_slack(pb.numerical_tolerance, q.min_inv); q.slack_hi = range_slack(pb.numerical_tolerance, q.max_inv);
         q.next_min = pl.space_min[p + 1]; q.next_max = pl.space_max[p + 1];
         const int cid = pb.constraint_id[p], first = pb.constraint_first[cid];
         q.c_kind = pb.constraint_kind[cid]; q.c_n = pb.constraint_count[cid];

@@ -135,7 +135,7 @@ struct ForwardParams {
     int cont_mode, spot_is_const;
     double spot_const, df, tol;
     double loss_pct, inv_cost, inv_cost_df, inj_cost, inj_df, wd_cost, wd_df, cons_inj, cons_wd;
-    double min_inv, max_inv, next_min, next_max;
+    double min_inv, max_inv, next_min, next_max, slack_lo, slack_hi;
     int c_kind, c_n; const double* c_x; const double* c_lo; const double* c_hi;
     const double* spot; const double* fac;   // valuation regressors of period p
     const double* beta; int ldb;
