@@ -1302,4 +1302,12 @@ int oracle_regress(const double* X /*col-major N x K*/, int64_t N, int K, const 
 
 double oracle_det_exp(double x) { return det_exp(x); }
 
+/* Philox4x32-10 block function (pinned by the Random123 known-answer vectors in tests/test_oracle_simulator.py). */
+void oracle_philox4x32_10(uint32_t ctr[4], uint32_t k0, uint32_t k1) { philox4x32_10(ctr, k0, k1); }
+
+/* The two standard normals the simulators draw for (seed, draw index, step, factor pair). */
+void oracle_philox_normal_pair(uint64_t seed, uint64_t draw, uint32_t step, uint32_t pair, double* z0, double* z1) {
+    philox_normal_pair(seed, draw, step, pair, *z0, *z1);
+}
+
 }  // extern "C"

@@ -196,3 +196,15 @@ def regress(X, y):
 
 def det_exp(x):
     return lib().oracle_det_exp(float(x))
+
+
+def philox4x32_10(ctr, key):
+    c = (C.c_uint32 * 4)(*[int(x) for x in ctr])
+    lib().oracle_philox4x32_10(c, C.c_uint32(int(key[0])), C.c_uint32(int(key[1])))
+    return [int(x) for x in c]
+
+
+def philox_normal_pair(seed, draw, step, pair):
+    z0, z1 = C.c_double(), C.c_double()
+    lib().oracle_philox_normal_pair(C.c_uint64(seed), C.c_uint64(draw), C.c_uint32(step), C.c_uint32(pair), C.byref(z0), C.byref(z1))
+    return z0.value, z1.value

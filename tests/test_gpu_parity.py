@@ -1,0 +1,223 @@
+"""Parity of the CUDA path (through the C ABI) with the CPU oracle.  Needs a B200: `pytest -m gpu`.
+
+Bars (BASELINE.json north_star):
+  * injected normals: simulated panels bit-exact; with the oracle's regression coefficients injected the whole value
+    surface and every forward decision index are bit-exact; end to end (own normal-equation regression vs the oracle's
+    Householder QR) NPV / deltas / profile / trigger prices within 1e-9 relative and no decision flips except between
+    decisions of numerically identical volume;
+  * device RNG: Philox stream identical to the oracle's, NPV within 3 standard errors.
+"""
+import numpy as np
+import pytest
+
+from storage_b200 import _abi, _native
+from storage_b200._abi import Rng
+from storage_b200.configs import build_config
+from oracle import oracle
+from fixtures import reference_problem, simple_daily_storage, ratchet_daily_storage, three_calls_problem
+
+pytestmark = pytest.mark.gpu
+REL = 1e-9   # north_star tolerance with injected normals
+
+
+def anti_normals(seed, S, F, N):
+    rs = np.random.default_rng(seed)
+    z = rs.standard_normal((S, F, (N + 1) // 2))
+    out = np.empty((S, F, N))
+    out[:, :, 0::2] = z[:, :, :(N + 1) // 2]
+    out[:, :, 1::2] = -z[:, :, :N // 2]
+    return out
+
+
+def rel_err(a, b, scale=None):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    assert np.array_equal(np.isnan(a), np.isnan(b))
+    m = ~np.isnan(b)
+    if not m.any():
+        return 0.0
+    s = scale if scale is not None else max(np.max(np.abs(b[m])), 1e-300)
+    return float(np.max(np.abs(a[m] - b[m])) / s)
+
+
+def material_flips(got, ref):
+    """Decision differences that change the decided volume by more than 1e-9 of the largest rate."""
+    scale = np.max(np.abs(ref.inject_withdraw))
+    return int(np.sum(np.abs(got.inject_withdraw - ref.inject_withdraw) > 1e-9 * max(scale, 1e-300)))
+
+
+CASES = {
+    "c1_readme_simple_3f": lambda: build_config("c1", num_sims=1000),
+    "c2_one_factor": lambda: build_config("c2", num_sims=1536),
+    "c3_ratchets_losses_3f": lambda: build_config("c3", num_sims=1024),
+    "c3_ragged_paths": lambda: build_config("c3", num_sims=333),
+    "c5_battery_half_hourly": lambda: build_config("c5", num_sims=512),
+    "reference_fixture_1f": lambda: reference_problem(num_sims=2000),
+    "reference_fixture_ratchets": lambda: reference_problem(storage=ratchet_daily_storage(), num_sims=768, numerical_tolerance=1e-9),
+    "terminal_value_not_empty": lambda: reference_problem(storage=simple_daily_storage(lambda p, i: p * i - 999.0), num_sims=512),
+    "before_storage_start": lambda: reference_problem(val_date="2019-07-20", inventory=0.0, num_sims=512),
+    "extra_decisions": lambda: reference_problem(num_sims=512, extra_decisions=2),
+    "three_calls": lambda: three_calls_problem(num_sims=1024)[0],
+}
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    with _native.Context(0) as c:
+        yield c
+
+
+@pytest.mark.parametrize("case", sorted(CASES))
+def test_staged_bit_exact_with_injected_normals_and_coefficients(case):
+    pb = CASES[case]()
+    S, F, P, K, N = pb.n_sim_periods, pb.n_factors, pb.n_periods, pb.n_basis, int(pb.n_sims)
+    zr, zv = anti_normals(1, S, F, N), anti_normals(2, S, F, N)
+    o = oracle.calculate(pb, Rng.from_normals(zr), Rng.from_normals(zv), keep_values=True, keep_factors=True,
+                         panels=("spot_regress", "spot_valuation", "inventory", "inject_withdraw", "pv"))
+    with _native.Context(0) as ctx:
+        ctx.request_outputs(panels=True, decision_index=True)
+        ctx.debug_keep_values(True)
+        ctx.set_problem(pb)
+        lo, hi = ctx.inventory_space()
+        assert np.array_equal(lo, o.inventory_space_min) and np.array_equal(hi, o.inventory_space_max)
+        for p in range(P):
+            assert np.array_equal(ctx.grid(p), o.grids[p, :o.grid_count[p]])
+        ctx.simulate(0, Rng.from_normals(zr))
+        assert np.array_equal(ctx.sim_panel(0), o.results.spot_regress)
+        for f in range(F):
+            assert np.array_equal(ctx.sim_panel(0, f), o.factors_regress[:, f, :])
+        for p in range(P - 1):
+            g = o.grid_count[p + 1]
+            if p == 0 and pb.first_period_is_current:
+                coeffs = np.zeros((g, K)); coeffs[:, 0] = o.current_continuation[:g]
+            else:
+                coeffs = o.regression_coeffs[p, :g, :]
+            ctx.debug_set_regression_coeffs(p, coeffs)
+        ctx.backward()
+        for p in range(P - 1, -1, -1):
+            assert np.array_equal(ctx.debug_values(p), o.values[p, :o.grid_count[p], :]), "value surface of period %d" % p
+        ctx.simulate(1, Rng.from_normals(zv))
+        ctx.forward()
+        r = ctx.get_results(panels=("inventory", "inject_withdraw", "pv", "spot_valuation"), decision_index=True)
+        assert np.array_equal(r.spot_valuation, o.results.spot_valuation)
+        assert np.array_equal(r.decision_index, o.results.decision_index)        # bit-exact decisions
+        assert np.array_equal(r.inject_withdraw, o.results.inject_withdraw)
+        assert np.array_equal(r.inventory, o.results.inventory)
+        assert np.array_equal(r.pv, o.results.pv)
+        assert rel_err(r.npv, o.results.npv) < 1e-13                              # only the summation order differs
+        assert rel_err(r.deltas, o.results.deltas) < 1e-12
+
+
+@pytest.mark.parametrize("case", sorted(CASES))
+def test_end_to_end_within_1e9_with_injected_normals(case, ctx):
+    pb = CASES[case]()
+    S, F, N = pb.n_sim_periods, pb.n_factors, int(pb.n_sims)
+    zr, zv = anti_normals(3, S, F, N), anti_normals(4, S, F, N)
+    ref = oracle.calculate(pb, Rng.from_normals(zr), Rng.from_normals(zv), panels=("inject_withdraw",)).results
+    got = ctx.calculate(pb, Rng.from_normals(zr), Rng.from_normals(zv), panels=("inject_withdraw",), decision_index=True)
+    assert rel_err(got.npv, ref.npv) < REL
+    assert rel_err(got.backward_npv, ref.backward_npv) < REL
+    assert rel_err(got.deltas, ref.deltas) < REL
+    assert rel_err(got.profile, ref.profile) < REL
+    assert material_flips(got, ref) == 0
+    price_scale = float(np.max(pb.forward))
+    assert rel_err(got.trigger_summary[:, [0, 2]], ref.trigger_summary[:, [0, 2]]) < REL      # volumes
+    assert rel_err(got.trigger_summary[:, [1, 3]], ref.trigger_summary[:, [1, 3]], price_scale) < 1e-7   # prices: a ratio of small differences
+    assert rel_err(got.trigger_inject[..., 0], ref.trigger_inject[..., 0]) < REL
+    assert rel_err(got.trigger_withdraw[..., 0], ref.trigger_withdraw[..., 0]) < REL
+    assert rel_err(got.pv_by_sim, ref.pv_by_sim, max(abs(ref.npv), 1.0)) < 1e-7
+
+
+@pytest.mark.parametrize("case", ["c2_one_factor", "c3_ratchets_losses_3f", "reference_fixture_1f"])
+def test_device_rng_matches_oracle_stream_and_npv_within_3_standard_errors(case, ctx):
+    pb = CASES[case]()
+    ref = oracle.calculate(pb, Rng.philox(11), Rng.philox(22), panels=("spot_regress", "spot_valuation")).results
+    got = ctx.calculate(pb, Rng.philox(11), Rng.philox(22), panels=("spot_regress", "spot_valuation"))
+    # same Philox counters and Box-Muller; log/sincos come from different math libraries -> a few ulps
+    assert rel_err(got.spot_regress, ref.spot_regress) < 1e-12
+    assert rel_err(got.spot_valuation, ref.spot_valuation) < 1e-12
+    assert abs(got.npv - ref.npv) < 3 * ref.npv_std_error
+    assert rel_err(got.npv_std_error, ref.npv_std_error) < 1e-3
+    # independent draws on the device: still within 3 standard errors (of the difference)
+    other = ctx.calculate(pb, Rng.philox(101), Rng.philox(202))
+    assert abs(other.npv - ref.npv) < 3 * np.hypot(ref.npv_std_error, other.npv_std_error) + 1e-9
+
+
+def test_panels_mode_accepts_external_simulations(ctx):
+    """LSMC_RNG_PANELS: spot/factor panels from another simulator (e.g. Cmdty.Core's own) are used as they are."""
+    pb = CASES["reference_fixture_1f"]().copy(n_sims=512)
+    spot_r, fac_r = oracle.simulate(pb, Rng.philox(5))
+    spot_v, fac_v = oracle.simulate(pb, Rng.philox(6))
+    ref = oracle.calculate(pb, Rng.from_panels(spot_r, fac_r), Rng.from_panels(spot_v, fac_v)).results
+    got = ctx.calculate(pb, Rng.from_panels(spot_r, fac_r), Rng.from_panels(spot_v, fac_v))
+    assert rel_err(got.npv, ref.npv) < REL and rel_err(got.deltas, ref.deltas) < REL
+
+
+def test_full_size_properties_c3(ctx):
+    """Size-independent properties at BASELINE's full C3 size (1M paths) where the oracle cannot follow."""
+    pb = build_config("c3", num_sims=1_000_000)
+    res = ctx.calculate(pb, Rng.philox(11), Rng.philox(22))
+    small = oracle.calculate(build_config("c3", num_sims=16384), Rng.philox(11), Rng.philox(22)).results
+    assert abs(res.npv - small.npv) < 4 * np.hypot(res.npv_std_error, small.npv_std_error)
+    assert abs(res.backward_npv - res.npv) < 0.01 * abs(res.npv)           # in-sample vs out-of-sample value
+    prof = res.profile
+    assert prof[0, 0] == pb.start_inventory and abs(prof[-1, 0]) < 1e-6    # must be empty at end
+    # expected inventory recursion: E[v_{t+1}] = E[v_t] + E[d_t] - E[loss_t]
+    assert np.allclose(prof[1:, 0], prof[:-1, 0] + prof[:-1, 1] - prof[:-1, 3], rtol=0, atol=1e-6)
+    assert np.allclose(prof[:, 4], -prof[:, 1] - prof[:, 2], rtol=0, atol=1e-9)   # net volume identity
+    assert abs(prof[:, 5].sum() - res.npv) < 1e-6 * abs(res.npv)                 # NPV = sum of expected period PVs
+    assert np.all(prof[:, 0] >= -1e-9) and np.all(prof[:, 0] <= pb.max_inventory.max() + 1e-9)
+    again = ctx.calculate(pb, Rng.philox(11), Rng.philox(22))
+    assert again.npv == res.npv and np.array_equal(again.deltas, res.deltas)      # deterministic reductions
+
+
+def test_discounted_deltas_identity(ctx):   # LSMCTest:846-869
+    pb = reference_problem(num_sims=256, mean_reversion=16.5)
+    a = ctx.calculate(pb, Rng.philox(11), Rng.philox(11))
+    b = ctx.calculate(pb.copy(discount_deltas=1), Rng.philox(11), Rng.philox(11))
+    assert np.array_equal(b.deltas, a.deltas * pb.settle_df)
+
+
+def test_progress_is_ascending_ends_at_one_and_counts_like_the_reference(ctx):
+    pb = reference_problem(num_sims=128)
+    seen = []
+    ctx.calculate(pb, Rng.philox(1), Rng.philox(2), on_progress=seen.append)
+    assert seen[-1] == 1.0 and 0.0 < seen[0] < 1.0                       # LSMCTest:873-895
+    assert all(b > a for a, b in zip(seen, seen[1:]))
+    assert len(seen) == 2 * (pb.n_periods - 1) + 1                        # test_multi_factor.py:229-230 (245 for 123 periods)
+
+
+def test_cancellation_maps_to_operation_cancelled(ctx):   # LSMCTest:899-916
+    pb = reference_problem(num_sims=128)
+    calls = []
+
+    def cancel_after_ten(v):
+        calls.append(v)
+        return len(calls) < 10
+
+    with pytest.raises(_native.LsmcError) as e:
+        ctx.calculate(pb, Rng.philox(1), Rng.philox(2), on_progress=cancel_after_ten)
+    assert e.value.status == _abi.LSMC_ECANCELLED and len(calls) == 10
+    again = ctx.calculate(pb, Rng.philox(1), Rng.philox(2))               # the context stays usable
+    assert np.isfinite(again.npv)
+
+
+def test_error_statuses(ctx):
+    pb = reference_problem(num_sims=64)
+    with pytest.raises(_native.LsmcError) as e:   # start inventory cannot be run down to empty by the end (SH.cs:100-103)
+        ctx.calculate(reference_problem(num_sims=64, val_date="2020-03-25", inventory=52_000.0), Rng.philox(1), Rng.philox(2))
+    assert e.value.status in (_abi.LSMC_ECONSTRAINT, _abi.LSMC_EINVAL)
+    with pytest.raises(_native.LsmcError) as e:
+        ctx.calculate(pb.copy(n_basis=0, spot_power=np.zeros(0, dtype=np.int32), factor_power=np.zeros((0, 1), dtype=np.int32)),
+                      Rng.philox(1), Rng.philox(2))
+    assert e.value.status == _abi.LSMC_EINVAL
+    with pytest.raises(_native.LsmcError) as e:
+        ctx.forward()                                                     # staged calls out of order
+    assert e.value.status == _abi.LSMC_EINVAL
+    with pytest.raises(_native.LsmcError) as e:
+        ctx.simulate(0, Rng(_abi.RNG_NORMALS))                            # normals mode without normals
+    assert e.value.status == _abi.LSMC_EINVAL
+
+
+def test_smoke_entry_point():
+    import __graft_entry__
+    __graft_entry__.smoke()
