@@ -98,6 +98,8 @@ __global__ void __launch_bounds__(512, 1) sweep_kernel(SweepParams q) {
     double* sNP = sC + (size_t)GnP * LD;          // [n_nodes][LD]
     double* sNM = sNP + (size_t)n_nodes * LD;     // [n_nodes][LD]
     double* sBeta = sNM + (size_t)n_nodes * LD;   // [GnP][Kp4]
+    double* sXT = sBeta + (size_t)GnP * Kp4;      // [8*MT][LD] preconditioned regressors of period p-1 (rows >= K are zero)
+    double* sT = sXT + (size_t)8 * MT * LD;       // [K][K] preconditioner T (upper triangular)
     __shared__ int16_t sNodeP[64 + 8], sNodeM[64 + 8];
     __shared__ BasisOpDev sOps[kMaxOps];
 
@@ -116,6 +118,8 @@ __global__ void __launch_bounds__(512, 1) sweep_kernel(SweepParams q) {
     }
     // zero the padded rows of the staged value tile once (never overwritten by the loads)
     for (int i = q.Gn * LD + tid; i < GnP * LD; i += blockDim.x) { sVn[i] = 0.0; sC[i] = 0.0; }
+    for (int i = tid; i < 8 * MT * LD; i += blockDim.x) sXT[i] = 0.0;
+    if (q.accum_mode == 1) for (int i = tid; i < q.K * q.K; i += blockDim.x) sT[i] = __ldg(q.precond + i);
 
     double acc[NTW][MT][2];
 #pragma unroll
@@ -163,6 +167,17 @@ __global__ void __launch_bounds__(512, 1) sweep_kernel(SweepParams q) {
             }
         }
         __syncthreads();
+        // ---- preconditioned regressors of period p-1: x~_j = sum_{i<=j} T[i][j] x_i (fixed fma order) ----
+        if (q.accum_mode == 1) {
+            for (int e = tid; e < q.K * TP; e += blockDim.x) {
+                const int j = e / TP, path = e - j * TP;
+                double acc = 0.0;
+                for (int i = 0; i <= j; i++) acc = fma(sT[i * q.K + j], sNM[(size_t)sNodeM[i] * LD + path], acc);
+                sXT[(size_t)j * LD + path] = acc;
+            }
+        } else if (q.accum_mode == 2) {
+            for (int path = tid; path < TP; path += blockDim.x) sXT[path] = sNM[(size_t)1 * LD + path];
+        }
         // ---- fitted continuation values for every next-grid row ----
         if (q.mode == 0) {
             const int NTn = GnP >> 3;
@@ -186,8 +201,8 @@ __global__ void __launch_bounds__(512, 1) sweep_kernel(SweepParams q) {
                     sC[(size_t)l * LD + c] = __ldg(q.beta + (size_t)l * q.ldb);
                 }
             }
-            __syncthreads();
         }
+        __syncthreads();
         // ---- decisions + normal-equation accumulation ----
 #pragma unroll
         for (int jj = 0; jj < NTW; jj++) {
@@ -255,7 +270,7 @@ __global__ void __launch_bounds__(512, 1) sweep_kernel(SweepParams q) {
                     if (q.accum_mode) {
 #pragma unroll
                         for (int m = 0; m < MT; m++) {
-                            const double a = sNM[(size_t)sNodeM[8 * m + g] * LD + path];
+                            const double a = sXT[(size_t)(8 * m + g) * LD + path];
                             dmma8x8x4(acc[jj][m][0], acc[jj][m][1], a, v);
                         }
                     }
@@ -263,13 +278,12 @@ __global__ void __launch_bounds__(512, 1) sweep_kernel(SweepParams q) {
             } else {
                 // trailing n-tiles: B = X_{p-1} itself -> X^T X
                 const int kb = 8 * (j - NT) + g;
-                const int16_t bnode = sNodeM[kb];
                 for (int ks = 0; ks < TP / 4; ks++) {
                     const int path = 4 * ks + t;
-                    const double b = sNM[(size_t)bnode * LD + path];
+                    const double b = sXT[(size_t)kb * LD + path];
 #pragma unroll
                     for (int m = 0; m < MT; m++) {
-                        const double a = sNM[(size_t)sNodeM[8 * m + g] * LD + path];
+                        const double a = sXT[(size_t)(8 * m + g) * LD + path];
                         dmma8x8x4(acc[jj][m][0], acc[jj][m][1], a, b);
                     }
                 }
@@ -290,9 +304,9 @@ __global__ void __launch_bounds__(512, 1) sweep_kernel(SweepParams q) {
     }
 }
 
-size_t sweep_smem_bytes(int TP, int Gn, int n_nodes, int ldb) {
+size_t sweep_smem_bytes(int TP, int Gn, int n_nodes, int ldb, int MT, int K) {
     const int LD = TP + 4, GnP = (Gn + 7) & ~7;
-    return sizeof(double) * ((size_t)2 * GnP * LD + (size_t)2 * n_nodes * LD + (size_t)GnP * ldb);
+    return sizeof(double) * ((size_t)2 * GnP * LD + (size_t)2 * n_nodes * LD + (size_t)GnP * ldb + (size_t)8 * MT * LD + (size_t)K * K);
 }
 
 template <int TP, int MT, int NTW>
@@ -333,9 +347,142 @@ cudaError_t launch_sweep(SweepParams& q, const SweepConfig& cfg, cudaStream_t st
     int NTW = ntw <= 1 ? 1 : (ntw <= 2 ? 2 : 4);
     if (ntw > 4) return cudaErrorInvalidValue;
     q.ncols = 8 * (NT + MT);
-    const size_t smem = sweep_smem_bytes(cfg.TP, q.Gn, cfg.n_nodes, q.ldb);
+    const size_t smem = sweep_smem_bytes(cfg.TP, q.Gn, cfg.n_nodes, q.ldb, MT, q.K);
     if (cfg.TP == 64) return launch_sweep_tp<64>(q, MT, NTW, cfg.blocks, warps, smem, stream);
     return launch_sweep_tp<32>(q, MT, NTW, cfg.blocks, warps, smem, stream);
+}
+
+
+// =================================================================================================
+// K2p: regression preconditioner.  One CTA per simulated period: Householder QR (no pivoting, like the reference's
+// thin QR, LSV.cs:187) of the design matrix on the first `nsub` paths, held column-major in shared memory; writes
+// T = R^-1 and the dropped-column flags.  The sweep accumulates the normal equations in the basis x~ = T^T x, whose
+// Gram matrix is ~ (N/nsub) I, so the Cholesky solve that follows has QR-grade accuracy however ill-conditioned the
+// raw monomials are (cond(X) reaches 1e13 at the first half-hourly steps of a two-factor model).
+// =================================================================================================
+__device__ __forceinline__ double block_sum(double v, double* scratch) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+    __syncthreads();
+    if (lane == 0) scratch[warp] = v;
+    __syncthreads();
+    double tot = 0.0;
+    for (int w = 0; w < nw; w++) tot += scratch[w];
+    return tot;
+}
+
+__global__ void __launch_bounds__(512) precond_kernel(PrecondParams q) {
+    extern __shared__ double psm[];
+    const int K = q.K, n = q.nsub, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
+    const int j = blockIdx.x;
+    const BasisDev* __restrict__ bd = q.basis;
+    double* A = psm;                      // [K][n] column-major
+    double* R = A + (size_t)K * n;        // [K][K]
+    double* col0 = R + K * K;             // [K] original column norms
+    double* scratch = col0 + K;           // [32]
+    __shared__ int s_dropped[64];
+    __shared__ double s_tau, s_scale;
+    __shared__ int s_skip;
+
+    for (int i = tid; i < n; i += blockDim.x) {
+        const double s = q.spot[(size_t)j * q.Npad + i];
+        double f[kMaxFactors];
+        for (int a = 0; a < q.F; a++) f[a] = q.fac[((size_t)j * q.F + a) * q.Npad + i];
+        for (int k = 0; k < K; k++) {
+            double acc = 1.0;
+            for (int e = 0; e < bd->spot_pow[k]; e++) acc *= s;
+            for (int a = 0; a < q.F; a++)
+                for (int e = 0; e < bd->fac_pow[k][a]; e++) acc *= f[a];
+            A[(size_t)k * n + i] = acc;
+        }
+    }
+    for (int e = tid; e < K * K; e += blockDim.x) R[e] = 0.0;
+    __syncthreads();
+    for (int k = 0; k < K; k++) {
+        double part = 0.0;
+        for (int i = tid; i < n; i += blockDim.x) { const double a = A[(size_t)k * n + i]; part += a * a; }
+        const double tot = block_sum(part, scratch);
+        if (tid == 0) col0[k] = sqrt(tot);
+    }
+    __syncthreads();
+
+    int r = 0;   // pivot row = number of columns kept so far (uniform across the block)
+    for (int k = 0; k < K; k++) {
+        double* ck = A + (size_t)k * n;
+        double part = 0.0;
+        for (int i = r + tid; i < n; i += blockDim.x) part += ck[i] * ck[i];
+        const double normsq = block_sum(part, scratch);
+        if (tid == 0) {
+            const double norm = sqrt(normsq);
+            if (r >= n || !(norm > 1e-13 * col0[k]) || col0[k] == 0.0) {
+                s_skip = 1; s_dropped[k] = 1;
+            } else {
+                const double alpha = ck[r];
+                const double beta = alpha >= 0.0 ? -norm : norm;
+                s_tau = (beta - alpha) / beta;
+                s_scale = 1.0 / (alpha - beta);
+                s_skip = 0; s_dropped[k] = 0;
+                R[k * K + k] = beta;
+            }
+        }
+        __syncthreads();
+        if (s_skip) {
+            if (tid == 0) { for (int m = 0; m < K; m++) { R[m * K + k] = 0.0; } R[k * K + k] = 1.0; }
+            __syncthreads();
+            continue;
+        }
+        const double tau = s_tau, scale = s_scale;
+        for (int i = r + 1 + tid; i < n; i += blockDim.x) ck[i] *= scale;
+        __syncthreads();
+        // apply H = I - tau v v^T (v_r = 1) to the trailing columns: one warp per column
+        for (int c = k + 1 + warp; c < K; c += nw) {
+            double* cc = A + (size_t)c * n;
+            double dot = 0.0;
+            for (int i = r + 1 + lane; i < n; i += 32) dot += ck[i] * cc[i];
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, off);
+            dot = (dot + cc[r]) * tau;
+            for (int i = r + 1 + lane; i < n; i += 32) cc[i] -= dot * ck[i];
+            if (lane == 0) { cc[r] -= dot; R[k * K + c] = cc[r]; }
+        }
+        __syncthreads();
+        r++;
+    }
+    // rows of R that belong to dropped columns stay e_k; entries R[k][c] for a dropped c were zeroed when c was
+    // skipped only for m < c processed so far -> clear the whole column again now
+    for (int e = tid; e < K * K; e += blockDim.x) {
+        const int row = e / K, c = e % K;
+        if (row != c && (s_dropped[c] || s_dropped[row])) R[e] = 0.0;
+    }
+    __syncthreads();
+    // T = R^-1, one thread per column
+    double* out = q.out + (size_t)j * precond_stride(K);
+    if (tid < K) {
+        const int c = tid;
+        double tcol[64];
+        for (int i = K - 1; i >= 0; i--) {
+            if (i > c) { tcol[i] = 0.0; continue; }
+            double sum = (i == c) ? 1.0 : 0.0;
+            for (int m = i + 1; m <= c; m++) sum -= R[i * K + m] * tcol[m];
+            tcol[i] = sum / R[i * K + i];
+        }
+        for (int i = 0; i < K; i++) out[(size_t)i * K + c] = tcol[i];
+        out[(size_t)K * K + c] = s_dropped[c] ? 1.0 : 0.0;
+    }
+}
+
+int precond_rows(int K, int64_t N) {
+    int cap = (int)((200 * 1024 / sizeof(double) - (size_t)K * K - K - 32) / K);
+    cap = std::min(cap, 2048) & ~31;
+    return (int)std::min<int64_t>(cap, N);
+}
+
+void launch_precond(const PrecondParams& q, cudaStream_t stream) {
+    const size_t smem = sizeof(double) * ((size_t)q.K * q.nsub + (size_t)q.K * q.K + q.K + 32);
+    static size_t configured = 0;
+    if (smem > configured) { cudaFuncSetAttribute(precond_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); configured = smem; }
+    precond_kernel<<<q.S, 512, smem, stream>>>(q);
 }
 
 // =================================================================================================
@@ -381,10 +528,12 @@ __global__ void __launch_bounds__(256) solve_kernel(SolveParams sp) {
     double* dscale = Graw + K * K;  // [K]
     __shared__ int dropped[64];
     const int gcol = 8 * sp.NT;
+    const double* T = sp.precond;
     for (int k = tid; k < K; k += blockDim.x) {
         double gkk = red[(size_t)k * ld + gcol + k];
-        dscale[k] = gkk > 0.0 ? rsqrt(gkk) : 0.0;
-        dropped[k] = gkk > 0.0 ? 0 : 1;
+        const bool flagged = T && T[(size_t)K * K + k] != 0.0;   // column found dependent by the preconditioner's QR
+        dscale[k] = (gkk > 0.0 && !flagged) ? rsqrt(gkk) : 0.0;
+        dropped[k] = (gkk > 0.0 && !flagged) ? 0 : 1;
     }
     __syncthreads();
     for (int e = tid; e < K * K; e += blockDim.x) {
@@ -439,7 +588,16 @@ __global__ void __launch_bounds__(256) solve_kernel(SolveParams sp) {
             }
         }
         double* b = sp.beta + (size_t)i * sp.ldb;
-        for (int k = 0; k < sp.ldb; k++) b[k] = k < K ? x[k] : 0.0;
+        if (T) {   // back to the monomial basis: beta = T x
+            for (int k = 0; k < K; k++) {
+                double acc = 0.0;
+                for (int m = k; m < K; m++) acc = fma(T[(size_t)k * K + m], x[m], acc);
+                r[k] = acc;
+            }
+            for (int k = 0; k < sp.ldb; k++) b[k] = k < K ? r[k] : 0.0;
+        } else {
+            for (int k = 0; k < sp.ldb; k++) b[k] = k < K ? x[k] : 0.0;
+        }
     }
 }
 

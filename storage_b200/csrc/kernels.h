@@ -19,6 +19,7 @@ struct SolveParams {
     int ncols, K, G, NT, ldb, accum_mode;
     int64_t n_global;
     double pivot_tol;
+    const double* precond;   // T [K][K] + flags [K] of the regressed period
     double* beta;            // [G][ldb]
 };
 
@@ -33,7 +34,9 @@ struct FinalParams {
     double* o_inventory; double* o_pv;
 };
 
-size_t sweep_smem_bytes(int TP, int Gn, int n_nodes, int ldb);
+size_t sweep_smem_bytes(int TP, int Gn, int n_nodes, int ldb, int MT, int K);
+int precond_rows(int K, int64_t N);
+void launch_precond(const PrecondParams& q, cudaStream_t stream);
 void launch_simulate(const SimParams& sp, cudaStream_t stream);
 cudaError_t launch_sweep(SweepParams& q, const SweepConfig& cfg, cudaStream_t stream);
 void launch_reduce_partials(const double* partial, int n_parts, int n_elem, double* out, cudaStream_t stream);

@@ -48,6 +48,7 @@ struct NcclApi {
     int (*GetUniqueId)(void*) = nullptr;
     int (*CommInitRank)(void**, int, char[128], int) = nullptr;   // ncclUniqueId is a 128-byte struct passed by value
     int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*Broadcast)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
     int (*CommDestroy)(void*) = nullptr;
     const char* (*GetErrorString)(int) = nullptr;
     bool load(std::string& err) {
@@ -58,9 +59,10 @@ struct NcclApi {
         GetUniqueId = (int (*)(void*))dlsym(handle, "ncclGetUniqueId");
         CommInitRank = (int (*)(void**, int, char[128], int))dlsym(handle, "ncclCommInitRank");
         AllReduce = (int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t))dlsym(handle, "ncclAllReduce");
+        Broadcast = (int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t))dlsym(handle, "ncclBroadcast");
         CommDestroy = (int (*)(void*))dlsym(handle, "ncclCommDestroy");
         GetErrorString = (const char* (*)(int))dlsym(handle, "ncclGetErrorString");
-        if (!GetUniqueId || !CommInitRank || !AllReduce || !CommDestroy) { err = "libnccl is missing symbols"; return false; }
+        if (!GetUniqueId || !CommInitRank || !AllReduce || !Broadcast || !CommDestroy) { err = "libnccl is missing symbols"; return false; }
         return true;
     }
 };
@@ -86,6 +88,7 @@ struct lsmc_ctx {
     DevBuf<int32_t> t_ndec, t_lo, t_hi;
     DevBuf<double> s_decay, s_chol, s_vol, s_drift, s_fwd, normals_stage;
     DevBuf<BasisDev> basis;
+    DevBuf<double> precond;     // [S][precond_stride(K)] regression preconditioners (rank 0's, broadcast)
     DevBuf<int> error_flag;
     DevBuf<double> panels[6];
     DevBuf<int8_t> decisions;
@@ -119,6 +122,11 @@ struct lsmc_ctx {
         if (world <= 1) return;
         int rc = g_nccl.AllReduce(buf, buf, count, /*ncclFloat64*/ 8, /*ncclSum*/ 0, comm, stream);
         if (rc != 0) throw Error(LSMC_ECUDA, std::string("ncclAllReduce: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "error"));
+    }
+    void broadcast0(double* buf, size_t count) {
+        if (world <= 1) return;
+        int rc = g_nccl.Broadcast(buf, buf, count, /*ncclFloat64*/ 8, /*root*/ 0, comm, stream);
+        if (rc != 0) throw Error(LSMC_ECUDA, std::string("ncclBroadcast: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "error"));
     }
 };
 
@@ -166,8 +174,8 @@ void set_problem(lsmc_ctx* c, const lsmc_problem* problem) {
     c->ldb = (pl.K + 3) & ~3;
     require(pl.basis.n_nodes <= kMaxNodes && (int)pl.basis.ops.size() <= kMaxOps, LSMC_EUNSUPPORTED, "basis functions need too many product nodes");
     require(pl.max_dec <= 16, LSMC_EUNSUPPORTED, "extra_decisions above 6 is not supported on the device path");
-    c->TP = sweep_smem_bytes(64, pl.max_grid, pl.basis.n_nodes, c->ldb) <= 200 * 1024 ? 64 : 32;
-    require(sweep_smem_bytes(c->TP, pl.max_grid, pl.basis.n_nodes, c->ldb) <= 220 * 1024, LSMC_EUNSUPPORTED, "inventory grid / basis too large for the sweep kernel's shared memory");
+    c->TP = sweep_smem_bytes(64, pl.max_grid, pl.basis.n_nodes, c->ldb, c->MT, pl.K) <= 200 * 1024 ? 64 : 32;
+    require(sweep_smem_bytes(c->TP, pl.max_grid, pl.basis.n_nodes, c->ldb, c->MT, pl.K) <= 220 * 1024, LSMC_EUNSUPPORTED, "inventory grid / basis too large for the sweep kernel's shared memory");
     require((pl.max_grid + 7) / 8 + c->MT <= 64, LSMC_EUNSUPPORTED, "inventory grid has too many points for the sweep kernel (max 448)");
     c->Npad = (c->N + 63) / 64 * 64;
     c->sweep_blocks = (int)std::min<int64_t>(c->num_sms, c->Npad / c->TP);
@@ -204,10 +212,19 @@ void set_problem(lsmc_ctx* c, const lsmc_problem* problem) {
         std::memset(&b, 0, sizeof(b));
         b.n_nodes = pl.basis.n_nodes; b.n_ops = (int)pl.basis.ops.size(); b.K = pl.K; b.F = pl.F;
         for (size_t i = 0; i < pl.basis.ops.size(); i++) b.ops[i] = BasisOpDev{pl.basis.ops[i].dst, pl.basis.ops[i].a, pl.basis.ops[i].b, 0};
-        for (int k = 0; k < pl.K; k++) b.node_of_basis[k] = pl.basis.node_of_basis[k];
+        for (int k = 0; k < pl.K; k++) {
+            b.node_of_basis[k] = pl.basis.node_of_basis[k];
+            require(pb.spot_power[k] <= 127, LSMC_EUNSUPPORTED, "basis exponent above 127");
+            b.spot_pow[k] = (int8_t)pb.spot_power[k];
+            for (int f = 0; f < pl.F; f++) {
+                require(pb.factor_power[k * pl.F + f] <= 127, LSMC_EUNSUPPORTED, "basis exponent above 127");
+                b.fac_pow[k][f] = (int8_t)pb.factor_power[k * pl.F + f];
+            }
+        }
         c->basis.upload(hb, s);
         CUDA_CHECK(cudaStreamSynchronize(s));   // hb goes out of scope
     }
+    c->precond.alloc((size_t)pl.S * precond_stride(pl.K));
     c->error_flag.alloc(1);
     CUDA_CHECK(cudaMemsetAsync(c->error_flag.p, 0, sizeof(int), s));
     if (c->outputs & 1) for (auto& pbuf : c->panels) pbuf.alloc((size_t)pl.P * Np);
@@ -250,6 +267,16 @@ void simulate(lsmc_ctx* c, int set, const lsmc_rng* rng) {
         launch_simulate(sp, s);
         CUDA_CHECK(cudaGetLastError());
         c->tm.kernel_launches++;
+    }
+    if (set == 0) {
+        // regression preconditioners for every simulated period, from the first paths of global rank 0
+        PrecondParams pq{};
+        pq.N = c->N; pq.Npad = c->Npad; pq.S = pl.S; pq.K = pl.K; pq.F = pl.F; pq.nsub = precond_rows(pl.K, c->N);
+        pq.spot = c->spot[0].p; pq.fac = c->fac.p; pq.basis = c->basis.p; pq.out = c->precond.p;
+        launch_precond(pq, s);
+        CUDA_CHECK(cudaGetLastError());
+        c->tm.kernel_launches++;
+        c->broadcast0(c->precond.p, (size_t)pl.S * precond_stride(pl.K));
     }
     if (set == 1) c->valuation_antithetic = (rng->mode == LSMC_RNG_PHILOX && rng->antithetic) ? 1 : 0;
     CUDA_CHECK(cudaEventRecord(c->event(set == 0 ? 1 : 5), s));
@@ -318,6 +345,7 @@ void backward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
         else {
             q.accum_mode = (p - 1 == 0 && s0 == 1) ? 2 : 1;
             regressors(p - 1, q.spot_m, q.fac_m);
+            if (q.accum_mode == 1) q.precond = c->precond.p + (size_t)(p - 1 - s0) * precond_stride(pl.K);
         }
         CUDA_CHECK(cudaEventRecord(c->event(ev_base), s));
         CUDA_CHECK(launch_sweep(q, cfg, s));
@@ -335,6 +363,7 @@ void backward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
             SolveParams sp{};
             sp.reduced = c->reduced.p; sp.ncols = q.ncols; sp.K = pl.K; sp.G = q.G; sp.NT = (q.G + 7) / 8; sp.ldb = c->ldb;
             sp.accum_mode = q.accum_mode; sp.n_global = c->Nglobal; sp.pivot_tol = 1e-13;
+            sp.precond = q.accum_mode == 1 ? q.precond : nullptr;
             sp.beta = c->beta_all.p + (size_t)(p - 1) * c->beta_stride();
             launch_solve(sp, s);
             c->tm.kernel_launches++;

@@ -87,7 +87,13 @@ struct BasisDev {
     int n_nodes, n_ops, K, F;
     BasisOpDev ops[kMaxOps];
     int16_t node_of_basis[64];
+    int8_t spot_pow[64];                 // exponents (BasisFunctions.cs:92-132), used by the preconditioner kernel
+    int8_t fac_pow[64][kMaxFactors];
 };
+
+// Per-period regression preconditioner: T = R_sub^-1 (upper triangular, K x K, row-major) from a
+// Householder QR of the design matrix on a subsample of paths, followed by K dropped-column flags.
+__host__ __device__ inline size_t precond_stride(int K) { return (size_t)K * K + K; }
 
 // ------------------------------------------------------------------------------------------------
 // Parameter blocks
@@ -125,8 +131,18 @@ struct SweepParams {
     const double* t_vol; const double* t_cost; const double* t_cons; const double* t_wlo; const double* t_whi;
     const int32_t* t_lo; const int32_t* t_hi;
     const BasisDev* basis;
+    const double* precond;    // preconditioner of period p-1 (accum_mode 1): T [K][K] + flags [K]
     double* partial;          // [gridDim.x][8*MT][ncols] normal-equation partials
     int ncols;                // 8 * (ceil(G/8) + MT)
+};
+
+struct PrecondParams {
+    int64_t N, Npad;
+    int S, K, F, nsub;
+    const double* spot;       // [S][Npad] regression set
+    const double* fac;        // [S][F][Npad]
+    const BasisDev* basis;
+    double* out;              // [S][precond_stride(K)]
 };
 
 struct ForwardParams {

@@ -20,7 +20,12 @@ def pandas_freq(freq: str) -> str:
     if freq not in FREQ_TO_PERIOD_TYPE:
         raise ValueError("freq parameter value of '{}' not supported. The allowable values can be found in the keys of "
                          "the dict curves.FREQ_TO_PERIOD_TYPE.".format(freq))
-    return FREQ_TO_PERIOD_TYPE[freq]
+    return pd.Period("2000-01-01", freq=FREQ_TO_PERIOD_TYPE[freq]).freqstr
+
+
+def pandas_freq_of_index(index: pd.PeriodIndex) -> str:
+    """Canonical pandas alias of a PeriodIndex's frequency (the reference compares `freqstr` with the storage freq)."""
+    return pd.Period("2000-01-01", freq=index.freq).freqstr
 
 
 def to_period(date_like: TimePeriodSpecType, freq: str) -> pd.Period:

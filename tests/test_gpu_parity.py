@@ -45,6 +45,27 @@ def material_flips(got, ref):
     return int(np.sum(np.abs(got.inject_withdraw - ref.inject_withdraw) > 1e-9 * max(scale, 1e-300)))
 
 
+def comparable_trigger_rows(got, ref, side):
+    """Rows whose trigger side is well defined.  The reference emits a side only when `max > alternative`
+    (LSV.cs:510,538); near the end of a must-be-empty storage both are the same forced volume up to rounding of the
+    MEAN inventory (a sum over sims, whose order differs on the device), so presence itself is rounding noise there.
+    Such degenerate rows (volume span below 1e-9 of the rate scale) are excluded and must stay rare."""
+    gp, rp = (got.trigger_inject, ref.trigger_inject) if side == 0 else (got.trigger_withdraw, ref.trigger_withdraw)
+    scale = max(np.nanmax(np.abs(rp[..., 0])) if np.any(~np.isnan(rp[..., 0])) else 0.0, 1e-300)
+
+    def degenerate(prof):
+        v = prof[..., 0]
+        has = ~np.isnan(v[:, 0])
+        span = np.where(has, np.nanmax(np.where(np.isnan(v), -np.inf, v), axis=1) - np.nanmin(np.where(np.isnan(v), np.inf, v), axis=1), np.inf)
+        return has & (span < 1e-9 * scale)
+
+    mismatch = np.isnan(gp[:, 0, 0]) != np.isnan(rp[:, 0, 0])
+    excluded = mismatch & (degenerate(gp) | degenerate(rp))
+    assert not np.any(mismatch & ~excluded), "trigger presence differs on a well-defined row"
+    assert excluded.sum() <= max(2, len(excluded) // 50)
+    return ~excluded
+
+
 CASES = {
     "c1_readme_simple_3f": lambda: build_config("c1", num_sims=1000),
     "c2_one_factor": lambda: build_config("c2", num_sims=1536),
@@ -120,10 +141,13 @@ def test_end_to_end_within_1e9_with_injected_normals(case, ctx):
     assert rel_err(got.profile, ref.profile) < REL
     assert material_flips(got, ref) == 0
     price_scale = float(np.max(pb.forward))
-    assert rel_err(got.trigger_summary[:, [0, 2]], ref.trigger_summary[:, [0, 2]]) < REL      # volumes
-    assert rel_err(got.trigger_summary[:, [1, 3]], ref.trigger_summary[:, [1, 3]], price_scale) < 1e-7   # prices: a ratio of small differences
-    assert rel_err(got.trigger_inject[..., 0], ref.trigger_inject[..., 0]) < REL
-    assert rel_err(got.trigger_withdraw[..., 0], ref.trigger_withdraw[..., 0]) < REL
+    for side, (gp, rp) in enumerate(((got.trigger_inject, ref.trigger_inject), (got.trigger_withdraw, ref.trigger_withdraw))):
+        rows = comparable_trigger_rows(got, ref, side)
+        cols = [2 * side, 2 * side + 1]
+        assert rel_err(got.trigger_summary[rows][:, cols[0]], ref.trigger_summary[rows][:, cols[0]]) < REL               # volumes
+        assert rel_err(got.trigger_summary[rows][:, cols[1]], ref.trigger_summary[rows][:, cols[1]], price_scale) < 1e-7  # prices: ratios of small differences
+        assert rel_err(gp[rows][..., 0], rp[rows][..., 0]) < REL
+        assert rel_err(gp[rows][..., 1], rp[rows][..., 1], price_scale) < 1e-6
     assert rel_err(got.pv_by_sim, ref.pv_by_sim, max(abs(ref.npv), 1.0)) < 1e-7
 
 
