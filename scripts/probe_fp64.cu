@@ -1,6 +1,6 @@
 // probe_fp64.cu — measures the FP64 roofs of a B200 that the sweep kernel is bounded by besides HBM:
 // scalar DFMA/DMUL/DADD issue rate, DMMA (mma.sync m8n8k4 / m16n8k8 f64) rate, and both interleaved.
-// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o probe_fp64 probe_fp64.cu ; run on the GPU box.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o /tmp/probe_fp64 scripts/probe_fp64.cu ; run on the GPU box.
 #include <cstdio>
 #include <cuda_runtime.h>
 
