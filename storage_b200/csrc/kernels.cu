@@ -68,290 +68,7 @@ void launch_simulate(const SimParams& sp, cudaStream_t stream) {
     }
 }
 
-// =================================================================================================
-// K3: fused backward sweep.
-//
-// A CTA walks path tiles of TP paths.  Per tile:
-//   stage   V_next[Gn][TP] -> smem (coalesced 16 B per lane), design-matrix nodes of period p and p-1 -> smem
-//   fit     C^[l][n] = sum_k beta[l][k] X_p[n][k]  for all next-grid rows l: DMMA, A = beta, B = X_p^T -> smem
-//   decide  lane (g,t) of warp w owns grid row i = 8*ntile + g and paths 4*ks + t: max over the bang-bang
-//           decisions of immediate + interpolated C^, realised value from interpolated V_next -> store V[i][n];
-//           the value just computed is the B operand of the DMMA that accumulates X_{p-1}^T V (and, on the
-//           trailing "basis" n-tiles, X_{p-1}^T X_{p-1}) without ever touching shared memory again.
-// The accumulators live in registers for the whole kernel and are written once per CTA.
-// =================================================================================================
-template <int TP, int MT, int NTW>
-__global__ void __launch_bounds__(512, 1) sweep_kernel(SweepParams q) {
-    constexpr int LD = TP + 4;   // row stride in doubles: consecutive rows 8 banks apart -> a half-warp's 4 rows x 4 paths hit 32 distinct banks
-    extern __shared__ double smem[];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, W = blockDim.x >> 5;
-    const int g = lane >> 2, t = lane & 3;
-    const BasisDev* __restrict__ bd = q.basis;
-    const int n_nodes = bd->n_nodes;
-    const int GnP = (q.Gn + 7) & ~7;
-    const int NT = (q.G + 7) >> 3;            // decision n-tiles
-    const int NTaug = q.accum_mode ? NT + MT : NT;
-    const int Kp4 = q.ldb;
-
-    double* sVn = smem;                           // [GnP][LD]
-    double* sC = sVn + (size_t)GnP * LD;          // [GnP][LD]
-    double* sNP = sC + (size_t)GnP * LD;          // [n_nodes][LD]
-    double* sNM = sNP + (size_t)n_nodes * LD;     // [n_nodes][LD]
-    double* sBeta = sNM + (size_t)n_nodes * LD;   // [GnP][Kp4]
-    double* sXT = sBeta + (size_t)GnP * Kp4;      // [8*MT][LD] preconditioned regressors of period p-1 (rows >= K are zero)
-    double* sT = sXT + (size_t)8 * MT * LD;       // [K][K] preconditioner T (upper triangular)
-    __shared__ int16_t sNodeP[64 + 8], sNodeM[64 + 8];
-    __shared__ BasisOpDev sOps[kMaxOps];
-
-    // one-time staging: basis program, coefficients
-    for (int i = tid; i < bd->n_ops; i += blockDim.x) sOps[i] = bd->ops[i];
-    for (int k = tid; k < 72; k += blockDim.x) {
-        int16_t node = (k < q.K) ? bd->node_of_basis[k] : (int16_t)0;
-        sNodeP[k] = node;
-        sNodeM[k] = (q.accum_mode == 1) ? node : (int16_t)((q.accum_mode == 2 && k == 0) ? 1 : 0);
-    }
-    if (q.mode == 0) {
-        for (int i = tid; i < GnP * Kp4; i += blockDim.x) {
-            int l = i / Kp4;
-            sBeta[i] = (l < q.Gn) ? __ldg(q.beta + i) : 0.0;
-        }
-    }
-    // zero the padded rows of the staged value tile once (never overwritten by the loads)
-    for (int i = q.Gn * LD + tid; i < GnP * LD; i += blockDim.x) { sVn[i] = 0.0; sC[i] = 0.0; }
-    for (int i = tid; i < 8 * MT * LD; i += blockDim.x) sXT[i] = 0.0;
-    if (q.accum_mode == 1) for (int i = tid; i < q.K * q.K; i += blockDim.x) sT[i] = __ldg(q.precond + i);
-
-    double acc[NTW][MT][2];
-#pragma unroll
-    for (int a = 0; a < NTW; a++)
-#pragma unroll
-        for (int m = 0; m < MT; m++) acc[a][m][0] = acc[a][m][1] = 0.0;
-
-    const int64_t n_tiles = q.Npad / TP;
-    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const int64_t n0 = tile * TP;
-        __syncthreads();   // previous tile fully consumed
-        // ---- stage V_next tile ----
-        if (q.mode == 0) {
-            constexpr int LPR = TP / 2;          // lanes per row (16 B each)
-            constexpr int RPW = 32 / LPR;        // rows per warp pass
-            const int sub = lane / LPR, col = (lane % LPR) * 2;
-            for (int r = warp * RPW + sub; r < q.Gn; r += W * RPW) {
-                const double2 v = __ldcs(reinterpret_cast<const double2*>(q.Vnext + (size_t)r * q.Npad + n0 + col));
-                *reinterpret_cast<double2*>(sVn + (size_t)r * LD + col) = v;
-            }
-        }
-        // ---- design-matrix nodes for period p (threads [0,TP)) and p-1 (threads [TP,2TP)) ----
-        if (tid < 2 * TP) {
-            const bool isM = tid >= TP;
-            const int path = isM ? tid - TP : tid;
-            const int64_t n = n0 + path;
-            double* nodes = isM ? sNM : sNP;
-            const bool live = n < q.N;
-            bool skip = isM ? (q.accum_mode != 1) : false;
-            const double* spot = isM ? q.spot_m : q.spot_p;
-            const double* fac = isM ? q.fac_m : q.fac_p;
-            nodes[0 * LD + path] = 0.0;
-            nodes[1 * LD + path] = (live && (!isM || q.accum_mode)) ? 1.0 : 0.0;
-            if (!skip) {
-                double s = (!isM && q.spot_is_const) ? q.spot_const : __ldcs(spot + n);
-                nodes[2 * LD + path] = live ? s : 0.0;
-                const bool need_fac = isM || (q.mode == 0 && q.cont_mode == 0);
-                if (need_fac) {
-                    for (int f = 0; f < q.F; f++) nodes[(3 + f) * LD + path] = live ? __ldcs(fac + (size_t)f * q.Npad + n) : 0.0;
-                    for (int o = 0; o < bd->n_ops; o++) {
-                        const BasisOpDev op = sOps[o];
-                        nodes[op.dst * LD + path] = mul_rn(nodes[op.a * LD + path], nodes[op.b * LD + path]);
-                    }
-                }
-            }
-        }
-        __syncthreads();
-        // ---- preconditioned regressors of period p-1: x~_j = sum_{i<=j} T[i][j] x_i (fixed fma order) ----
-        if (q.accum_mode == 1) {
-            for (int e = tid; e < q.K * TP; e += blockDim.x) {
-                const int j = e / TP, path = e - j * TP;
-                double acc = 0.0;
-                for (int i = 0; i <= j; i++) acc = fma(sT[i * q.K + j], sNM[(size_t)sNodeM[i] * LD + path], acc);
-                sXT[(size_t)j * LD + path] = acc;
-            }
-        } else if (q.accum_mode == 2) {
-            for (int path = tid; path < TP; path += blockDim.x) sXT[path] = sNM[(size_t)1 * LD + path];
-        }
-        // ---- fitted continuation values for every next-grid row ----
-        if (q.mode == 0) {
-            const int NTn = GnP >> 3;
-            if (q.cont_mode == 0) {
-                for (int mt = warp; mt < NTn; mt += W) {
-                    const double* brow = sBeta + (size_t)(8 * mt + g) * Kp4;
-#pragma unroll 1
-                    for (int nt = 0; nt < TP / 8; nt++) {
-                        double c0 = 0.0, c1 = 0.0;
-                        for (int ks = 0; ks < Kp4; ks += 4) {
-                            const double a = brow[ks + t];
-                            const double b = sNP[(size_t)sNodeP[ks + t] * LD + 8 * nt + g];
-                            dmma8x8x4(c0, c1, a, b);
-                        }
-                        *reinterpret_cast<double2*>(sC + (size_t)(8 * mt + g) * LD + 8 * nt + 2 * t) = make_double2(c0, c1);
-                    }
-                }
-            } else {
-                for (int i = tid; i < q.Gn * TP; i += blockDim.x) {
-                    int l = i / TP, c = i % TP;
-                    sC[(size_t)l * LD + c] = __ldg(q.beta + (size_t)l * q.ldb);
-                }
-            }
-        }
-        __syncthreads();
-        // ---- decisions + normal-equation accumulation ----
-#pragma unroll
-        for (int jj = 0; jj < NTW; jj++) {
-            const int j = warp + jj * W;
-            if (j >= NTaug) break;
-            if (j < NT) {
-                const int i = 8 * j + g;
-                const bool row_ok = i < q.G;
-                // decision table of this lane's grid row -> registers (specialised for up to 3 decisions; more
-                // decisions re-read the table from L1 inside the loop)
-                int nd = 0; double invc = 0.0, gridv = 0.0;
-                double dv[3], dc[3], dm[3], wl[3], wh[3]; int lo[3], hi[3];
-                const size_t trow = (size_t)(row_ok ? i : 0) * q.max_dec;
-                if (q.mode == 0) {
-                    if (row_ok) { nd = __ldg(q.t_ndec + i); invc = __ldg(q.t_invcost + i); }
-#pragma unroll
-                    for (int d = 0; d < 3; d++) {
-                        const bool on = d < nd;
-                        dv[d] = on ? __ldg(q.t_vol + trow + d) : 0.0;
-                        dc[d] = on ? __ldg(q.t_cost + trow + d) : 0.0;
-                        dm[d] = on ? __ldg(q.t_cons + trow + d) : 0.0;
-                        wl[d] = on ? __ldg(q.t_wlo + trow + d) : 0.0;
-                        wh[d] = on ? __ldg(q.t_whi + trow + d) : 0.0;
-                        lo[d] = on ? __ldg(q.t_lo + trow + d) : 0;
-                        hi[d] = on ? __ldg(q.t_hi + trow + d) : 0;
-                    }
-                } else if (row_ok) gridv = __ldg(q.grid + i);
-#pragma unroll 2
-                for (int ks = 0; ks < TP / 4; ks++) {
-                    const int path = 4 * ks + t;
-                    double v = 0.0;
-                    if (row_ok) {
-                        const double s = sNP[2 * LD + path];
-                        if (q.mode == 1) {
-                            v = q.must_be_empty ? 0.0
-                                : add_rn(add_rn(add_rn(q.tc0, mul_rn(q.tc1, s)), mul_rn(q.tc2, gridv)), mul_rn(q.tc3, mul_rn(s, gridv)));
-                        } else {
-                            double best = 0.0, bestC = 0.0; int bl = 0, bh = 0; double bwl = 1.0, bwh = 0.0;
-                            auto consider = [&](int d, double vol, double cost, double cons, double wlo, double whi, int l, int h) {
-                                const double a = mul_rn(mul_rn(-vol, s), q.df);
-                                const double c = mul_rn(mul_rn(-cons, s), q.df);
-                                const double imm = add_rn(sub_rn(a, cost), c);
-                                const double cl = sC[(size_t)l * LD + path];
-                                double cont = cl;
-                                if (h != l) cont = add_rn(mul_rn(sC[(size_t)h * LD + path], whi), mul_rn(cl, wlo));
-                                const double tot = sub_rn(add_rn(imm, cont), invc);
-                                if (d == 0 || tot > best) { best = tot; bestC = cont; bl = l; bh = h; bwl = wlo; bwh = whi; }
-                            };
-                            if (nd <= 3) {
-#pragma unroll
-                                for (int d = 0; d < 3; d++)
-                                    if (d < nd) consider(d, dv[d], dc[d], dm[d], wl[d], wh[d], lo[d], hi[d]);
-                            } else {
-                                for (int d = 0; d < nd; d++)
-                                    consider(d, __ldg(q.t_vol + trow + d), __ldg(q.t_cost + trow + d), __ldg(q.t_cons + trow + d),
-                                             __ldg(q.t_wlo + trow + d), __ldg(q.t_whi + trow + d), __ldg(q.t_lo + trow + d), __ldg(q.t_hi + trow + d));
-                            }
-                            const double al = sVn[(size_t)bl * LD + path];
-                            double act = al;
-                            if (bh != bl) act = add_rn(mul_rn(sVn[(size_t)bh * LD + path], bwh), mul_rn(al, bwl));
-                            v = add_rn(best, add_rn(-bestC, act));
-                        }
-                        __stcs(q.Vout + (size_t)i * q.Npad + n0 + path, v);
-                    }
-                    if (q.accum_mode) {
-#pragma unroll
-                        for (int m = 0; m < MT; m++) {
-                            const double a = sXT[(size_t)(8 * m + g) * LD + path];
-                            dmma8x8x4(acc[jj][m][0], acc[jj][m][1], a, v);
-                        }
-                    }
-                }
-            } else {
-                // trailing n-tiles: B = X_{p-1} itself -> X^T X
-                const int kb = 8 * (j - NT) + g;
-                for (int ks = 0; ks < TP / 4; ks++) {
-                    const int path = 4 * ks + t;
-                    const double b = sXT[(size_t)kb * LD + path];
-#pragma unroll
-                    for (int m = 0; m < MT; m++) {
-                        const double a = sXT[(size_t)(8 * m + g) * LD + path];
-                        dmma8x8x4(acc[jj][m][0], acc[jj][m][1], a, b);
-                    }
-                }
-            }
-        }
-    }
-    // ---- per-CTA partial: partial[cta][k][col], k = 8m+g, col = 8j+2t ----
-    if (q.accum_mode) {
-        double* out = q.partial + (size_t)blockIdx.x * (8 * MT) * q.ncols;
-#pragma unroll
-        for (int jj = 0; jj < NTW; jj++) {
-            const int j = warp + jj * W;
-            if (j >= NTaug) break;
-#pragma unroll
-            for (int m = 0; m < MT; m++)
-                *reinterpret_cast<double2*>(out + (size_t)(8 * m + g) * q.ncols + 8 * j + 2 * t) = make_double2(acc[jj][m][0], acc[jj][m][1]);
-        }
-    }
-}
-
-size_t sweep_smem_bytes(int TP, int Gn, int n_nodes, int ldb, int MT, int K) {
-    const int LD = TP + 4, GnP = (Gn + 7) & ~7;
-    return sizeof(double) * ((size_t)2 * GnP * LD + (size_t)2 * n_nodes * LD + (size_t)GnP * ldb + (size_t)8 * MT * LD + (size_t)K * K);
-}
-
-template <int TP, int MT, int NTW>
-static cudaError_t launch_sweep_t(const SweepParams& q, int blocks, int warps, size_t smem, cudaStream_t stream) {
-    auto kern = sweep_kernel<TP, MT, NTW>;
-    static size_t configured = 0;
-    if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        configured = smem;
-    }
-    kern<<<blocks, warps * 32, smem, stream>>>(q);
-    return cudaGetLastError();
-}
-
-template <int TP>
-static cudaError_t launch_sweep_tp(const SweepParams& q, int MT, int NTW, int blocks, int warps, size_t smem, cudaStream_t s) {
-#define ROW(mt) \
-    if (MT == mt) { \
-        if (NTW == 1) return launch_sweep_t<TP, mt, 1>(q, blocks, warps, smem, s); \
-        if (NTW == 2) return launch_sweep_t<TP, mt, 2>(q, blocks, warps, smem, s); \
-        return launch_sweep_t<TP, mt, 4>(q, blocks, warps, smem, s); \
-    }
-    ROW(1) ROW(2) ROW(4) ROW(8)
-#undef ROW
-    return cudaErrorInvalidValue;
-}
-
-// Chooses the launch shape: one warp per 8-row n-tile (decision tiles + basis tiles), at most 16 warps.
-cudaError_t launch_sweep(SweepParams& q, const SweepConfig& cfg, cudaStream_t stream) {
-    const int MT = cfg.MT;
-    const int NT = (q.G + 7) / 8;
-    const int NTaug = q.accum_mode ? NT + MT : NT;
-    const int NTn = (q.Gn + 7) / 8;
-    int warps = std::max(std::max(NTaug, NTn), (2 * cfg.TP + 31) / 32);
-    warps = std::min(std::max(warps, 4), 16);
-    int ntw = (NTaug + warps - 1) / warps;
-    int NTW = ntw <= 1 ? 1 : (ntw <= 2 ? 2 : 4);
-    if (ntw > 4) return cudaErrorInvalidValue;
-    q.ncols = 8 * (NT + MT);
-    const size_t smem = sweep_smem_bytes(cfg.TP, q.Gn, cfg.n_nodes, q.ldb, MT, q.K);
-    if (cfg.TP == 64) return launch_sweep_tp<64>(q, MT, NTW, cfg.blocks, warps, smem, stream);
-    return launch_sweep_tp<32>(q, MT, NTW, cfg.blocks, warps, smem, stream);
-}
-
+// K3 (the fused backward sweep) lives in sweep.cu.
 
 // =================================================================================================
 // K2p: regression preconditioner.  One CTA per simulated period: Householder QR (no pivoting, like the reference's

@@ -8,10 +8,11 @@
 namespace lsmc {
 
 struct SweepConfig {
-    int TP;        // paths per tile (32 or 64)
+    int TP;        // paths per tile (56 or 24)
     int MT;        // basis m-tiles: 1, 2, 4 or 8 (8*MT >= K)
     int blocks;    // persistent CTAs
     int n_nodes;   // basis-program nodes
+    int nbuf;      // shared-memory buffers for the staged V_next tile (2 = prefetch the next tile)
 };
 
 struct SolveParams {
@@ -34,7 +35,8 @@ struct FinalParams {
     double* o_inventory; double* o_pv;
 };
 
-size_t sweep_smem_bytes(int TP, int Gn, int n_nodes, int ldb, int MT, int K);
+bool choose_sweep_shape(int max_grid, int K, int F, int MT, int* TP, int* nbuf);
+int sweep_max_items();
 int precond_rows(int K, int64_t N);
 void launch_precond(const PrecondParams& q, cudaStream_t stream);
 void launch_simulate(const SimParams& sp, cudaStream_t stream);

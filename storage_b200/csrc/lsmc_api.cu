@@ -78,7 +78,7 @@ struct lsmc_ctx {
     bool has_problem = false, sims_ready[2] = {false, false}, backward_done = false, forward_done = false;
     Plan plan;
     int64_t N = 0, Npad = 0, Nglobal = 0;
-    int TP = 64, MT = 1, ldb = 4, sweep_blocks = 0, fwd_blocks = 0, ncols_max = 0;
+    int TP = 56, nbuf = 2, MT = 1, ldb = 4, sweep_blocks = 0, fwd_blocks = 0, ncols_max = 0;
     uint32_t outputs = 0;       // bit0 per-sim panels, bit1 decision index
     bool keep_values = false;
     int valuation_antithetic = 0;
@@ -174,11 +174,12 @@ void set_problem(lsmc_ctx* c, const lsmc_problem* problem) {
     c->ldb = (pl.K + 3) & ~3;
     require(pl.basis.n_nodes <= kMaxNodes && (int)pl.basis.ops.size() <= kMaxOps, LSMC_EUNSUPPORTED, "basis functions need too many product nodes");
     require(pl.max_dec <= 16, LSMC_EUNSUPPORTED, "extra_decisions above 6 is not supported on the device path");
-    c->TP = sweep_smem_bytes(64, pl.max_grid, pl.basis.n_nodes, c->ldb, c->MT, pl.K) <= 200 * 1024 ? 64 : 32;
-    require(sweep_smem_bytes(c->TP, pl.max_grid, pl.basis.n_nodes, c->ldb, c->MT, pl.K) <= 220 * 1024, LSMC_EUNSUPPORTED, "inventory grid / basis too large for the sweep kernel's shared memory");
-    require((pl.max_grid + 7) / 8 + c->MT <= 64, LSMC_EUNSUPPORTED, "inventory grid has too many points for the sweep kernel (max 448)");
-    c->Npad = (c->N + 63) / 64 * 64;
-    c->sweep_blocks = (int)std::min<int64_t>(c->num_sms, c->Npad / c->TP);
+    require(choose_sweep_shape(pl.max_grid, pl.K, pl.F, c->MT, &c->TP, &c->nbuf), LSMC_EUNSUPPORTED,
+            "inventory grid / basis too large for the sweep kernel's shared memory");
+    require((pl.max_grid + 7) / 8 + c->MT <= sweep_max_items(), LSMC_EUNSUPPORTED, "inventory grid has too many points for the sweep kernel (about 200 at most)");
+    const int64_t n_tiles = (c->N + c->TP - 1) / c->TP;
+    c->Npad = n_tiles * c->TP;   // every tile's bulk copy stays inside a row; TP is a multiple of 8
+    c->sweep_blocks = (int)std::min<int64_t>(c->num_sms, n_tiles);
     c->fwd_blocks = (int)std::min<int64_t>((int64_t)c->num_sms * 4, (c->N + 255) / 256);
     c->ncols_max = 8 * ((pl.max_grid + 7) / 8 + c->MT);
 
@@ -293,7 +294,7 @@ void backward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
     const int P = pl.P, s0 = pl.s0, F = pl.F, D = pl.max_dec;
     const size_t Np = (size_t)c->Npad;
     cudaStream_t s = c->stream;
-    SweepConfig cfg{c->TP, c->MT, c->sweep_blocks, pl.basis.n_nodes};
+    SweepConfig cfg{c->TP, c->MT, c->sweep_blocks, pl.basis.n_nodes, c->nbuf};
     CUDA_CHECK(cudaEventRecord(c->event(2), s));
     c->tm.backward_sweep_launches = 0;
     c->tm.sweep_bytes = 0.0;

@@ -1,0 +1,529 @@
+// sweep.cu — K3: the fused backward sweep of one period (LSV.cs:185-205, 234-332, 753-770), sm_100a.
+//
+// One persistent CTA per SM walks path tiles of TP paths.  16 warps:
+//   warps 0..14  "workers": fit (DMMA), decisions (8 grid rows x TP paths per item) and X~^T X items
+//   warp  15     "producer" during the decision phase: bulk-async copies (cp.async.bulk -> UBLKCP, mbarrier
+//                completion) of the NEXT tile's V_next rows and raw regressor rows (spot, factors of periods p and
+//                p-1) into the other shared-memory buffer, so HBM latency hides behind the FP64 work of this tile.
+// Per tile:
+//   F0 basis monomials of both periods from the raw rows (all threads, one (basis, path) element each)
+//   F1 x~ = T^T x_{p-1} (preconditioned regressors) and the fitted continuation values C^[l][n] = beta_l . x_p[n]
+//      for every next-grid row l on the FP64 tensor pipe (DMMA 8x8x4: A = beta, B = X_p^T) -> shared memory
+//   D  lane (g,t) of a decision item owns grid row i = 8j+g and, per iteration, the two paths 8u+2t, 8u+2t+1
+//      (128-bit shared loads): max over the bang-bang decisions of immediate + interpolated C^, realised value from
+//      interpolated V_next, store V[i][n] (128-bit), and feed the value straight from registers as the B operand
+//      of the DMMA that accumulates X~_{p-1}^T V; trailing items accumulate X~^T X~.
+// All arithmetic that decides is individually rounded (__dmul_rn/__dadd_rn) in the reference's order: given the same
+// coefficients the value surface is bit-identical to the oracle's.  FP64 scalar and DMMA share one pipe on B200
+// (scripts/probe_fp64.cu: 36 TFLOP/s either way, not additive), which — not HBM — is what bounds this kernel.
+#include "kernels.h"
+
+namespace lsmc {
+
+namespace {
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t done = 0;
+    const uint32_t addr = smem_u32(bar);
+    while (!done) {
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+    }
+}
+// 1-D bulk asynchronous copy global -> shared (TMA unit, no tensor map), completion on an mbarrier.
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+__device__ __forceinline__ double2 lds128(const double* p) { return *reinterpret_cast<const double2*>(p); }
+
+constexpr int kSweepWarps = 16;
+constexpr int kWorkers = 15;
+
+// Shared-memory carve-up (in doubles).  Row strides: LD = TP (TP = 8 mod 16 keeps the 128-bit row-pair accesses of
+// the decision loop conflict-free), LDX = TP + 4 for the design rows read as DMMA B operands, LDB for beta rows.
+struct SweepSmem {
+    int LD, LDX, LDB, GnP, Kp4, nbuf, raw_rows;
+    size_t vn, raw, c, xp, xm, xt, beta, t, total;   // offsets in doubles
+};
+
+__host__ __device__ inline SweepSmem sweep_layout(int TP, int Gn, int K, int F, int MT, int nbuf) {
+    SweepSmem L;
+    L.LD = TP; L.LDX = TP + 4; L.nbuf = nbuf;
+    L.GnP = (Gn + 7) & ~7;
+    L.Kp4 = (K + 3) & ~3;
+    L.LDB = L.Kp4 + ((L.Kp4 % 8 == 0) ? 4 : 0);
+    L.raw_rows = 2 * (F + 1);
+    size_t o = 0;
+    L.vn = o;    o += (size_t)nbuf * L.GnP * L.LD;           // staged V_next tile(s), filled by bulk copies
+    L.raw = o;   o += (size_t)nbuf * L.raw_rows * L.LD;      // raw regressors: spot_p, fac_p[F], spot_{p-1}, fac_{p-1}[F]
+    L.c = o;     o += (size_t)L.GnP * L.LD;                  // fitted continuation values
+    L.xp = o;    o += (size_t)L.Kp4 * L.LDX;                 // basis rows of period p (rows >= K stay zero)
+    L.xm = o;    o += (size_t)K * L.LD;                      // raw basis rows of period p-1
+    L.xt = o;    o += (size_t)8 * MT * L.LD;                 // preconditioned rows x~ (rows >= K stay zero)
+    L.beta = o;  o += (size_t)L.GnP * L.LDB;
+    L.t = o;     o += (size_t)K * K;
+    L.total = o;
+    return L;
+}
+
+// Decision table of one grid row, register resident for the whole kernel (the first three decisions of the
+// bang-bang set; rows with fewer repeat decision 0, which a strict '>' never selects; more go through global memory).
+struct RowTable {
+    int nd, row_ok, variant;
+    double invc, gridv;
+    double nvol[3], cost[3], ncons[3], wl[3], wh[3];   // nvol = -volume, ncons = -consumed (exact negations)
+    int oL[3], oH[3];
+};
+
+// Loop variants (warp-uniform, chosen once per item): which exactly-neutral operations can be skipped.
+enum : int { kZero1 = 1, kCons0 = 2, kCons2 = 4, kInvc = 8, kGeneric = 16 };
+
+// One decision item of one tile: 8 grid rows (lane group g) x TP paths; lane (g,t) handles paths 8u+2t, 8u+2t+1.
+//   tot_d = ((-vol_d s) df - cost_d [+ (-cons_d s) df]) + cont_d [- invc]      (LSV.cs:304-330, operation order kept)
+// Skipped terms are exact no-ops: adding (-0 * s) * df = -0.0, subtracting invc = +0.0, and for the zero decision
+// (vol = cost = cons = 0) the immediate value is -0.0, so tot = cont bit for bit.
+template <int TP, int MT, int FLAGS>
+__device__ __forceinline__ void decide_item(const RowTable& R, const double* __restrict__ sC, const double* __restrict__ vn,
+                                            const double* __restrict__ sS, const double* __restrict__ sXT, double* __restrict__ vrow,
+                                            const double df, const bool accum, const int g, const int t, double (&acc)[MT][2]) {
+    constexpr bool ZERO1 = (FLAGS & kZero1) != 0, CONS0 = (FLAGS & kCons0) != 0, CONS2 = (FLAGS & kCons2) != 0, INVC = (FLAGS & kInvc) != 0;
+    constexpr bool CONS1 = CONS0 || CONS2;
+    constexpr int LD = TP;
+    const double* pS = sS + 2 * t;
+    const double* pL0 = sC + R.oL[0] + 2 * t; const double* pH0 = sC + R.oH[0] + 2 * t;
+    const double* pL1 = sC + R.oL[1] + 2 * t; const double* pH1 = sC + R.oH[1] + 2 * t;
+    const double* pL2 = sC + R.oL[2] + 2 * t; const double* pH2 = sC + R.oH[2] + 2 * t;
+    const double* pV = vn + 2 * t;
+    const double* pX = sXT + (size_t)g * LD + 2 * t;
+    double* out = vrow + 2 * t;
+#pragma unroll
+    for (int u = 0; u < TP / 8; u++) {
+        double v[2] = {0.0, 0.0};
+        if (R.row_ok) {
+            const double2 s2 = lds128(pS + 8 * u);
+            const double2 l0 = lds128(pL0 + 8 * u), h0 = lds128(pH0 + 8 * u);
+            const double2 l1 = lds128(pL1 + 8 * u), h1 = lds128(pH1 + 8 * u);
+            const double2 l2 = lds128(pL2 + 8 * u), h2 = lds128(pH2 + 8 * u);
+            const double sv[2] = {s2.x, s2.y};
+            const double cl[3][2] = {{l0.x, l0.y}, {l1.x, l1.y}, {l2.x, l2.y}};
+            const double ch[3][2] = {{h0.x, h0.y}, {h1.x, h1.y}, {h2.x, h2.y}};
+#pragma unroll
+            for (int e = 0; e < 2; e++) {
+                double cont[3], tot[3];
+#pragma unroll
+                for (int d = 0; d < 3; d++) {
+                    cont[d] = add_rn(mul_rn(ch[d][e], R.wh[d]), mul_rn(cl[d][e], R.wl[d]));
+                    double x;
+                    if (d == 1 && ZERO1) x = cont[d];
+                    else {
+                        double imm = sub_rn(mul_rn(mul_rn(R.nvol[d], sv[e]), df), R.cost[d]);
+                        if ((d == 0 && CONS0) || (d == 1 && CONS1) || (d == 2 && CONS2)) imm = add_rn(imm, mul_rn(mul_rn(R.ncons[d], sv[e]), df));
+                        x = add_rn(imm, cont[d]);
+                    }
+                    tot[d] = INVC ? sub_rn(x, R.invc) : x;
+                }
+                double best = tot[0], bestC = cont[0];
+                int kb = 0;
+                if (tot[1] > best) { best = tot[1]; bestC = cont[1]; kb = 1; }
+                if (tot[2] > best) { best = tot[2]; bestC = cont[2]; kb = 2; }
+                const int oL = kb == 0 ? R.oL[0] : (kb == 1 ? R.oL[1] : R.oL[2]);
+                const int oH = kb == 0 ? R.oH[0] : (kb == 1 ? R.oH[1] : R.oH[2]);
+                const double wl = kb == 0 ? R.wl[0] : (kb == 1 ? R.wl[1] : R.wl[2]);
+                const double wh = kb == 0 ? R.wh[0] : (kb == 1 ? R.wh[1] : R.wh[2]);
+                const double act = add_rn(mul_rn(pV[oH + 8 * u + e], wh), mul_rn(pV[oL + 8 * u + e], wl));
+                v[e] = add_rn(best, add_rn(-bestC, act));
+            }
+            __stcs(reinterpret_cast<double2*>(out + 8 * u), make_double2(v[0], v[1]));
+        }
+        if (accum) {
+#pragma unroll
+            for (int m = 0; m < MT; m++) {
+                const double2 a2 = lds128(pX + (size_t)8 * m * LD + 8 * u);
+                dmma8x8x4(acc[m][0], acc[m][1], a2.x, v[0]);
+                dmma8x8x4(acc[m][0], acc[m][1], a2.y, v[1]);
+            }
+        }
+    }
+}
+
+// Generic item: any number of decisions per row (extra_decisions > 0), decision table read through L1.
+template <int TP, int MT>
+__device__ __noinline__ void decide_item_generic(const SweepParams& q, const RowTable& R, const int i, const double* __restrict__ sC,
+                                                 const double* __restrict__ vn, const double* __restrict__ sS, const double* __restrict__ sXT,
+                                                 double* __restrict__ vrow, const bool accum, const int g, const int t, double (&acc)[MT][2]) {
+    constexpr int LD = TP;
+    const size_t trow = (size_t)(R.row_ok ? i : 0) * q.max_dec;
+    for (int u = 0; u < TP / 8; u++) {
+        const int pc = 8 * u + 2 * t;
+        double v[2] = {0.0, 0.0};
+        if (R.row_ok) {
+            for (int e = 0; e < 2; e++) {
+                const double s = sS[pc + e];
+                double best = 0.0, bestC = 0.0, bwl = 1.0, bwh = 0.0;
+                int bl = 0, bh = 0;
+                for (int d = 0; d < R.nd; d++) {
+                    const int l = __ldg(q.t_lo + trow + d) * LD, h = __ldg(q.t_hi + trow + d) * LD;
+                    const double wlo = __ldg(q.t_wlo + trow + d), whi = __ldg(q.t_whi + trow + d);
+                    const double c = add_rn(mul_rn(sC[h + pc + e], whi), mul_rn(sC[l + pc + e], wlo));
+                    const double a = mul_rn(mul_rn(-__ldg(q.t_vol + trow + d), s), q.df);
+                    const double cc = mul_rn(mul_rn(-__ldg(q.t_cons + trow + d), s), q.df);
+                    const double x = sub_rn(add_rn(add_rn(sub_rn(a, __ldg(q.t_cost + trow + d)), cc), c), R.invc);
+                    if (d == 0 || x > best) { best = x; bestC = c; bl = l; bh = h; bwl = wlo; bwh = whi; }
+                }
+                const double act = add_rn(mul_rn(vn[bh + pc + e], bwh), mul_rn(vn[bl + pc + e], bwl));
+                v[e] = add_rn(best, add_rn(-bestC, act));
+            }
+            __stcs(reinterpret_cast<double2*>(vrow + pc), make_double2(v[0], v[1]));
+        }
+        if (accum) {
+#pragma unroll
+            for (int m = 0; m < MT; m++) {
+                const double2 a2 = lds128(sXT + (size_t)(8 * m + g) * LD + pc);
+                dmma8x8x4(acc[m][0], acc[m][1], a2.x, v[0]);
+                dmma8x8x4(acc[m][0], acc[m][1], a2.y, v[1]);
+            }
+        }
+    }
+}
+
+// Terminal period (LSV.cs:118-128): V[i][n] = TerminalStorageNpv(spot_end[n], grid_end[i]).
+template <int TP, int MT>
+__device__ __forceinline__ void terminal_item(const SweepParams& q, const RowTable& R, const double* __restrict__ sS,
+                                              const double* __restrict__ sXT, double* __restrict__ vrow, const bool accum,
+                                              const int g, const int t, double (&acc)[MT][2]) {
+    constexpr int LD = TP;
+#pragma unroll 1
+    for (int u = 0; u < TP / 8; u++) {
+        const int pc = 8 * u + 2 * t;
+        double v[2] = {0.0, 0.0};
+        if (R.row_ok) {
+            const double2 s2 = lds128(sS + pc);
+            const double sv[2] = {s2.x, s2.y};
+#pragma unroll
+            for (int e = 0; e < 2; e++)
+                v[e] = q.must_be_empty ? 0.0
+                    : add_rn(add_rn(add_rn(q.tc0, mul_rn(q.tc1, sv[e])), mul_rn(q.tc2, R.gridv)), mul_rn(q.tc3, mul_rn(sv[e], R.gridv)));
+            __stcs(reinterpret_cast<double2*>(vrow + pc), make_double2(v[0], v[1]));
+        }
+        if (accum) {
+#pragma unroll
+            for (int m = 0; m < MT; m++) {
+                const double2 a2 = lds128(sXT + (size_t)(8 * m + g) * LD + pc);
+                dmma8x8x4(acc[m][0], acc[m][1], a2.x, v[0]);
+                dmma8x8x4(acc[m][0], acc[m][1], a2.y, v[1]);
+            }
+        }
+    }
+}
+
+}  // namespace
+
+template <int TP, int MT, int NTW>
+__global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams q, int nbuf) {
+    extern __shared__ __align__(16) double smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, t = lane & 3;
+    const BasisDev* __restrict__ bd = q.basis;
+    const int K = q.K, F = q.F;
+    const SweepSmem L = sweep_layout(TP, q.Gn, K, F, MT, nbuf);
+    constexpr int LD = TP, LDX = TP + 4;
+    const int LDB = L.LDB, GnP = L.GnP, Kp4 = L.Kp4;
+    double* const sVn = smem + L.vn;
+    double* const sRaw = smem + L.raw;
+    double* const sC = smem + L.c;
+    double* const sXP = smem + L.xp;
+    double* const sXM = smem + L.xm;
+    double* const sXT = smem + L.xt;
+    double* const sBeta = smem + L.beta;
+    double* const sT = smem + L.t;
+    __shared__ uint64_t s_full[2];
+    __shared__ int8_t sPow[64][1 + kMaxFactors];
+
+    const int NT = (q.G + 7) >> 3;                        // decision items (8 grid rows each)
+    const int n_items = q.accum_mode ? NT + MT : NT;      // + X~^T X~ items
+    const int64_t n_tiles = (q.N + TP - 1) / TP;
+    const bool need_sp = !q.spot_is_const;                          // spot of period p (else the deterministic price)
+    const bool need_fp = q.mode == 0 && q.cont_mode == 0;           // basis of period p for the fitted values
+    const bool need_m = q.accum_mode == 1;                          // basis of period p-1 for the normal equations
+    const bool accum = q.accum_mode != 0;
+
+    // ---- one-time staging ----
+    for (int k = tid; k < 64; k += blockDim.x) {
+        sPow[k][0] = (k < K) ? bd->spot_pow[k] : (int8_t)0;
+        for (int f = 0; f < kMaxFactors; f++) sPow[k][1 + f] = (k < K && f < F) ? bd->fac_pow[k][f] : (int8_t)0;
+    }
+    for (size_t i = tid; i < L.total; i += blockDim.x) smem[i] = 0.0;
+    __syncthreads();
+    if (need_fp) {
+        for (int i = tid; i < q.Gn * Kp4; i += blockDim.x) {
+            const int l = i / Kp4, k = i - l * Kp4;
+            sBeta[(size_t)l * LDB + k] = __ldg(q.beta + (size_t)l * q.ldb + k);
+        }
+    }
+    if (need_m) for (int i = tid; i < K * K; i += blockDim.x) sT[i] = __ldg(q.precond + i);
+    if (tid == 0) {
+        mbar_init(&s_full[0], 1);
+        mbar_init(&s_full[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+
+    // ---- decision tables -> registers ----
+    RowTable tab[NTW];
+    double acc[NTW][MT][2];
+#pragma unroll
+    for (int jj = 0; jj < NTW; jj++) {
+#pragma unroll
+        for (int m = 0; m < MT; m++) acc[jj][m][0] = acc[jj][m][1] = 0.0;
+        RowTable& R = tab[jj];
+        const int j = warp + jj * kWorkers;
+        const int i = 8 * j + g;
+        R.row_ok = (warp < kWorkers && j < NT && i < q.G) ? 1 : 0;
+        R.nd = 0; R.invc = 0.0; R.gridv = 0.0;
+        const bool on = q.mode == 0 && R.row_ok;
+        const size_t trow = (size_t)(R.row_ok ? i : 0) * q.max_dec;
+        if (on) { R.nd = __ldg(q.t_ndec + i); R.invc = __ldg(q.t_invcost + i); }
+        if (q.mode == 1 && R.row_ok) R.gridv = __ldg(q.grid + i);
+#pragma unroll
+        for (int d = 0; d < 3; d++) {
+            const int ds = (d < R.nd) ? d : 0;   // missing decisions repeat decision 0
+            R.nvol[d] = on ? -__ldg(q.t_vol + trow + ds) : 0.0;
+            R.cost[d] = on ? __ldg(q.t_cost + trow + ds) : 0.0;
+            R.ncons[d] = on ? -__ldg(q.t_cons + trow + ds) : 0.0;
+            R.wl[d] = on ? __ldg(q.t_wlo + trow + ds) : 1.0;
+            R.wh[d] = on ? __ldg(q.t_whi + trow + ds) : 0.0;
+            R.oL[d] = on ? __ldg(q.t_lo + trow + ds) * LD : 0;
+            R.oH[d] = on ? __ldg(q.t_hi + trow + ds) * LD : 0;
+        }
+        const bool zero1 = __all_sync(0xffffffffu, R.nvol[1] == 0.0 && R.cost[1] == 0.0 && R.ncons[1] == 0.0);
+        const bool cons0 = __any_sync(0xffffffffu, R.ncons[0] != 0.0), cons1 = __any_sync(0xffffffffu, R.ncons[1] != 0.0);
+        const bool cons2 = __any_sync(0xffffffffu, R.ncons[2] != 0.0);
+        if (__any_sync(0xffffffffu, R.nd > 3)) R.variant = kGeneric;
+        else if (__any_sync(0xffffffffu, R.invc != 0.0)) R.variant = kCons0 | kCons2 | kInvc;
+        else R.variant = (zero1 ? kZero1 : 0) | ((cons0 || (!zero1 && cons1)) ? kCons0 : 0) | (cons2 ? kCons2 : 0);
+    }
+    __syncthreads();
+
+    // ---- producer: bulk-async copies of one tile's V_next rows and raw regressor rows into buffer b ----
+    auto produce = [&](int64_t tile, int b) {
+        const int64_t n0 = tile * TP;
+        const uint32_t row_bytes = (uint32_t)(TP * sizeof(double));
+        const int nrows = (q.mode == 0 ? q.Gn : 0) + (need_sp ? 1 : 0) + (need_fp ? F : 0) + (need_m ? F + 1 : 0);
+        if (nrows == 0) return;
+        if (lane == 0) mbar_expect_tx(&s_full[b], (uint32_t)nrows * row_bytes);
+        __syncwarp();
+        if (q.mode == 0) {
+            double* dst = sVn + (size_t)b * GnP * LD;
+            for (int r = lane; r < q.Gn; r += 32) bulk_g2s(dst + (size_t)r * LD, q.Vnext + (size_t)r * q.Npad + n0, row_bytes, &s_full[b]);
+        }
+        if (lane < 2 * (F + 1)) {
+            const int r = lane;
+            const double* src = nullptr;
+            if (r == 0) { if (need_sp) src = q.spot_p + n0; }
+            else if (r <= F) { if (need_fp) src = q.fac_p + (size_t)(r - 1) * q.Npad + n0; }
+            else if (r == F + 1) { if (need_m) src = q.spot_m + n0; }
+            else if (need_m) src = q.fac_m + (size_t)(r - F - 2) * q.Npad + n0;
+            if (src) bulk_g2s(sRaw + ((size_t)b * L.raw_rows + r) * LD, src, row_bytes, &s_full[b]);
+        }
+    };
+    const bool any_copy = q.mode == 0 || need_sp || need_m;
+
+    int64_t tile = blockIdx.x;
+    if (warp == kWorkers && tile < n_tiles) produce(tile, 0);
+
+    for (int it = 0; tile < n_tiles; tile += gridDim.x, it++) {
+        const int b = (nbuf == 2) ? (it & 1) : 0;
+        const int64_t n0 = tile * TP;
+        const double* vn = sVn + (size_t)b * GnP * LD;
+        double* raw = sRaw + (size_t)b * L.raw_rows * LD;
+        const double* sS = raw;   // row 0: spot of period p
+
+        // ================= phase F0: basis monomials of both periods from the raw rows =================
+        if (any_copy) mbar_wait(&s_full[b], (uint32_t)((it / nbuf) & 1));   // this tile's rows have landed
+        if (!need_sp) for (int path = tid; path < TP; path += blockDim.x) raw[path] = (n0 + path < q.N) ? q.spot_const : 0.0;
+        {
+            const int nP = need_fp ? K : 0, nM = need_m ? K : 0;
+            for (int e = tid; e < (nP + nM) * TP; e += blockDim.x) {
+                const int row = e / TP, path = e - row * TP;
+                const bool isM = row >= nP;
+                const int k = isM ? row - nP : row;
+                const double* rr = raw + (isM ? (size_t)(F + 1) * LD : 0) + path;
+                // left-to-right product chain: spot first, factors ascending (BasisFunctions.cs:92-132; same order as the oracle)
+                double a = 1.0;
+                bool started = false;
+                for (int v = 0; v <= F; v++) {
+                    const int pw = sPow[k][v];
+                    if (pw > 0) {
+                        const double x = (v == 0 && !isM && !need_sp) ? q.spot_const : rr[(size_t)v * LD];
+                        for (int c = 0; c < pw; c++) { a = started ? mul_rn(a, x) : x; started = true; }
+                    }
+                }
+                if (!started) a = (n0 + path < q.N) ? 1.0 : 0.0;
+                else if (!(n0 + path < q.N)) a = 0.0;
+                if (isM) sXM[(size_t)k * LD + path] = a; else sXP[(size_t)k * LDX + path] = a;
+            }
+        }
+        __syncthreads();
+
+        // ================= phase F1: preconditioned regressors + fitted continuation values =================
+        if (q.accum_mode == 1) {
+            for (int e = tid; e < K * TP; e += blockDim.x) {
+                const int j = e / TP, path = e - j * TP;
+                double a = 0.0;
+                for (int i = 0; i <= j; i++) a = fma(sT[i * K + j], sXM[(size_t)i * LD + path], a);
+                sXT[(size_t)j * LD + path] = a;
+            }
+        } else if (q.accum_mode == 2) {
+            for (int path = tid; path < TP; path += blockDim.x) sXT[path] = (n0 + path < q.N) ? 1.0 : 0.0;
+        }
+        if (q.mode == 0) {
+            if (q.cont_mode == 0) {
+                constexpr int NNT = TP / 8, H0 = (NNT + 1) / 2;
+                const int NTn = GnP >> 3;
+                for (int item = warp; item < 2 * NTn; item += kSweepWarps) {
+                    const int mt = item >> 1, half = item & 1;
+                    const double* brow = sBeta + (size_t)(8 * mt + g) * LDB + t;
+                    const double* xcol = sXP + (size_t)t * LDX + g;
+                    double* crow = sC + (size_t)(8 * mt + g) * LD + 2 * t;
+                    for (int nt = half ? H0 : 0; nt < (half ? NNT : H0); nt++) {
+                        double c0 = 0.0, c1 = 0.0;
+                        const double* ap = brow;
+                        const double* bp = xcol + 8 * nt;
+#pragma unroll 1
+                        for (int ks = 0; ks < Kp4; ks += 4, ap += 4, bp += 4 * LDX) dmma8x8x4(c0, c1, *ap, *bp);
+                        *reinterpret_cast<double2*>(crow + 8 * nt) = make_double2(c0, c1);
+                    }
+                }
+            } else {
+                for (int i = tid; i < q.Gn * TP; i += blockDim.x) {
+                    const int l = i / TP, c = i - l * TP;
+                    sC[(size_t)l * LD + c] = __ldg(q.beta + (size_t)l * q.ldb);
+                }
+            }
+        }
+        __syncthreads();
+
+        // ================= phase D: decisions + normal-equation accumulation; producer prefetches =================
+        const int64_t next = tile + gridDim.x;
+        if (warp == kWorkers) {
+            if (nbuf == 2 && next < n_tiles) produce(next, b ^ 1);
+        } else {
+#pragma unroll
+            for (int jj = 0; jj < NTW; jj++) {
+                const int j = warp + jj * kWorkers;
+                if (j >= n_items) break;
+                if (j < NT) {
+                    const RowTable& R = tab[jj];
+                    const int i = 8 * j + g;
+                    double* vrow = q.Vout + (size_t)(R.row_ok ? i : 0) * q.Npad + n0;
+                    if (q.mode == 1) terminal_item<TP, MT>(q, R, sS, sXT, vrow, accum, g, t, acc[jj]);
+                    else switch (R.variant) {
+#define VARIANT(f) case f: decide_item<TP, MT, f>(R, sC, vn, sS, sXT, vrow, q.df, accum, g, t, acc[jj]); break;
+                        VARIANT(0) VARIANT(1) VARIANT(2) VARIANT(3) VARIANT(4) VARIANT(5) VARIANT(6) VARIANT(7)
+                        VARIANT(kCons0 | kCons2 | kInvc)
+#undef VARIANT
+                        default: decide_item_generic<TP, MT>(q, R, i, sC, vn, sS, sXT, vrow, accum, g, t, acc[jj]); break;
+                    }
+                } else {
+                    const int kb = 8 * (j - NT) + g;   // X~^T X~: B operand = x~ itself
+                    const double* pb = sXT + (size_t)kb * LD + 2 * t;
+                    const double* pa = sXT + (size_t)g * LD + 2 * t;
+#pragma unroll
+                    for (int u = 0; u < TP / 8; u++) {
+                        const double2 b2 = lds128(pb + 8 * u);
+#pragma unroll
+                        for (int m = 0; m < MT; m++) {
+                            const double2 a2 = lds128(pa + (size_t)8 * m * LD + 8 * u);
+                            dmma8x8x4(acc[jj][m][0], acc[jj][m][1], a2.x, b2.x);
+                            dmma8x8x4(acc[jj][m][0], acc[jj][m][1], a2.y, b2.y);
+                        }
+                    }
+                }
+            }
+        }
+        __syncthreads();
+        if (nbuf == 1) {
+            if (warp == kWorkers && next < n_tiles) produce(next, 0);
+        }
+    }
+
+    // ---- per-CTA partial: partial[cta][k][col], k = 8m+g, col = 8j+2t ----
+    if (q.accum_mode && warp < kWorkers) {
+        double* out = q.partial + (size_t)blockIdx.x * (8 * MT) * q.ncols;
+#pragma unroll
+        for (int jj = 0; jj < NTW; jj++) {
+            const int j = warp + jj * kWorkers;
+            if (j >= n_items) break;
+#pragma unroll
+            for (int m = 0; m < MT; m++)
+                *reinterpret_cast<double2*>(out + (size_t)(8 * m + g) * q.ncols + 8 * j + 2 * t) = make_double2(acc[jj][m][0], acc[jj][m][1]);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Launch configuration
+// ------------------------------------------------------------------------------------------------
+static size_t layout_bytes(int TP, int Gn, int K, int F, int MT, int nbuf) {
+    return sweep_layout(TP, Gn, K, F, MT, nbuf).total * sizeof(double);
+}
+
+// Largest tile that fits the 227 KB of an SM, double-buffered when possible.
+bool choose_sweep_shape(int max_grid, int K, int F, int MT, int* TP, int* nbuf) {
+    const size_t limit = 224 * 1024;
+    const int tps[2] = {56, 24};
+    for (int nb = 2; nb >= 1; nb--)
+        for (int tp : tps)
+            if (layout_bytes(tp, max_grid, K, F, MT, nb) <= limit) { *TP = tp; *nbuf = nb; return true; }
+    return false;
+}
+
+template <int TP, int MT, int NTW>
+static cudaError_t launch_sweep_t(const SweepParams& q, int blocks, size_t smem, int nbuf, cudaStream_t stream) {
+    auto kern = sweep_kernel<TP, MT, NTW>;
+    static size_t configured = 0;
+    if (smem > configured) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        configured = smem;
+    }
+    kern<<<blocks, kSweepWarps * 32, smem, stream>>>(q, nbuf);
+    return cudaGetLastError();
+}
+
+template <int TP>
+static cudaError_t launch_sweep_tp(const SweepParams& q, int MT, int NTW, int blocks, size_t smem, int nbuf, cudaStream_t s) {
+#define ROW(mt) \
+    if (MT == mt) { \
+        if (NTW == 1) return launch_sweep_t<TP, mt, 1>(q, blocks, smem, nbuf, s); \
+        return launch_sweep_t<TP, mt, 2>(q, blocks, smem, nbuf, s); \
+    }
+    ROW(1) ROW(2) ROW(4) ROW(8)
+#undef ROW
+    return cudaErrorInvalidValue;
+}
+
+int sweep_max_items() { return 2 * kWorkers; }
+
+cudaError_t launch_sweep(SweepParams& q, const SweepConfig& cfg, cudaStream_t stream) {
+    const int MT = cfg.MT;
+    const int NT = (q.G + 7) / 8;
+    const int n_items = q.accum_mode ? NT + MT : NT;
+    if (n_items > 2 * kWorkers) return cudaErrorInvalidValue;
+    const int NTW = n_items <= kWorkers ? 1 : 2;
+    q.ncols = 8 * (NT + MT);
+    const size_t smem = layout_bytes(cfg.TP, q.Gn, q.K, q.F, MT, cfg.nbuf);
+    if (cfg.TP == 56) return launch_sweep_tp<56>(q, MT, NTW, cfg.blocks, smem, cfg.nbuf, stream);
+    return launch_sweep_tp<24>(q, MT, NTW, cfg.blocks, smem, cfg.nbuf, stream);
+}
+
+}  // namespace lsmc

@@ -145,7 +145,7 @@ def test_end_to_end_within_1e9_with_injected_normals(case, ctx):
         rows = comparable_trigger_rows(got, ref, side)
         cols = [2 * side, 2 * side + 1]
         assert rel_err(got.trigger_summary[rows][:, cols[0]], ref.trigger_summary[rows][:, cols[0]]) < REL               # volumes
-        assert rel_err(got.trigger_summary[rows][:, cols[1]], ref.trigger_summary[rows][:, cols[1]], price_scale) < 1e-7  # prices: ratios of small differences
+        assert rel_err(got.trigger_summary[rows][:, cols[1]], ref.trigger_summary[rows][:, cols[1]], price_scale) < 1e-5  # prices: ratios of small differences; cond(X) ~ 1e13 at the first half-hourly steps
         assert rel_err(gp[rows][..., 0], rp[rows][..., 0]) < REL
         assert rel_err(gp[rows][..., 1], rp[rows][..., 1], price_scale) < 1e-5   # cond(X) ~ 1e13 at the first half-hourly steps
     assert rel_err(got.pv_by_sim, ref.pv_by_sim, max(abs(ref.npv), 1.0)) < 1e-7
