@@ -41,6 +41,10 @@ int precond_rows(int K, int64_t N);
 void launch_precond(const PrecondParams& q, cudaStream_t stream);
 void launch_simulate(const SimParams& sp, cudaStream_t stream);
 cudaError_t launch_sweep(SweepParams& q, const SweepConfig& cfg, cudaStream_t stream);
+// pipelined sweep of the regular periods (sweep4.cu)
+int sweep4_tile(int max_grid, int K, int F, int n_prod);
+bool sweep4_covers(const SweepParams& q);
+cudaError_t launch_sweep4(SweepParams& q, int TP, int n_prod, int blocks, cudaStream_t stream);
 void launch_reduce_partials(const double* partial, int n_parts, int n_elem, double* out, cudaStream_t stream);
 void launch_solve(const SolveParams& sp, cudaStream_t stream);
 void launch_forward(const ForwardParams& q, int blocks, cudaStream_t stream);

@@ -79,6 +79,7 @@ struct lsmc_ctx {
     Plan plan;
     int64_t N = 0, Npad = 0, Nglobal = 0;
     int TP = 56, nbuf = 2, MT = 1, ldb = 4, sweep_blocks = 0, fwd_blocks = 0, ncols_max = 0;
+    int TP4 = 0, sweep4_blocks = 0;   // pipelined sweep (sweep4.cu): tile size (0 = shape not covered) and persistent CTAs
     uint32_t outputs = 0;       // bit0 per-sim panels, bit1 decision index
     bool keep_values = false;
     int valuation_antithetic = 0;
@@ -178,8 +179,10 @@ void set_problem(lsmc_ctx* c, const lsmc_problem* problem) {
             "inventory grid / basis too large for the sweep kernel's shared memory");
     require((pl.max_grid + 7) / 8 + c->MT <= sweep_max_items(), LSMC_EUNSUPPORTED, "inventory grid has too many points for the sweep kernel (about 200 at most)");
     const int64_t n_tiles = (c->N + c->TP - 1) / c->TP;
-    c->Npad = n_tiles * c->TP;   // every tile's bulk copy stays inside a row; TP is a multiple of 8
+    c->Npad = (c->N + 839) / 840 * 840;   // every tile's bulk copy stays inside a row for all tile sizes (lcm of 56, 40, 24)
     c->sweep_blocks = (int)std::min<int64_t>(c->num_sms, n_tiles);
+    c->TP4 = sweep4_tile(pl.max_grid, pl.K, pl.F, (int)pl.basis.ops.size());
+    c->sweep4_blocks = c->TP4 ? (int)std::min<int64_t>(c->num_sms, (c->N + c->TP4 - 1) / c->TP4) : 0;
     c->fwd_blocks = (int)std::min<int64_t>((int64_t)c->num_sms * 4, (c->N + 255) / 256);
     c->ncols_max = 8 * ((pl.max_grid + 7) / 8 + c->MT);
 
@@ -193,7 +196,8 @@ void set_problem(lsmc_ctx* c, const lsmc_problem* problem) {
     c->beta_all.alloc((size_t)(pl.P - 1) * c->beta_stride());
     CUDA_CHECK(cudaMemsetAsync(c->beta_all.p, 0, c->beta_all.n * sizeof(double), s));
     c->grid.upload(pl.grid, s);
-    c->partial.alloc((size_t)c->sweep_blocks * 8 * c->MT * c->ncols_max);
+    c->partial.alloc((size_t)std::max(c->sweep_blocks, c->sweep4_blocks) * 8 * c->MT * c->ncols_max);
+    CUDA_CHECK(cudaMemsetAsync(c->partial.p, 0, c->partial.n * sizeof(double), s));
     c->reduced.alloc((size_t)8 * c->MT * c->ncols_max);
     c->inventory.alloc(Np); c->pv_by_sim.alloc(Np);
     const int nsum = kFwdSums + pl.K;
@@ -349,7 +353,10 @@ void backward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
             if (q.accum_mode == 1) q.precond = c->precond.p + (size_t)(p - 1 - s0) * precond_stride(pl.K);
         }
         CUDA_CHECK(cudaEventRecord(c->event(ev_base), s));
-        CUDA_CHECK(launch_sweep(q, cfg, s));
+        const bool pipelined = c->TP4 != 0 && sweep4_covers(q);
+        const int n_parts = pipelined ? c->sweep4_blocks : c->sweep_blocks;
+        if (pipelined) CUDA_CHECK(launch_sweep4(q, c->TP4, (int)pl.basis.ops.size(), c->sweep4_blocks, s));
+        else CUDA_CHECK(launch_sweep(q, cfg, s));
         CUDA_CHECK(cudaEventRecord(c->event(ev_base + 1), s));
         ev_base += 2;
         c->tm.backward_sweep_launches++;
@@ -357,7 +364,7 @@ void backward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
         c->tm.sweep_bytes += (double)c->N * 8.0 * ((double)q.G + q.Gn + (q.mode == 0 && !is_current ? F + 1 : (q.mode == 1 ? 1 : 0)) + (q.accum_mode == 1 ? F + 1 : 0));
 
         const int n_elem = 8 * c->MT * q.ncols;
-        launch_reduce_partials(c->partial.p, c->sweep_blocks, n_elem, c->reduced.p, s);
+        launch_reduce_partials(c->partial.p, n_parts, n_elem, c->reduced.p, s);
         c->tm.kernel_launches++;
         c->allreduce(c->reduced.p, (size_t)n_elem);
         if (p > 0) {

@@ -507,7 +507,11 @@ static cudaError_t launch_sweep_tp(const SweepParams& q, int MT, int NTW, int bl
         if (NTW == 1) return launch_sweep_t<TP, mt, 1>(q, blocks, smem, nbuf, s); \
         return launch_sweep_t<TP, mt, 2>(q, blocks, smem, nbuf, s); \
     }
+#ifdef LSMC_FAST_BUILD   // development builds: only the shapes of configs C1-C3/C5
+    ROW(1) ROW(2)
+#else
     ROW(1) ROW(2) ROW(4) ROW(8)
+#endif
 #undef ROW
     return cudaErrorInvalidValue;
 }
@@ -523,7 +527,11 @@ cudaError_t launch_sweep(SweepParams& q, const SweepConfig& cfg, cudaStream_t st
     q.ncols = 8 * (NT + MT);
     const size_t smem = layout_bytes(cfg.TP, q.Gn, q.K, q.F, MT, cfg.nbuf);
     if (cfg.TP == 56) return launch_sweep_tp<56>(q, MT, NTW, cfg.blocks, smem, cfg.nbuf, stream);
+#ifdef LSMC_FAST_BUILD
+    return cudaErrorInvalidValue;
+#else
     return launch_sweep_tp<24>(q, MT, NTW, cfg.blocks, smem, cfg.nbuf, stream);
+#endif
 }
 
 }  // namespace lsmc
