@@ -10,7 +10,7 @@ import numpy as np
 from . import _abi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "liblsmc_b200.so")
+LIB_PATH = os.environ.get("LSMC_B200_LIB") or os.path.join(_HERE, "liblsmc_b200.so")   # override: development builds only
 
 EXPORTS = (
     "lsmc_version", "lsmc_create", "lsmc_destroy", "lsmc_last_error", "lsmc_comm_unique_id", "lsmc_comm_init",

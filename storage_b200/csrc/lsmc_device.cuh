@@ -76,7 +76,7 @@ __device__ __forceinline__ void philox_normal_pair(uint64_t seed, uint64_t draw,
 // FP64 tensor-core tile: D(8x8) += A(8x4, row) * B(4x8, col).  SASS: DMMA.8x8x4.
 // lane = 4*g + t:  A[g][t], B[t][g], D[g][2t], D[g][2t+1].
 __device__ __forceinline__ void dmma8x8x4(double& d0, double& d1, double a, double b) {
-    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+    asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
                  : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
 }
 

@@ -53,6 +53,10 @@ __device__ __forceinline__ void tma_2d(void* dst, const CUtensorMap* map, int c0
 __device__ __forceinline__ void aux_bar() { asm volatile("bar.sync 1, 96;" ::: "memory"); }
 __device__ __forceinline__ double2 lds128(const double* p) { return *reinterpret_cast<const double2*>(p); }
 
+#ifndef LSMC_ABLATE   // development only: timing ablations (results are wrong when != 0)
+#define LSMC_ABLATE 0
+#endif
+
 constexpr int kWarps = 16;
 constexpr int kDecWarps = 13;          // grid rows <= 104
 constexpr int kAuxWarps = 3;
@@ -64,7 +68,7 @@ __host__ __device__ inline size_t al128(size_t b) { return (b + 127) & ~(size_t)
 
 // Shared-memory carve-up in BYTES; every TMA destination is 128-byte aligned.
 struct Layout4 {
-    int GnP, MT, LDP;
+    int GnP, MT, LDP, VP;                                 // VP: pitch of the V_next tile (TP + 4: conflict-free 64-bit gathers)
     size_t o_sp, o_fp, o_sm, o_fm, stage;                 // raw stage: spot_p | fac_p[F] | spot_m | fac_m[F]
     size_t vn, c, raw, prod, xt, zero, ones, ones_last, total;
 };
@@ -74,11 +78,12 @@ __host__ __device__ inline Layout4 layout4(int TP, int Gn, int K, int F, int n_p
     L.GnP = (Gn + 7) & ~7;
     L.MT = (K + 7) >> 3;
     L.LDP = TP + 4;
+    L.VP = TP + 4;
     const size_t row = (size_t)TP * 8;
     L.o_sp = 0; L.o_fp = al128(row); L.o_sm = L.o_fp + al128(F * row); L.o_fm = L.o_sm + al128(row);
     L.stage = L.o_fm + al128(F * row);
     size_t o = 0;
-    L.vn = o;   o += al128((size_t)2 * L.GnP * row);
+    L.vn = o;   o += al128((size_t)2 * L.GnP * L.VP * 8);
     L.c = o;    o += al128((size_t)2 * L.GnP * row);
     L.raw = o;  o += kRawStages * L.stage;
     L.prod = o; o += al128((size_t)2 * (n_prod > 0 ? n_prod : 1) * L.LDP * 8);
@@ -98,7 +103,7 @@ struct RowTab {
     int row_ok, variant;
     double invc;
     double nvol[3], cost[3], ncons[3], wl[3], wh[3];   // nvol = -volume, ncons = -consumed (exact negations)
-    int oL[3], oH[3];                                  // element offsets of the interpolation rows inside a tile buffer
+    int rL[3], rH[3];                                  // interpolation rows of the next grid
 };
 
 enum : int { kZero1 = 1, kCons0 = 2, kCons2 = 4, kInvc = 8, kGeneric = 16 };
@@ -113,9 +118,10 @@ __device__ __forceinline__ void decide_tile(const RowTab& R, const double* __res
     constexpr bool ZERO1 = (FLAGS & kZero1) != 0, CONS0 = (FLAGS & kCons0) != 0, CONS2 = (FLAGS & kCons2) != 0, INVC = (FLAGS & kInvc) != 0;
     constexpr bool CONS1 = CONS0 || CONS2;
     const double* pS = sS + 2 * t;
-    const double* pL0 = sC + R.oL[0] + 2 * t; const double* pH0 = sC + R.oH[0] + 2 * t;
-    const double* pL1 = sC + R.oL[1] + 2 * t; const double* pH1 = sC + R.oH[1] + 2 * t;
-    const double* pL2 = sC + R.oL[2] + 2 * t; const double* pH2 = sC + R.oH[2] + 2 * t;
+    constexpr int VP = TP + 4;
+    const double* pL0 = sC + R.rL[0] * TP + 2 * t; const double* pH0 = sC + R.rH[0] * TP + 2 * t;
+    const double* pL1 = sC + R.rL[1] * TP + 2 * t; const double* pH1 = sC + R.rH[1] * TP + 2 * t;
+    const double* pL2 = sC + R.rL[2] * TP + 2 * t; const double* pH2 = sC + R.rH[2] * TP + 2 * t;
     const double* pV = sV + 2 * t;
     const double* pXd = sXT + (size_t)g * TP + 2 * t;            // DMMA A operand: x~[8m+g][.]
     const double* pXs = sXT + (size_t)(8 * MTD) * TP + 2 * t;    // scalar remainder rows x~[8 MTD + r][.]
@@ -147,25 +153,39 @@ __device__ __forceinline__ void decide_tile(const RowTab& R, const double* __res
             const bool a1 = x0[1] > x0[0], b1 = x1[1] > x1[0];
             double best0 = a1 ? x0[1] : x0[0], best1 = b1 ? x1[1] : x1[0];
             double bc0 = a1 ? c0[1] : c0[0], bc1 = b1 ? c1[1] : c1[0];
-            int oL0 = a1 ? R.oL[1] : R.oL[0], oL1 = b1 ? R.oL[1] : R.oL[0];
-            int oH0 = a1 ? R.oH[1] : R.oH[0], oH1 = b1 ? R.oH[1] : R.oH[0];
+            int oL0 = a1 ? R.rL[1] : R.rL[0], oL1 = b1 ? R.rL[1] : R.rL[0];
+            int oH0 = a1 ? R.rH[1] : R.rH[0], oH1 = b1 ? R.rH[1] : R.rH[0];
             double wl0 = a1 ? R.wl[1] : R.wl[0], wl1 = b1 ? R.wl[1] : R.wl[0];
             double wh0 = a1 ? R.wh[1] : R.wh[0], wh1 = b1 ? R.wh[1] : R.wh[0];
             const bool a2 = x0[2] > best0, b2 = x1[2] > best1;
             best0 = a2 ? x0[2] : best0; best1 = b2 ? x1[2] : best1;
             bc0 = a2 ? c0[2] : bc0; bc1 = b2 ? c1[2] : bc1;
-            oL0 = a2 ? R.oL[2] : oL0; oL1 = b2 ? R.oL[2] : oL1;
-            oH0 = a2 ? R.oH[2] : oH0; oH1 = b2 ? R.oH[2] : oH1;
+            oL0 = a2 ? R.rL[2] : oL0; oL1 = b2 ? R.rL[2] : oL1;
+            oH0 = a2 ? R.rH[2] : oH0; oH1 = b2 ? R.rH[2] : oH1;
             wl0 = a2 ? R.wl[2] : wl0; wl1 = b2 ? R.wl[2] : wl1;
             wh0 = a2 ? R.wh[2] : wh0; wh1 = b2 ? R.wh[2] : wh1;
-            const double act0 = add_rn(mul_rn(pV[oH0 + u8], wh0), mul_rn(pV[oL0 + u8], wl0));
-            const double act1 = add_rn(mul_rn(pV[oH1 + u8 + 1], wh1), mul_rn(pV[oL1 + u8 + 1], wl1));
+#if LSMC_ABLATE == 1
+            oL0 = oL1 = R.rL[0]; oH0 = oH1 = R.rH[0]; wl0 = wl1 = R.wl[0]; wh0 = wh1 = R.wh[0];
+#endif
+#if LSMC_ABLATE == 2
+            const double act0 = best0, act1 = best1;
+#else
+            const double act0 = add_rn(mul_rn(pV[oH0 * VP + u8], wh0), mul_rn(pV[oL0 * VP + u8], wl0));
+            const double act1 = add_rn(mul_rn(pV[oH1 * VP + u8 + 1], wh1), mul_rn(pV[oL1 * VP + u8 + 1], wl1));
+#endif
             v0 = add_rn(best0, add_rn(-bc0, act0));
             v1 = add_rn(best1, add_rn(-bc1, act1));
             // lanes of rows beyond the grid compute on row 0 (valid memory, finite values) and contribute zeros
+#if LSMC_ABLATE == 4
+            if (v0 == 1.2345e300) __stcs(reinterpret_cast<double2*>(out + 2 * t + u8), make_double2(v0, v1));
+#else
             if (R.row_ok) __stcs(reinterpret_cast<double2*>(out + 2 * t + u8), make_double2(v0, v1));
             else { v0 = 0.0; v1 = 0.0; }
+#endif
         }
+#if LSMC_ABLATE == 3
+        accS[0] += v0 + v1;
+#else
 #pragma unroll
         for (int m = 0; m < MTD; m++) {
             const double2 a2 = lds128(pXd + (size_t)8 * m * TP + u8);
@@ -178,6 +198,7 @@ __device__ __forceinline__ void decide_tile(const RowTab& R, const double* __res
             accS[r] = fma(a2.x, v0, accS[r]);
             accS[r] = fma(a2.y, v1, accS[r]);
         }
+#endif
     }
 }
 
@@ -253,8 +274,8 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
                 R.ncons[d] = on ? -__ldg(q.t_cons + trow + ds) : 0.0;
                 R.wl[d] = on ? __ldg(q.t_wlo + trow + ds) : 1.0;
                 R.wh[d] = on ? __ldg(q.t_whi + trow + ds) : 0.0;
-                R.oL[d] = on ? __ldg(q.t_lo + trow + ds) * TP : 0;
-                R.oH[d] = on ? __ldg(q.t_hi + trow + ds) * TP : 0;
+                R.rL[d] = on ? __ldg(q.t_lo + trow + ds) : 0;
+                R.rH[d] = on ? __ldg(q.t_hi + trow + ds) : 0;
             }
             const bool zero1 = __all_sync(0xffffffffu, R.nvol[1] == 0.0 && R.cost[1] == 0.0 && R.ncons[1] == 0.0);
             const bool cons0 = __any_sync(0xffffffffu, R.ncons[0] != 0.0), cons1 = __any_sync(0xffffffffu, R.ncons[1] != 0.0);
@@ -279,16 +300,18 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
             mbar_wait(&rfull[stage], (uint32_t)sphase);   // spot row (landed long ago; makes the async-proxy writes visible here)
             mbar_wait(&vfull[b], par);                    // V_next tile
             const double* sC = reinterpret_cast<const double*>(sm + L.c) + (size_t)b * GnP * TP;
-            const double* sV = reinterpret_cast<const double*>(sm + L.vn) + (size_t)b * GnP * TP;
+            const double* sV = reinterpret_cast<const double*>(sm + L.vn) + (size_t)b * GnP * (TP + 4);
             const double* sS = reinterpret_cast<const double*>(sm + L.raw + (size_t)stage * L.stage + L.o_sp);
             const double* sX = reinterpret_cast<const double*>(sm + L.xt) + (size_t)b * 8 * MT * TP;
             double* out = vrow + tile * TP;
+#if LSMC_ABLATE != 5
             switch (R.variant) {
 #define VARIANT(f) case f: decide_tile<TP, MTD, KS, f>(R, sC, sV, sS, sX, out, q.df, g, t, acc, accS); break;
                 VARIANT(0) VARIANT(1) VARIANT(2) VARIANT(3) VARIANT(4) VARIANT(5) VARIANT(6) VARIANT(7)
                 default: decide_tile<TP, MTD, KS, kCons0 | kCons2 | kInvc>(R, sC, sV, sS, sX, out, q.df, g, t, acc, accS); break;
 #undef VARIANT
             }
+#endif
             mbar_arrive(&dfree[b]);
             if (++stage == kRawStages) { stage = 0; sphase ^= 1; }
         }
@@ -331,7 +354,7 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
         }
         // warp 13: T^T fragments (A[g][t] = T[4 ks + t][8 m + g]) and the Gram accumulators
         double tfrag[MT][KSTEPS];
-        double xacc[MT][MT][2];
+        double xacc[2][MT][MT][2];   // two sets (even / odd iterations) halve the dependent DMMA chains
 #pragma unroll
         for (int m = 0; m < MT; m++) {
 #pragma unroll
@@ -340,13 +363,13 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
                 tfrag[m][ks] = (aw == 0 && i2 < K && j2 < K) ? __ldg(q.precond + (size_t)i2 * K + j2) : 0.0;
             }
 #pragma unroll
-            for (int n = 0; n < MT; n++) xacc[m][n][0] = xacc[m][n][1] = 0.0;
+            for (int n = 0; n < MT; n++) xacc[0][m][n][0] = xacc[0][m][n][1] = xacc[1][m][n][0] = xacc[1][m][n][1] = 0.0;
         }
 
-        const uint32_t vn_bytes = (uint32_t)((size_t)q.Gn * ROW), raw_bytes = (uint32_t)(2 * (F + 1) * ROW);
+        const uint32_t vn_bytes = (uint32_t)((size_t)q.Gn * (TP + 4) * 8), raw_bytes = (uint32_t)(2 * (F + 1) * ROW);
         auto produce_vn = [&](int64_t tile, int b) {
             mbar_expect_tx(&vfull[b], vn_bytes);
-            tma_2d(sm + L.vn + (size_t)b * GnP * ROW, &mapV, (int)(tile * TP), 0, &vfull[b]);
+            tma_2d(sm + L.vn + (size_t)b * GnP * (TP + 4) * 8, &mapV, (int)(tile * TP), 0, &vfull[b]);
         };
         auto produce_raw = [&](int64_t tile, int s) {
             unsigned char* st = sm + L.raw + (size_t)s * L.stage;
@@ -395,6 +418,7 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
             aux_bar();
 
             double* sC = reinterpret_cast<double*>(sm + L.c) + (size_t)b * GnP * TP;
+#if LSMC_ABLATE != 6
             if (aw == 0) {
                 // ---- x~ = T^T x_{p-1} on the tensor pipe, then X~^T X~ ----
                 double* xt = reinterpret_cast<double*>(sm + L.xt) + (size_t)b * 8 * MT * TP;
@@ -403,16 +427,18 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
                 for (int ks = 0; ks < KSTEPS; ks++) pm[ks] = resolve(descM[ks]) + g;
 #pragma unroll
                 for (int nt = 0; nt < TP / 8; nt++) {
-                    double bop[KSTEPS];
+                    double bop[KSTEPS], cx[MT][2];
 #pragma unroll
                     for (int ks = 0; ks < KSTEPS; ks++) bop[ks] = pm[ks][8 * nt];
 #pragma unroll
-                    for (int m = 0; m < MT; m++) {
-                        double c0 = 0.0, c1 = 0.0;
+                    for (int m = 0; m < MT; m++) cx[m][0] = cx[m][1] = 0.0;
 #pragma unroll
-                        for (int ks = 0; ks < KSTEPS; ks++) dmma8x8x4(c0, c1, tfrag[m][ks], bop[ks]);
-                        *reinterpret_cast<double2*>(xt + (size_t)(8 * m + g) * TP + 8 * nt + 2 * t) = make_double2(c0, c1);
-                    }
+                    for (int ks = 0; ks < KSTEPS; ks++)
+#pragma unroll
+                        for (int m = 0; m < MT; m++) dmma8x8x4(cx[m][0], cx[m][1], tfrag[m][ks], bop[ks]);
+#pragma unroll
+                    for (int m = 0; m < MT; m++)
+                        *reinterpret_cast<double2*>(xt + (size_t)(8 * m + g) * TP + 8 * nt + 2 * t) = make_double2(cx[m][0], cx[m][1]);
                 }
                 __syncwarp();
                 const double* px = xt + (size_t)g * TP + 2 * t;
@@ -425,33 +451,45 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
                     for (int m = 0; m < MT; m++)
 #pragma unroll
                         for (int n = 0; n < MT; n++) {
-                            dmma8x8x4(xacc[m][n][0], xacc[m][n][1], f2[m].x, f2[n].x);
-                            dmma8x8x4(xacc[m][n][0], xacc[m][n][1], f2[m].y, f2[n].y);
+                            dmma8x8x4(xacc[0][m][n][0], xacc[0][m][n][1], f2[m].x, f2[n].x);
+                            dmma8x8x4(xacc[1][m][n][0], xacc[1][m][n][1], f2[m].y, f2[n].y);
                         }
                 }
             }
             // ---- fitted continuation values C^[l][n] = beta_l . x_p[n] on the FP64 tensor pipe ----
-            if (mt_cnt > 0) {
+            {
                 const double* pp[KSTEPS];
 #pragma unroll
                 for (int ks = 0; ks < KSTEPS; ks++) pp[ks] = resolve(descP[ks]) + g;
                 double* crow = sC + (size_t)(8 * mt_base + g) * TP + 2 * t;
+                if (aw != 0) {
+                    // six row blocks per warp: independent accumulator chains issued back to back, stores predicated
 #pragma unroll
-                for (int nt = 0; nt < TP / 8; nt++) {
-                    double bop[KSTEPS];
+                    for (int nt = 0; nt < TP / 8; nt++) {
+                        double bop[KSTEPS], cf[kFitTiles][2];
 #pragma unroll
-                    for (int ks = 0; ks < KSTEPS; ks++) bop[ks] = pp[ks][8 * nt];
+                        for (int ks = 0; ks < KSTEPS; ks++) bop[ks] = pp[ks][8 * nt];
 #pragma unroll
-                    for (int mi = 0; mi < kFitTiles; mi++) {
-                        if (mi < mt_cnt) {
-                            double c0 = 0.0, c1 = 0.0;
+                        for (int mi = 0; mi < kFitTiles; mi++) cf[mi][0] = cf[mi][1] = 0.0;
 #pragma unroll
-                            for (int ks = 0; ks < KSTEPS; ks++) dmma8x8x4(c0, c1, bfrag[mi][ks], bop[ks]);
-                            *reinterpret_cast<double2*>(crow + (size_t)8 * mi * TP + 8 * nt) = make_double2(c0, c1);
-                        }
+                        for (int ks = 0; ks < KSTEPS; ks++)
+#pragma unroll
+                            for (int mi = 0; mi < kFitTiles; mi++) dmma8x8x4(cf[mi][0], cf[mi][1], bfrag[mi][ks], bop[ks]);
+#pragma unroll
+                        for (int mi = 0; mi < kFitTiles; mi++)
+                            if (mi < mt_cnt) *reinterpret_cast<double2*>(crow + (size_t)8 * mi * TP + 8 * nt) = make_double2(cf[mi][0], cf[mi][1]);
+                    }
+                } else if (mt_cnt > 0) {
+#pragma unroll
+                    for (int nt = 0; nt < TP / 8; nt++) {
+                        double c0 = 0.0, c1 = 0.0;
+#pragma unroll
+                        for (int ks = 0; ks < KSTEPS; ks++) dmma8x8x4(c0, c1, bfrag[0][ks], pp[ks][8 * nt]);
+                        *reinterpret_cast<double2*>(crow + 8 * nt) = make_double2(c0, c1);
                     }
                 }
             }
+#endif
             mbar_arrive(&cready[b]);
             if (++stage == kRawStages) { stage = 0; sphase ^= 1; }
         }
@@ -461,7 +499,7 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
             for (int m = 0; m < MT; m++)
 #pragma unroll
                 for (int n = 0; n < MT; n++)
-                    *reinterpret_cast<double2*>(po + (size_t)(8 * m + g) * q.ncols + 8 * (NT + n) + 2 * t) = make_double2(xacc[m][n][0], xacc[m][n][1]);
+                    *reinterpret_cast<double2*>(po + (size_t)(8 * m + g) * q.ncols + 8 * (NT + n) + 2 * t) = make_double2(xacc[0][m][n][0] + xacc[1][m][n][0], xacc[0][m][n][1] + xacc[1][m][n][1]);
         }
     }
 }
@@ -517,7 +555,7 @@ static cudaError_t launch4_t(const SweepParams& q, int n_prod, int blocks, cudaS
         configured = smem;
     }
     CUtensorMap mv, msp, mfp, msm, mfm;
-    if (!make_map(&mv, q.Vnext, q.Npad, q.Gn, TP, q.Gn) || !make_map(&msp, q.spot_p, q.Npad, 1, TP, 1) ||
+    if (!make_map(&mv, q.Vnext, q.Npad, q.Gn, TP + 4, q.Gn) || !make_map(&msp, q.spot_p, q.Npad, 1, TP, 1) ||
         !make_map(&mfp, q.fac_p, q.Npad, q.F, TP, q.F) || !make_map(&msm, q.spot_m, q.Npad, 1, TP, 1) ||
         !make_map(&mfm, q.fac_m, q.Npad, q.F, TP, q.F))
         return cudaErrorInvalidValue;
