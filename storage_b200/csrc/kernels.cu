@@ -228,10 +228,11 @@ void launch_reduce_partials(const double* partial, int n_parts, int n_elem, doub
 // Column-equilibrated Cholesky (G~ = D G D, D = diag(G)^-1/2) with a pivot guard that drops numerically dependent
 // columns, one step of iterative refinement against the unscaled system, beta = D x.
 // =================================================================================================
-__global__ void __launch_bounds__(256) solve_kernel(SolveParams sp) {
+template <int KT>
+__global__ void __launch_bounds__(128) solve_kernel(SolveParams sp) {
     extern __shared__ double sm[];
     const int K = sp.K, G = sp.G, ld = sp.ncols, tid = threadIdx.x;
-    const double* red = sp.reduced;
+    const double* __restrict__ red = sp.reduced;
     if (sp.accum_mode == 2) {   // current period: continuation = mean over sims (LSV.cs:171-182)
         for (int i = tid; i < G; i += blockDim.x) {
             double* b = sp.beta + (size_t)i * sp.ldb;
@@ -243,6 +244,7 @@ __global__ void __launch_bounds__(256) solve_kernel(SolveParams sp) {
     double* A = sm;                 // [K][K] scaled Gram -> Cholesky factor (lower)
     double* Graw = A + K * K;       // [K][K] unscaled Gram
     double* dscale = Graw + K * K;  // [K]
+    double* Tm = dscale + K;        // [K][K] preconditioner (when present)
     __shared__ int dropped[64];
     const int gcol = 8 * sp.NT;
     const double* T = sp.precond;
@@ -252,6 +254,7 @@ __global__ void __launch_bounds__(256) solve_kernel(SolveParams sp) {
         dscale[k] = (gkk > 0.0 && !flagged) ? rsqrt(gkk) : 0.0;
         dropped[k] = (gkk > 0.0 && !flagged) ? 0 : 1;
     }
+    if (T) for (int e = tid; e < K * K; e += blockDim.x) Tm[e] = T[e];
     __syncthreads();
     for (int e = tid; e < K * K; e += blockDim.x) {
         int r = e / K, c = e % K;
@@ -261,66 +264,97 @@ __global__ void __launch_bounds__(256) solve_kernel(SolveParams sp) {
         A[e] = gv * dscale[r] * dscale[c];
     }
     __syncthreads();
-    for (int j = 0; j < K; j++) {
-        if (tid == 0) {
-            double piv = A[j * K + j];
-            if (dropped[j] || !(piv > sp.pivot_tol)) { dropped[j] = 1; A[j * K + j] = 1.0; }
-            else A[j * K + j] = sqrt(piv);
+    // Cholesky by warp 0 (lane = row, rows lane and lane + 32): no block-wide barriers in the column loop
+    if (tid < 32) {
+        for (int j = 0; j < K; j++) {
+            if (tid == 0) {
+                double piv = A[j * K + j];
+                if (dropped[j] || !(piv > sp.pivot_tol)) { dropped[j] = 1; A[j * K + j] = 1.0; }
+                else A[j * K + j] = sqrt(piv);
+            }
+            __syncwarp();
+            const bool dj = dropped[j];
+            const double ljj = A[j * K + j];
+            for (int i = j + 1 + tid; i < K; i += 32) A[i * K + j] = dj ? 0.0 : A[i * K + j] / ljj;
+            __syncwarp();
+            for (int i = j + 1 + tid; i < K; i += 32) {
+                const double aij = A[i * K + j];
+                for (int k = j + 1; k <= i; k++) A[i * K + k] -= aij * A[k * K + j];
+            }
+            __syncwarp();
         }
-        __syncthreads();
-        const bool dj = dropped[j];
-        const double ljj = A[j * K + j];
-        for (int i = j + 1 + tid; i < K; i += blockDim.x) A[i * K + j] = dj ? 0.0 : A[i * K + j] / ljj;
-        __syncthreads();
-        const int rem = K - j - 1;
-        for (int e = tid; e < rem * rem; e += blockDim.x) {
-            int i = j + 1 + e / rem, k = j + 1 + e % rem;
-            if (k <= i) A[i * K + k] -= A[i * K + j] * A[k * K + j];
-        }
-        __syncthreads();
     }
-    // each thread: one right-hand side at a time
+    __syncthreads();
+    // each thread: one right-hand side at a time, vectors in registers (KT = compile-time bound of K)
     for (int i = tid; i < G; i += blockDim.x) {
-        double x[64], r[64];
-        for (int k = 0; k < K; k++) { r[k] = red[(size_t)k * ld + i]; x[k] = 0.0; }
+        double x[KT], r[KT], y[KT];
+#pragma unroll
+        for (int k = 0; k < KT; k++) { r[k] = k < K ? red[(size_t)k * ld + i] : 0.0; x[k] = 0.0; y[k] = 0.0; }
+#pragma unroll 1
         for (int pass = 0; pass < 2; pass++) {
-            double y[64];
-            for (int k = 0; k < K; k++) {   // L y = D r
-                double s = r[k] * dscale[k];
-                for (int m = 0; m < k; m++) s -= A[k * K + m] * y[m];
-                y[k] = dropped[k] ? 0.0 : s / A[k * K + k];
+#pragma unroll
+            for (int k = 0; k < KT; k++) {   // L y = D r
+                if (k < K) {
+                    double s = r[k] * dscale[k];
+#pragma unroll
+                    for (int m = 0; m < k; m++) s -= A[k * K + m] * y[m];
+                    y[k] = dropped[k] ? 0.0 : s / A[k * K + k];
+                }
             }
-            for (int k = K - 1; k >= 0; k--) {   // L^T z = y
-                double s = y[k];
-                for (int m = k + 1; m < K; m++) s -= A[m * K + k] * y[m];
-                y[k] = dropped[k] ? 0.0 : s / A[k * K + k];
+#pragma unroll
+            for (int k = KT - 1; k >= 0; k--) {   // L^T z = y
+                if (k < K) {
+                    double s = y[k];
+#pragma unroll
+                    for (int m = k + 1; m < KT; m++) if (m < K) s -= A[m * K + k] * y[m];
+                    y[k] = dropped[k] ? 0.0 : s / A[k * K + k];
+                }
             }
-            for (int k = 0; k < K; k++) x[k] += y[k] * dscale[k];
+#pragma unroll
+            for (int k = 0; k < KT; k++) if (k < K) x[k] += y[k] * dscale[k];
             if (pass == 0) {   // residual of the unscaled system
-                for (int k = 0; k < K; k++) {
-                    double s = red[(size_t)k * ld + i];
-                    for (int m = 0; m < K; m++) s = fma(-Graw[k * K + m], x[m], s);
-                    r[k] = dropped[k] ? 0.0 : s;
+#pragma unroll
+                for (int k = 0; k < KT; k++) {
+                    if (k < K) {
+                        double s = red[(size_t)k * ld + i];
+#pragma unroll
+                        for (int m = 0; m < KT; m++) if (m < K) s = fma(-Graw[k * K + m], x[m], s);
+                        r[k] = dropped[k] ? 0.0 : s;
+                    }
                 }
             }
         }
         double* b = sp.beta + (size_t)i * sp.ldb;
         if (T) {   // back to the monomial basis: beta = T x
-            for (int k = 0; k < K; k++) {
-                double acc = 0.0;
-                for (int m = k; m < K; m++) acc = fma(T[(size_t)k * K + m], x[m], acc);
-                r[k] = acc;
+#pragma unroll
+            for (int k = 0; k < KT; k++) {
+                if (k < K) {
+                    double acc = 0.0;
+#pragma unroll
+                    for (int m = k; m < KT; m++) if (m < K) acc = fma(Tm[k * K + m], x[m], acc);
+                    b[k] = acc;
+                }
             }
-            for (int k = 0; k < sp.ldb; k++) b[k] = k < K ? r[k] : 0.0;
+            for (int k = K; k < sp.ldb; k++) b[k] = 0.0;
         } else {
-            for (int k = 0; k < sp.ldb; k++) b[k] = k < K ? x[k] : 0.0;
+#pragma unroll
+            for (int k = 0; k < KT; k++) if (k < K) b[k] = x[k];
+            for (int k = K; k < sp.ldb; k++) b[k] = 0.0;
         }
     }
 }
 
 void launch_solve(const SolveParams& sp, cudaStream_t stream) {
-    size_t smem = sizeof(double) * ((size_t)2 * sp.K * sp.K + sp.K);
-    solve_kernel<<<1, 256, smem, stream>>>(sp);
+    size_t smem = sizeof(double) * ((size_t)3 * sp.K * sp.K + sp.K);
+    if (sp.K <= 4) solve_kernel<4><<<1, 128, smem, stream>>>(sp);
+    else if (sp.K <= 8) solve_kernel<8><<<1, 128, smem, stream>>>(sp);
+    else if (sp.K <= 12) solve_kernel<12><<<1, 128, smem, stream>>>(sp);
+    else if (sp.K <= 16) solve_kernel<16><<<1, 128, smem, stream>>>(sp);
+    else {
+        static bool configured = false;
+        if (!configured) { cudaFuncSetAttribute(solve_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * (3 * 64 * 64 + 64))); configured = true; }
+        solve_kernel<64><<<1, 128, smem, stream>>>(sp);
+    }
 }
 
 // =================================================================================================
@@ -362,135 +396,173 @@ __device__ __forceinline__ bool bisect_dev(const double* grid, int n, double inv
 }
 
 constexpr int kFwdMaxDec = 16;
+constexpr int kFwdThreads = 256;
 
-__global__ void __launch_bounds__(256) forward_kernel(ForwardParams q) {
-    const BasisDev* __restrict__ bd = q.basis;
-    const int K = q.K, nsum = kFwdSums + K;
-    extern __shared__ double fsm[];   // [warps][nsum]
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-    double sums[kFwdSums];
+// All periods [p0, p1) in one launch: a thread owns its paths for the whole pass (no cross-path dependence in the forward
+// simulation, LSV.cs:426-480), the per-period descriptors come from a device array, basis-program nodes live in a
+// per-thread column of shared memory and the regressor row / column sums in registers (KT = compile-time bound of K).
+template <int KT>
+__global__ void __launch_bounds__(kFwdThreads, KT <= 16 ? 3 : 1) forward_kernel(const ForwardParams* __restrict__ pp, int p0, int p1) {
+    extern __shared__ double fsm[];   // [n_nodes][blockDim] node columns, [K][blockDim] column sums, [warps][nsum] reduction scratch
+    __shared__ ForwardParams sq;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
+    for (int p = p0; p < p1; p++) {
+        __syncthreads();
+        if (tid == 0) sq = pp[p];
+        __syncthreads();
+        const ForwardParams& q = sq;
+        const BasisDev* __restrict__ bd = q.basis;
+        const int K = q.K, nsum = kFwdSums + K;
+        double* nodes = fsm + tid;                                   // node j at nodes[j * blockDim.x]
+        double* xsum = nodes + (size_t)bd->n_nodes * blockDim.x;      // column k at xsum[k * blockDim.x]
+        double* red = fsm + (size_t)(bd->n_nodes + K) * blockDim.x;  // [warps][nsum]
+        double sums[kFwdSums];
 #pragma unroll
-    for (int i = 0; i < kFwdSums; i++) sums[i] = 0.0;
-    double xsum[64];
-    for (int k = 0; k < K; k++) xsum[k] = 0.0;
+        for (int i = 0; i < kFwdSums; i++) sums[i] = 0.0;
+        for (int k = 0; k < K; k++) xsum[(size_t)k * blockDim.x] = 0.0;
 
-    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; n < q.N; n += stride) {
-        const double s = q.spot_is_const ? q.spot_const : __ldcs(q.spot + n);
-        const double v = q.inventory[n];
-        double xrow[64];
-        if (q.cont_mode == 0) {
-            double nodes[kMaxNodes];
-            nodes[0] = 0.0; nodes[1] = 1.0; nodes[2] = s;
-            for (int f = 0; f < q.F; f++) nodes[3 + f] = __ldcs(q.fac + (size_t)f * q.Npad + n);
-            for (int o = 0; o < bd->n_ops; o++) {
-                const BasisOpDev op = bd->ops[o];
-                nodes[op.dst] = mul_rn(nodes[op.a], nodes[op.b]);
+        const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+        for (int64_t n = (int64_t)blockIdx.x * blockDim.x + tid; n < q.N; n += stride) {
+            const double s = q.spot_is_const ? q.spot_const : __ldcs(q.spot + n);
+            const double v = q.inventory[n];
+            double xrow[KT];
+            if (q.cont_mode == 0) {
+                nodes[0] = 0.0; nodes[(size_t)blockDim.x] = 1.0; nodes[(size_t)2 * blockDim.x] = s;
+                for (int f = 0; f < q.F; f++) nodes[(size_t)(3 + f) * blockDim.x] = __ldcs(q.fac + (size_t)f * q.Npad + n);
+                for (int o = 0; o < bd->n_ops; o++) {
+                    const BasisOpDev op = bd->ops[o];
+                    nodes[(size_t)op.dst * blockDim.x] = mul_rn(nodes[(size_t)op.a * blockDim.x], nodes[(size_t)op.b * blockDim.x]);
+                }
+#pragma unroll
+                for (int k = 0; k < KT; k++) {
+                    xrow[k] = (k < K) ? nodes[(size_t)bd->node_of_basis[k] * blockDim.x] : 0.0;
+                    if (k < K) xsum[(size_t)k * blockDim.x] += xrow[k];
+                }
             }
-            for (int k = 0; k < K; k++) { xrow[k] = nodes[bd->node_of_basis[k]]; xsum[k] += xrow[k]; }
-        }
-        // CmdtyStorage.GetInjectWithdrawRange (CmdtyStorage.cs:86-100)
-        if (v < q.min_inv - q.slack_lo || v > q.max_inv + q.slack_hi) atomicExch(q.error_flag, 1);
-        double rmin, rmax;
-        if (q.c_kind == LSMC_CONSTRAINT_CONSTANT) { rmin = __ldg(q.c_lo); rmax = __ldg(q.c_hi); }
-        else if (q.c_kind == LSMC_CONSTRAINT_PIECEWISE_LINEAR) { rmax = spline_dev(q.c_x, q.c_hi, q.c_n, v); rmin = spline_dev(q.c_x, q.c_lo, q.c_n, v); }
-        else {
-            if (v < __ldg(q.c_x) - q.slack_hi || v > __ldg(q.c_x + q.c_n - 1) + q.slack_hi) atomicExch(q.error_flag, 2);
-            int idx = min(max(last_at_or_below(q.c_x, q.c_n, v), 0), q.c_n - 1);
-            rmin = __ldg(q.c_lo + idx); rmax = __ldg(q.c_hi + idx);
-        }
-        const double loss = mul_rn(q.loss_pct, v);
-        // bang-bang decision set (SH.cs:109-197)
-        double dec[kFwdMaxDec];
-        int nd;
-        {
-            const double base = sub_rn(v, loss);
-            const double afterW = add_rn(rmin, base), afterJ = add_rn(rmax, base);
-            double w, jn;
-            if (afterW > q.next_max) { if (!(sub_rn(afterW, q.next_max) < q.tol)) atomicExch(q.error_flag, 3); w = sub_rn(q.next_max, base); }
-            else w = afterW > q.next_min ? rmin : sub_rn(q.next_min, base);
-            if (afterJ < q.next_min) { if (!(sub_rn(q.next_min, afterJ) < q.tol)) atomicExch(q.error_flag, 3); jn = sub_rn(q.next_min, base); }
-            else jn = afterJ < q.next_max ? rmax : sub_rn(q.next_max, base);
-            const int ex = q.extra;
-            if (w >= 0.0 || jn <= 0.0) {
-                nd = ex + 2;
-                dec[0] = w;
-                const double step = (jn - w) / (ex + 1);
-                for (int i = 0; i < ex; i++) dec[1 + i] = add_rn(mul_rn((double)(i + 1), step), w);
-                dec[nd - 1] = jn;
-            } else {
-                nd = 2 * ex + 3;
-                dec[0] = w;
-                const double stepw = (0.0 - w) / (ex + 1), stepj = (jn - 0.0) / (ex + 1);
-                for (int i = 0; i < ex; i++) { dec[1 + i] = add_rn(mul_rn((double)(i + 1), stepw), w); dec[ex + 2 + i] = add_rn(mul_rn((double)(i + 1), stepj), 0.0); }
-                dec[ex + 1] = 0.0;
-                dec[nd - 1] = jn;
-            }
-        }
-        const double inv_cost_npv = q.inv_cost == 0.0 ? 0.0 : mul_rn(mul_rn(v, q.inv_cost), q.inv_cost_df);
-        double best = 0.0, best_imm = 0.0, best_cons = 0.0, best_vol = 0.0;
-        int best_d = 0;
-        for (int d = 0; d < nd; d++) {
-            const double vol = dec[d];
-            const double after = sub_rn(add_rn(v, vol), loss);
-            const double cons = vol > 0.0 ? mul_rn(q.cons_inj, fabs(vol)) : mul_rn(q.cons_wd, fabs(-vol));
-            const double a = mul_rn(mul_rn(-vol, s), q.df);
-            const double c = mul_rn(mul_rn(-cons, s), q.df);
-            const double cost = vol > 0.0 ? mul_rn(mul_rn(q.inj_cost, vol), q.inj_df) : mul_rn(mul_rn(q.wd_cost, fabs(-vol)), q.wd_df);
-            const double imm = sub_rn(add_rn(sub_rn(a, cost), c), inv_cost_npv);
-            int lo, hi;
-            if (!bisect_dev(q.next_grid, q.Gn, after, q.tol, lo, hi)) { atomicExch(q.error_flag, 4); lo = hi = 0; }
-            auto fitted = [&](int l) {
-                const double* b = q.beta + (size_t)l * q.ldb;
-                if (q.cont_mode == 1) return __ldg(b);
-                double acc = 0.0;
-                for (int k = 0; k < K; k++) acc = fma(xrow[k], __ldg(b + k), acc);
-                return acc;
-            };
-            double cont;
-            if (lo == hi) cont = fitted(lo);
+            // CmdtyStorage.GetInjectWithdrawRange (CmdtyStorage.cs:86-100)
+            if (v < q.min_inv - q.slack_lo || v > q.max_inv + q.slack_hi) atomicExch(q.error_flag, 1);
+            double rmin, rmax;
+            if (q.c_kind == LSMC_CONSTRAINT_CONSTANT) { rmin = __ldg(q.c_lo); rmax = __ldg(q.c_hi); }
+            else if (q.c_kind == LSMC_CONSTRAINT_PIECEWISE_LINEAR) { rmax = spline_dev(q.c_x, q.c_hi, q.c_n, v); rmin = spline_dev(q.c_x, q.c_lo, q.c_n, v); }
             else {
-                const double gl = __ldg(q.next_grid + lo), gu = __ldg(q.next_grid + hi);
-                const double wl = sub_rn(gu, after) / sub_rn(gu, gl);
-                const double wu = sub_rn(1.0, wl);
-                cont = add_rn(mul_rn(fitted(lo), wl), mul_rn(fitted(hi), wu));
+                if (v < __ldg(q.c_x) - q.slack_hi || v > __ldg(q.c_x + q.c_n - 1) + q.slack_hi) atomicExch(q.error_flag, 2);
+                int idx = min(max(last_at_or_below(q.c_x, q.c_n, v), 0), q.c_n - 1);
+                rmin = __ldg(q.c_lo + idx); rmax = __ldg(q.c_hi + idx);
             }
-            const double tot = add_rn(imm, cont);
-            if (d == 0 || tot > best) { best = tot; best_imm = imm; best_cons = cons; best_vol = vol; best_d = d; }
-        }
-        const double next_inv = sub_rn(add_rn(v, best_vol), loss);
-        q.inventory[n] = next_inv;
-        q.pv_by_sim[n] = add_rn(q.pv_by_sim[n], best_imm);
-        const double net = sub_rn(-best_vol, best_cons);
-        sums[0] += v; sums[1] += best_vol; sums[2] += best_cons; sums[3] += loss; sums[4] += net; sums[5] += best_imm;
-        sums[6] += mul_rn(-(add_rn(best_vol, best_cons)), s);
-        if (q.o_inventory) __stcs(q.o_inventory + n, v);
-        if (q.o_volume) __stcs(q.o_volume + n, best_vol);
-        if (q.o_consumed) __stcs(q.o_consumed + n, best_cons);
-        if (q.o_loss) __stcs(q.o_loss + n, loss);
-        if (q.o_net) __stcs(q.o_net + n, net);
-        if (q.o_pv) __stcs(q.o_pv + n, best_imm);
-        if (q.o_decision) q.o_decision[n] = (int8_t)best_d;
-    }
-    // block reduction (fixed order)
-    for (int i = 0; i < nsum; i++) {
-        double val = i < kFwdSums ? sums[i] : xsum[i - kFwdSums];
+            const double loss = mul_rn(q.loss_pct, v);
+            // bang-bang decision set (SH.cs:109-197)
+            double dec[kFwdMaxDec];
+            int nd;
+            {
+                const double base = sub_rn(v, loss);
+                const double afterW = add_rn(rmin, base), afterJ = add_rn(rmax, base);
+                double w, jn;
+                if (afterW > q.next_max) { if (!(sub_rn(afterW, q.next_max) < q.tol)) atomicExch(q.error_flag, 3); w = sub_rn(q.next_max, base); }
+                else w = afterW > q.next_min ? rmin : sub_rn(q.next_min, base);
+                if (afterJ < q.next_min) { if (!(sub_rn(q.next_min, afterJ) < q.tol)) atomicExch(q.error_flag, 3); jn = sub_rn(q.next_min, base); }
+                else jn = afterJ < q.next_max ? rmax : sub_rn(q.next_max, base);
+                const int ex = q.extra;
+                if (ex == 0) {   // the common case stays in registers
+                    dec[0] = w;
+                    if (w >= 0.0 || jn <= 0.0) { nd = 2; dec[1] = jn; dec[2] = jn; }
+                    else { nd = 3; dec[1] = 0.0; dec[2] = jn; }
+                } else if (w >= 0.0 || jn <= 0.0) {
+                    nd = ex + 2;
+                    dec[0] = w;
+                    const double step = (jn - w) / (ex + 1);
+                    for (int i = 0; i < ex; i++) dec[1 + i] = add_rn(mul_rn((double)(i + 1), step), w);
+                    dec[nd - 1] = jn;
+                } else {
+                    nd = 2 * ex + 3;
+                    dec[0] = w;
+                    const double stepw = (0.0 - w) / (ex + 1), stepj = (jn - 0.0) / (ex + 1);
+                    for (int i = 0; i < ex; i++) { dec[1 + i] = add_rn(mul_rn((double)(i + 1), stepw), w); dec[ex + 2 + i] = add_rn(mul_rn((double)(i + 1), stepj), 0.0); }
+                    dec[ex + 1] = 0.0;
+                    dec[nd - 1] = jn;
+                }
+            }
+            const double inv_cost_npv = q.inv_cost == 0.0 ? 0.0 : mul_rn(mul_rn(v, q.inv_cost), q.inv_cost_df);
+            double best = 0.0, best_imm = 0.0, best_cons = 0.0, best_vol = 0.0;
+            int best_d = 0;
+            auto consider = [&](int d, double vol) {
+                const double after = sub_rn(add_rn(v, vol), loss);
+                const double cons = vol > 0.0 ? mul_rn(q.cons_inj, fabs(vol)) : mul_rn(q.cons_wd, fabs(-vol));
+                const double a = mul_rn(mul_rn(-vol, s), q.df);
+                const double c = mul_rn(mul_rn(-cons, s), q.df);
+                const double cost = vol > 0.0 ? mul_rn(mul_rn(q.inj_cost, vol), q.inj_df) : mul_rn(mul_rn(q.wd_cost, fabs(-vol)), q.wd_df);
+                const double imm = sub_rn(add_rn(sub_rn(a, cost), c), inv_cost_npv);
+                int lo, hi;
+                if (!bisect_dev(q.next_grid, q.Gn, after, q.tol, lo, hi)) { atomicExch(q.error_flag, 4); lo = hi = 0; }
+                auto fitted = [&](int l) {
+                    const double* b = q.beta + (size_t)l * q.ldb;
+                    if (q.cont_mode == 1) return __ldg(b);
+                    double acc = 0.0;
 #pragma unroll
-        for (int off = 16; off > 0; off >>= 1) val += __shfl_xor_sync(0xffffffffu, val, off);
-        if (lane == 0) fsm[warp * nsum + i] = val;
-    }
-    __syncthreads();
-    for (int i = threadIdx.x; i < nsum; i += blockDim.x) {
-        double tot = 0.0;
-        for (int w = 0; w < nwarps; w++) tot += fsm[w * nsum + i];
-        q.sums[(size_t)blockIdx.x * nsum + i] = tot;
+                    for (int k = 0; k < KT; k++) if (k < K) acc = fma(xrow[k], __ldg(b + k), acc);
+                    return acc;
+                };
+                double cont;
+                if (lo == hi) cont = fitted(lo);
+                else {
+                    const double gl = __ldg(q.next_grid + lo), gu = __ldg(q.next_grid + hi);
+                    const double wl = sub_rn(gu, after) / sub_rn(gu, gl);
+                    const double wu = sub_rn(1.0, wl);
+                    cont = add_rn(mul_rn(fitted(lo), wl), mul_rn(fitted(hi), wu));
+                }
+                const double tot = add_rn(imm, cont);
+                if (d == 0 || tot > best) { best = tot; best_imm = imm; best_cons = cons; best_vol = vol; best_d = d; }
+            };
+            if (q.extra == 0) {
+                consider(0, dec[0]);
+                consider(1, dec[1]);
+                if (nd == 3) consider(2, dec[2]);
+            } else {
+                for (int d = 0; d < nd; d++) consider(d, dec[d]);
+            }
+            const double next_inv = sub_rn(add_rn(v, best_vol), loss);
+            q.inventory[n] = next_inv;
+            q.pv_by_sim[n] = add_rn(q.pv_by_sim[n], best_imm);
+            const double net = sub_rn(-best_vol, best_cons);
+            sums[0] += v; sums[1] += best_vol; sums[2] += best_cons; sums[3] += loss; sums[4] += net; sums[5] += best_imm;
+            sums[6] += mul_rn(-(add_rn(best_vol, best_cons)), s);
+            if (q.o_inventory) __stcs(q.o_inventory + n, v);
+            if (q.o_volume) __stcs(q.o_volume + n, best_vol);
+            if (q.o_consumed) __stcs(q.o_consumed + n, best_cons);
+            if (q.o_loss) __stcs(q.o_loss + n, loss);
+            if (q.o_net) __stcs(q.o_net + n, net);
+            if (q.o_pv) __stcs(q.o_pv + n, best_imm);
+            if (q.o_decision) q.o_decision[n] = (int8_t)best_d;
+        }
+        // block reduction (fixed order)
+#pragma unroll
+        for (int i = 0; i < kFwdSums + KT; i++) {
+            if (i < nsum) {
+                double val = i < kFwdSums ? sums[i < kFwdSums ? i : 0] : xsum[(size_t)(i >= kFwdSums ? i - kFwdSums : 0) * blockDim.x];
+#pragma unroll
+                for (int off = 16; off > 0; off >>= 1) val += __shfl_xor_sync(0xffffffffu, val, off);
+                if (lane == 0) red[warp * nsum + i] = val;
+            }
+        }
+        __syncthreads();
+        for (int i = tid; i < nsum; i += blockDim.x) {
+            double tot = 0.0;
+            for (int w = 0; w < nwarps; w++) tot += red[w * nsum + i];
+            q.sums[(size_t)blockIdx.x * nsum + i] = tot;
+        }
     }
 }
 
-void launch_forward(const ForwardParams& q, int blocks, cudaStream_t stream) {
-    const int threads = 256;
-    size_t smem = sizeof(double) * (threads / 32) * (kFwdSums + q.K);
-    forward_kernel<<<blocks, threads, smem, stream>>>(q);
+void launch_forward(const ForwardParams* pp, int p0, int p1, int K, int n_nodes, int blocks, cudaStream_t stream) {
+    const size_t smem = sizeof(double) * ((size_t)(n_nodes + K) * kFwdThreads + (size_t)(kFwdThreads / 32) * (kFwdSums + K));
+    if (K <= 4) forward_kernel<4><<<blocks, kFwdThreads, smem, stream>>>(pp, p0, p1);
+    else if (K <= 8) forward_kernel<8><<<blocks, kFwdThreads, smem, stream>>>(pp, p0, p1);
+    else if (K <= 12) forward_kernel<12><<<blocks, kFwdThreads, smem, stream>>>(pp, p0, p1);
+    else if (K <= 16) forward_kernel<16><<<blocks, kFwdThreads, smem, stream>>>(pp, p0, p1);
+    else {
+        static size_t configured = 0;
+        if (smem > configured) { cudaFuncSetAttribute(forward_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); configured = smem; }
+        forward_kernel<64><<<blocks, kFwdThreads, smem, stream>>>(pp, p0, p1);
+    }
 }
 
 // Column reduction of block partials: out[r][c] = sum_b in[r][b][c]; one warp per (r, c).

@@ -89,6 +89,7 @@ struct lsmc_ctx {
     DevBuf<int32_t> t_ndec, t_lo, t_hi;
     DevBuf<double> s_decay, s_chol, s_vol, s_drift, s_fwd, normals_stage;
     DevBuf<BasisDev> basis;
+    DevBuf<ForwardParams> fwd_params;   // [P-1] per-period descriptors of the forward pass
     DevBuf<double> precond;     // [S][precond_stride(K)] regression preconditioners (rank 0's, broadcast)
     DevBuf<int> error_flag;
     DevBuf<double> panels[6];
@@ -183,7 +184,7 @@ void set_problem(lsmc_ctx* c, const lsmc_problem* problem) {
     c->sweep_blocks = (int)std::min<int64_t>(c->num_sms, n_tiles);
     c->TP4 = sweep4_tile(pl.max_grid, pl.K, pl.F, (int)pl.basis.ops.size());
     c->sweep4_blocks = c->TP4 ? (int)std::min<int64_t>(c->num_sms, (c->N + c->TP4 - 1) / c->TP4) : 0;
-    c->fwd_blocks = (int)std::min<int64_t>((int64_t)c->num_sms * 4, (c->N + 255) / 256);
+    c->fwd_blocks = (int)std::min<int64_t>((int64_t)c->num_sms * (pl.K <= 16 ? 3 : 1), (c->N + 255) / 256);   // all CTAs resident: each walks every period
     c->ncols_max = 8 * ((pl.max_grid + 7) / 8 + c->MT);
 
     cudaStream_t s = c->stream;
@@ -419,8 +420,10 @@ void forward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
     const bool panels = (c->outputs & 1) != 0;
     double progress = 0.66;
     const double fwd_step = (1.0 - 0.66) / P;   // LSV.cs:371
+    std::vector<ForwardParams> hq((size_t)(P - 1));
     for (int p = 0; p < P - 1; p++) {
-        ForwardParams q{};
+        ForwardParams& q = hq[p];
+        q = ForwardParams{};
         q.N = c->N; q.Npad = c->Npad; q.p = p; q.Gn = pl.grid_size(p + 1); q.K = K; q.F = F; q.max_dec = pl.max_dec; q.extra = pb.extra_decisions;
         const bool is_current = (p == 0 && s0 == 1);
         q.cont_mode = is_current ? 1 : 0; q.spot_is_const = is_current ? 1 : 0; q.spot_const = pb.forward[p];
@@ -446,15 +449,22 @@ void forward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
             q.o_loss = c->panels[3].p + (size_t)p * Np; q.o_net = c->panels[4].p + (size_t)p * Np; q.o_pv = c->panels[5].p + (size_t)p * Np;
         }
         if (c->outputs & 2) q.o_decision = c->decisions.p + (size_t)p * Np;
-        launch_forward(q, c->fwd_blocks, s);
+    }
+    c->fwd_params.upload(hq, s);
+    if (!cb) {   // the whole pass in one launch
+        launch_forward(c->fwd_params.p, 0, P - 1, K, pl.basis.n_nodes, c->fwd_blocks, s);
         c->tm.kernel_launches++;
-        progress += fwd_step;
-        if (cb) {
+    } else {     // one launch per period so that progress / cancellation keep the reference's cadence (LSV.cs:488-490)
+        for (int p = 0; p < P - 1; p++) {
+            launch_forward(c->fwd_params.p, p, p + 1, K, pl.basis.n_nodes, c->fwd_blocks, s);
+            c->tm.kernel_launches++;
+            progress += fwd_step;
             CUDA_CHECK(cudaStreamSynchronize(s));
             check_device_error_flag(c);
             if (cb(user, progress) != 0) throw Error(LSMC_ECANCELLED, "The operation was canceled.");
         }
     }
+    CUDA_CHECK(cudaGetLastError());
     launch_reduce_rows(c->fwd_sums.p, P - 1, c->fwd_blocks, nsum, c->fwd_red.p, s);
     c->tm.kernel_launches++;
     c->allreduce(c->fwd_red.p, (size_t)(P - 1) * nsum);
