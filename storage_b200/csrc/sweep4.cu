@@ -56,12 +56,18 @@ __device__ __forceinline__ double2 lds128(const double* p) { return *reinterpret
 #ifndef LSMC_ABLATE   // development only: timing ablations (results are wrong when != 0)
 #define LSMC_ABLATE 0
 #endif
+// 5: no decisions; 6: no aux DMMA work; 7: 5 + no fit; 8: 5 + no x~ / Gram; 9: 5 + 6 (TMA + barrier skeleton only)
+#define AB_NO_DECIDE (LSMC_ABLATE == 5 || LSMC_ABLATE == 7 || LSMC_ABLATE == 8 || LSMC_ABLATE == 9)
+#define AB_NO_XT (LSMC_ABLATE == 6 || LSMC_ABLATE == 8 || LSMC_ABLATE == 9)
+#define AB_NO_FIT (LSMC_ABLATE == 6 || LSMC_ABLATE == 7 || LSMC_ABLATE == 9)
+// 13: only decision warps 0..6 decide; 14: only warps 0, 4, 8, 12 (one sub-partition) decide
 
 constexpr int kWarps = 16;
 constexpr int kDecWarps = 13;          // grid rows <= 104
 constexpr int kAuxWarps = 3;
 constexpr int kRawStages = 3;
 constexpr int kMaxProd = 32;           // product nodes of the basis program
+constexpr int kLutBytes = 24 * 16 + 24 * 8;
 constexpr int kFitTiles = 6;           // C^ row blocks per fit warp (warps 14, 15; warp 13 takes the 13th)
 
 __host__ __device__ inline size_t al128(size_t b) { return (b + 127) & ~(size_t)127; }
@@ -70,7 +76,7 @@ __host__ __device__ inline size_t al128(size_t b) { return (b + 127) & ~(size_t)
 struct Layout4 {
     int GnP, MT, LDP, VP;                                 // VP: pitch of the V_next tile (TP + 4: conflict-free 64-bit gathers)
     size_t o_sp, o_fp, o_sm, o_fm, stage;                 // raw stage: spot_p | fac_p[F] | spot_m | fac_m[F]
-    size_t vn, c, raw, prod, xt, zero, ones, ones_last, total;
+    size_t vn, vn_buf, c, raw, prod, xt, zero, ones, ones_last, lut, total;   // vn_buf: bytes of one V_next buffer
 };
 
 __host__ __device__ inline Layout4 layout4(int TP, int Gn, int K, int F, int n_prod) {
@@ -83,7 +89,8 @@ __host__ __device__ inline Layout4 layout4(int TP, int Gn, int K, int F, int n_p
     L.o_sp = 0; L.o_fp = al128(row); L.o_sm = L.o_fp + al128(F * row); L.o_fm = L.o_sm + al128(row);
     L.stage = L.o_fm + al128(F * row);
     size_t o = 0;
-    L.vn = o;   o += al128((size_t)2 * L.GnP * L.VP * 8);
+    L.vn_buf = al128((size_t)Gn * L.VP * 8);
+    L.vn = o;   o += 2 * L.vn_buf;
     L.c = o;    o += al128((size_t)2 * L.GnP * row);
     L.raw = o;  o += kRawStages * L.stage;
     L.prod = o; o += al128((size_t)2 * (n_prod > 0 ? n_prod : 1) * L.LDP * 8);
@@ -91,6 +98,7 @@ __host__ __device__ inline Layout4 layout4(int TP, int Gn, int K, int F, int n_p
     L.zero = o; o += al128(row);
     L.ones = o; o += al128(row);
     L.ones_last = o; o += al128(row);
+    L.lut = o;  o += (size_t)kDecWarps * kLutBytes;   // per decision warp: (w_lo, w_hi)[3][8] then (row_lo, row_hi)[3][8]
     L.total = o;
     return L;
 }
@@ -108,27 +116,75 @@ struct RowTab {
 
 enum : int { kZero1 = 1, kCons0 = 2, kCons2 = 4, kInvc = 8, kGeneric = 16 };
 
-// One tile of one decision warp.  tot_d = ((-vol_d s) df - cost_d [+ (-cons_d s) df]) + cont_d [- invc]
-// (LSV.cs:304-330, operation order kept; the skipped terms are exact no-ops, see sweep.cu).
+// Shared state of one CTA's pipeline, handed to the per-variant decision loops.
+struct Pipe4 {
+    unsigned char* sm;
+    uint64_t *vfull, *cready, *dfree, *rfull;
+};
+
+// Timing ablations: a decision warp that only keeps the pipeline's hand-shakes going.
+__device__ __noinline__ void decision_loop_empty(const SweepParams& q, const Pipe4& P, int TP) {
+    const int64_t n_tiles = (q.N + TP - 1) / TP;
+    int stage = 0, sphase = 0, it = 0;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, it++) {
+        const int b = it & 1;
+        const uint32_t par = (uint32_t)((it >> 1) & 1);
+        mbar_wait(&P.cready[b], par);
+        mbar_wait(&P.rfull[stage], (uint32_t)sphase);
+        mbar_wait(&P.vfull[b], par);
+        mbar_arrive(&P.dfree[b]);
+        if (++stage == kRawStages) { stage = 0; sphase ^= 1; }
+    }
+}
+
+// The decision warps' tile loop for one table variant.  tot_d = ((-vol_d s) df - cost_d [+ (-cons_d s) df]) + cont_d [- invc]
+// (LSV.cs:304-330, operation order kept; the skipped terms are exact no-ops, see sweep.cu).  Each 8-path step is split
+// into phase A (fitted values -> totals -> first strictly greatest, SH.cs:206-222) and phase B (weights and rows of the
+// chosen decision from the warp's table in shared memory, gather of V_next, value, store, normal-equation update); phase B
+// of step u-1 is issued after phase A of step u, so the two dependent shared-memory round trips of the gather hide
+// behind independent FP64 work.
 template <int TP, int MTD, int KS, int FLAGS>
-__device__ __forceinline__ void decide_tile(const RowTab& R, const double* __restrict__ sC, const double* __restrict__ sV,
-                                            const double* __restrict__ sS, const double* __restrict__ sXT,
-                                            double* __restrict__ out, const double df, const int g, const int t,
-                                            double (&acc)[MTD > 0 ? MTD : 1][2], double (&accS)[KS > 0 ? KS : 1]) {
+__device__ __forceinline__ void decision_loop(const SweepParams& q, const Layout4& L, const Pipe4& P, const RowTab& R,
+                                              const int j, const int g, const int t) {
     constexpr bool ZERO1 = (FLAGS & kZero1) != 0, CONS0 = (FLAGS & kCons0) != 0, CONS2 = (FLAGS & kCons2) != 0, INVC = (FLAGS & kInvc) != 0;
     constexpr bool CONS1 = CONS0 || CONS2;
-    const double* pS = sS + 2 * t;
-    constexpr int VP = TP + 4;
-    const double* pL0 = sC + R.rL[0] * TP + 2 * t; const double* pH0 = sC + R.rH[0] * TP + 2 * t;
-    const double* pL1 = sC + R.rL[1] * TP + 2 * t; const double* pH1 = sC + R.rH[1] * TP + 2 * t;
-    const double* pL2 = sC + R.rL[2] * TP + 2 * t; const double* pH2 = sC + R.rH[2] * TP + 2 * t;
-    const double* pV = sV + 2 * t;
-    const double* pXd = sXT + (size_t)g * TP + 2 * t;            // DMMA A operand: x~[8m+g][.]
-    const double* pXs = sXT + (size_t)(8 * MTD) * TP + 2 * t;    // scalar remainder rows x~[8 MTD + r][.]
+    constexpr int MT = MTD + (KS > 0 ? 1 : 0);
+    constexpr int NIT = TP / 8;
+    const int GnP = L.GnP;
+    const int64_t n_tiles = (q.N + TP - 1) / TP;
+    const double df = q.df;
+    double acc[MTD > 0 ? MTD : 1][2];
+    double accS[KS > 0 ? KS : 1];
 #pragma unroll
-    for (int u8 = 0; u8 < TP; u8 += 8) {
-        double v0, v1;
-        {
+    for (int m = 0; m < (MTD > 0 ? MTD : 1); m++) acc[m][0] = acc[m][1] = 0.0;
+#pragma unroll
+    for (int r = 0; r < (KS > 0 ? KS : 1); r++) accS[r] = 0.0;
+    const int i = 8 * j + g;
+    double* const vrow = q.Vout + (size_t)(R.row_ok ? i : 0) * q.Npad + 2 * t;
+    const unsigned char* const lutw = P.sm + L.lut + (size_t)j * kLutBytes + g * 16;           // + 128 k
+    const unsigned char* const luto = P.sm + L.lut + (size_t)j * kLutBytes + 24 * 16 + g * 8;   // + 64 k
+
+    int stage = 0, sphase = 0, it = 0;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, it++) {
+        const int b = it & 1;
+        const uint32_t par = (uint32_t)((it >> 1) & 1);
+        mbar_wait(&P.cready[b], par);                   // C^ and x~ of this tile are in place
+        mbar_wait(&P.rfull[stage], (uint32_t)sphase);   // spot row (landed long ago; makes the async-proxy writes visible here)
+        mbar_wait(&P.vfull[b], par);                    // V_next tile
+        const double* sC = reinterpret_cast<const double*>(P.sm + L.c) + (size_t)b * GnP * TP + 2 * t;
+        const unsigned char* pV = P.sm + L.vn + (size_t)b * L.vn_buf + 16 * t;
+        const double* pS = reinterpret_cast<const double*>(P.sm + L.raw + (size_t)stage * L.stage + L.o_sp) + 2 * t;
+        const double* sX = reinterpret_cast<const double*>(P.sm + L.xt) + (size_t)b * 8 * MT * TP + 2 * t;
+        const double* pL0 = sC + R.rL[0] * TP; const double* pH0 = sC + R.rH[0] * TP;
+        const double* pL1 = sC + R.rL[1] * TP; const double* pH1 = sC + R.rH[1] * TP;
+        const double* pL2 = sC + R.rL[2] * TP; const double* pH2 = sC + R.rH[2] * TP;
+        const double* pXd = sX + (size_t)g * TP;            // DMMA A operand: x~[8m+g][.]
+        const double* pXs = sX + (size_t)(8 * MTD) * TP;    // scalar remainder rows x~[8 MTD + r][.]
+        double* out = vrow + tile * TP;
+
+        double best0, best1, bc0, bc1;   // carried from phase A to phase B
+        int k0, k1;
+        auto phaseA = [&](const int u8) {
             const double2 s2 = lds128(pS + u8);
             double c0[3], c1[3], x0[3], x1[3];
 #pragma unroll
@@ -149,56 +205,68 @@ __device__ __forceinline__ void decide_tile(const RowTab& R, const double* __res
                 }
                 if (INVC) { x0[d] = sub_rn(x0[d], R.invc); x1[d] = sub_rn(x1[d], R.invc); }
             }
-            // first strictly greatest total (SH.cs:206-222)
             const bool a1 = x0[1] > x0[0], b1 = x1[1] > x1[0];
-            double best0 = a1 ? x0[1] : x0[0], best1 = b1 ? x1[1] : x1[0];
-            double bc0 = a1 ? c0[1] : c0[0], bc1 = b1 ? c1[1] : c1[0];
-            int oL0 = a1 ? R.rL[1] : R.rL[0], oL1 = b1 ? R.rL[1] : R.rL[0];
-            int oH0 = a1 ? R.rH[1] : R.rH[0], oH1 = b1 ? R.rH[1] : R.rH[0];
-            double wl0 = a1 ? R.wl[1] : R.wl[0], wl1 = b1 ? R.wl[1] : R.wl[0];
-            double wh0 = a1 ? R.wh[1] : R.wh[0], wh1 = b1 ? R.wh[1] : R.wh[0];
+            best0 = a1 ? x0[1] : x0[0]; best1 = b1 ? x1[1] : x1[0];
+            bc0 = a1 ? c0[1] : c0[0]; bc1 = b1 ? c1[1] : c1[0];
+            k0 = a1 ? 1 : 0; k1 = b1 ? 1 : 0;
             const bool a2 = x0[2] > best0, b2 = x1[2] > best1;
             best0 = a2 ? x0[2] : best0; best1 = b2 ? x1[2] : best1;
             bc0 = a2 ? c0[2] : bc0; bc1 = b2 ? c1[2] : bc1;
-            oL0 = a2 ? R.rL[2] : oL0; oL1 = b2 ? R.rL[2] : oL1;
-            oH0 = a2 ? R.rH[2] : oH0; oH1 = b2 ? R.rH[2] : oH1;
-            wl0 = a2 ? R.wl[2] : wl0; wl1 = b2 ? R.wl[2] : wl1;
-            wh0 = a2 ? R.wh[2] : wh0; wh1 = b2 ? R.wh[2] : wh1;
-#if LSMC_ABLATE == 1
-            oL0 = oL1 = R.rL[0]; oH0 = oH1 = R.rH[0]; wl0 = wl1 = R.wl[0]; wh0 = wh1 = R.wh[0];
-#endif
-#if LSMC_ABLATE == 2
-            const double act0 = best0, act1 = best1;
-#else
-            const double act0 = add_rn(mul_rn(pV[oH0 * VP + u8], wh0), mul_rn(pV[oL0 * VP + u8], wl0));
-            const double act1 = add_rn(mul_rn(pV[oH1 * VP + u8 + 1], wh1), mul_rn(pV[oL1 * VP + u8 + 1], wl1));
-#endif
-            v0 = add_rn(best0, add_rn(-bc0, act0));
-            v1 = add_rn(best1, add_rn(-bc1, act1));
+            k0 = a2 ? 2 : k0; k1 = b2 ? 2 : k1;
+        };
+        auto phaseB = [&](const int u8, const double bst0, const double bst1, const double bcc0, const double bcc1, const int kk0, const int kk1) {
+            const double2 w0 = *reinterpret_cast<const double2*>(lutw + 128 * kk0);
+            const double2 w1 = *reinterpret_cast<const double2*>(lutw + 128 * kk1);
+            const int2 o0 = *reinterpret_cast<const int2*>(luto + 64 * kk0);
+            const int2 o1 = *reinterpret_cast<const int2*>(luto + 64 * kk1);
+            const double vl0 = *reinterpret_cast<const double*>(pV + o0.x + 8 * u8), vh0 = *reinterpret_cast<const double*>(pV + o0.y + 8 * u8);
+            const double vl1 = *reinterpret_cast<const double*>(pV + o1.x + 8 * u8 + 8), vh1 = *reinterpret_cast<const double*>(pV + o1.y + 8 * u8 + 8);
+            const double act0 = add_rn(mul_rn(vh0, w0.y), mul_rn(vl0, w0.x));
+            const double act1 = add_rn(mul_rn(vh1, w1.y), mul_rn(vl1, w1.x));
+            double v0 = add_rn(bst0, add_rn(-bcc0, act0));
+            double v1 = add_rn(bst1, add_rn(-bcc1, act1));
             // lanes of rows beyond the grid compute on row 0 (valid memory, finite values) and contribute zeros
-#if LSMC_ABLATE == 4
-            if (v0 == 1.2345e300) __stcs(reinterpret_cast<double2*>(out + 2 * t + u8), make_double2(v0, v1));
-#else
-            if (R.row_ok) __stcs(reinterpret_cast<double2*>(out + 2 * t + u8), make_double2(v0, v1));
+            if (R.row_ok) __stcs(reinterpret_cast<double2*>(out + u8), make_double2(v0, v1));
             else { v0 = 0.0; v1 = 0.0; }
-#endif
-        }
-#if LSMC_ABLATE == 3
-        accS[0] += v0 + v1;
-#else
 #pragma unroll
-        for (int m = 0; m < MTD; m++) {
-            const double2 a2 = lds128(pXd + (size_t)8 * m * TP + u8);
-            dmma8x8x4(acc[m][0], acc[m][1], a2.x, v0);
-            dmma8x8x4(acc[m][0], acc[m][1], a2.y, v1);
-        }
+            for (int m = 0; m < MTD; m++) {
+                const double2 a2 = lds128(pXd + (size_t)8 * m * TP + u8);
+                dmma8x8x4(acc[m][0], acc[m][1], a2.x, v0);
+                dmma8x8x4(acc[m][0], acc[m][1], a2.y, v1);
+            }
 #pragma unroll
-        for (int r = 0; r < KS; r++) {
-            const double2 a2 = lds128(pXs + (size_t)r * TP + u8);
-            accS[r] = fma(a2.x, v0, accS[r]);
-            accS[r] = fma(a2.y, v1, accS[r]);
+            for (int r = 0; r < KS; r++) {
+                const double2 a2 = lds128(pXs + (size_t)r * TP + u8);
+                accS[r] = fma(a2.x, v0, accS[r]);
+                accS[r] = fma(a2.y, v1, accS[r]);
+            }
+        };
+        phaseA(0);
+#pragma unroll
+        for (int u = 1; u < NIT; u++) {
+            const double pb0 = best0, pb1 = best1, pc0 = bc0, pc1 = bc1;
+            const int pk0 = k0, pk1 = k1;
+            phaseA(8 * u);
+            phaseB(8 * (u - 1), pb0, pb1, pc0, pc1, pk0, pk1);
         }
-#endif
+        phaseB(8 * (NIT - 1), best0, best1, bc0, bc1, k0, k1);
+        mbar_arrive(&P.dfree[b]);
+        if (++stage == kRawStages) { stage = 0; sphase ^= 1; }
+    }
+    // per-CTA partial: partial[cta][k][col]; DMMA blocks: k = 8m+g, col = 8j+2t; scalar rows: k = 8 MTD + r, col = 8j+g
+    double* po = q.partial + (size_t)blockIdx.x * (8 * MT) * q.ncols;
+#pragma unroll
+    for (int m = 0; m < MTD; m++)
+        *reinterpret_cast<double2*>(po + (size_t)(8 * m + g) * q.ncols + 8 * j + 2 * t) = make_double2(acc[m][0], acc[m][1]);
+#pragma unroll
+    for (int r = 0; r < KS; r++) {
+        double v = accS[r];
+        v += __shfl_xor_sync(0xffffffffu, v, 1);
+        v += __shfl_xor_sync(0xffffffffu, v, 2);
+        if (t == 0) po[(size_t)(8 * MTD + r) * q.ncols + 8 * j + g] = v;
+    }
+    if (KS > 0 && t != 0) {   // rows K .. 8 MT - 1 of the scalar block are padding: keep them zero
+        for (int r = KS + t - 1; r < 8; r += 3) po[(size_t)(8 * MTD + r) * q.ncols + 8 * j + g] = 0.0;
     }
 }
 
@@ -283,53 +351,26 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
             if (__any_sync(0xffffffffu, R.invc != 0.0)) R.variant = kCons0 | kCons2 | kInvc;
             else R.variant = (zero1 ? kZero1 : 0) | ((cons0 || (!zero1 && cons1)) ? kCons0 : 0) | (cons2 ? kCons2 : 0);
         }
-        double acc[MTD > 0 ? MTD : 1][2];
-        double accS[KS > 0 ? KS : 1];
-#pragma unroll
-        for (int m = 0; m < (MTD > 0 ? MTD : 1); m++) acc[m][0] = acc[m][1] = 0.0;
-#pragma unroll
-        for (int r = 0; r < (KS > 0 ? KS : 1); r++) accS[r] = 0.0;
-        double* const vrow = q.Vout + (size_t)(R.row_ok ? i : 0) * q.Npad;
-
-        int stage = 0, sphase = 0;
-        int it = 0;
-        for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, it++) {
-            const int b = it & 1;
-            const uint32_t par = (uint32_t)((it >> 1) & 1);
-            mbar_wait(&cready[b], par);                   // C^ and x~ of this tile are in place
-            mbar_wait(&rfull[stage], (uint32_t)sphase);   // spot row (landed long ago; makes the async-proxy writes visible here)
-            mbar_wait(&vfull[b], par);                    // V_next tile
-            const double* sC = reinterpret_cast<const double*>(sm + L.c) + (size_t)b * GnP * TP;
-            const double* sV = reinterpret_cast<const double*>(sm + L.vn) + (size_t)b * GnP * (TP + 4);
-            const double* sS = reinterpret_cast<const double*>(sm + L.raw + (size_t)stage * L.stage + L.o_sp);
-            const double* sX = reinterpret_cast<const double*>(sm + L.xt) + (size_t)b * 8 * MT * TP;
-            double* out = vrow + tile * TP;
-#if LSMC_ABLATE != 5
-            switch (R.variant) {
-#define VARIANT(f) case f: decide_tile<TP, MTD, KS, f>(R, sC, sV, sS, sX, out, q.df, g, t, acc, accS); break;
-                VARIANT(0) VARIANT(1) VARIANT(2) VARIANT(3) VARIANT(4) VARIANT(5) VARIANT(6) VARIANT(7)
-                default: decide_tile<TP, MTD, KS, kCons0 | kCons2 | kInvc>(R, sC, sV, sS, sX, out, q.df, g, t, acc, accS); break;
+        // the warp's selection table: (w_lo, w_hi) and byte offsets of the interpolation rows in the V_next tile, per (decision, row)
+        if (t < 3) {
+            unsigned char* lut = sm + L.lut + (size_t)j * kLutBytes;
+            reinterpret_cast<double2*>(lut)[t * 8 + g] = make_double2(t == 0 ? R.wl[0] : t == 1 ? R.wl[1] : R.wl[2], t == 0 ? R.wh[0] : t == 1 ? R.wh[1] : R.wh[2]);
+            const int rl = t == 0 ? R.rL[0] : t == 1 ? R.rL[1] : R.rL[2], rh = t == 0 ? R.rH[0] : t == 1 ? R.rH[1] : R.rH[2];
+            reinterpret_cast<int2*>(lut + 24 * 16)[t * 8 + g] = make_int2(rl * (TP + 4) * 8, rh * (TP + 4) * 8);
+        }
+        __syncwarp();
+        const Pipe4 P{sm, vfull, cready, dfree, rfull};
+#if AB_NO_DECIDE
+        decision_loop_empty(q, P, TP);
+#else
+        if ((LSMC_ABLATE == 13 && j >= 7) || (LSMC_ABLATE == 14 && (j & 3) != 0)) { decision_loop_empty(q, P, TP); return; }
+        switch (R.variant) {
+#define VARIANT(f) case f: decision_loop<TP, MTD, KS, f>(q, L, P, R, j, g, t); break;
+            VARIANT(0) VARIANT(1) VARIANT(2) VARIANT(3) VARIANT(4) VARIANT(5) VARIANT(6) VARIANT(7)
+            default: decision_loop<TP, MTD, KS, kCons0 | kCons2 | kInvc>(q, L, P, R, j, g, t); break;
 #undef VARIANT
-            }
+        }
 #endif
-            mbar_arrive(&dfree[b]);
-            if (++stage == kRawStages) { stage = 0; sphase ^= 1; }
-        }
-        // per-CTA partial: partial[cta][k][col]; DMMA blocks: k = 8m+g, col = 8j+2t; scalar rows: k = 8 MTD + r, col = 8j+g
-        double* po = q.partial + (size_t)blockIdx.x * (8 * MT) * q.ncols;
-#pragma unroll
-        for (int m = 0; m < MTD; m++)
-            *reinterpret_cast<double2*>(po + (size_t)(8 * m + g) * q.ncols + 8 * j + 2 * t) = make_double2(acc[m][0], acc[m][1]);
-#pragma unroll
-        for (int r = 0; r < KS; r++) {
-            double v = accS[r];
-            v += __shfl_xor_sync(0xffffffffu, v, 1);
-            v += __shfl_xor_sync(0xffffffffu, v, 2);
-            if (t == 0) po[(size_t)(8 * MTD + r) * q.ncols + 8 * j + g] = v;
-        }
-        if (KS > 0 && t != 0) {   // rows K .. 8 MT - 1 of the scalar block are padding: keep them zero
-            for (int r = KS + t - 1; r < 8; r += 3) po[(size_t)(8 * MTD + r) * q.ncols + 8 * j + g] = 0.0;
-        }
     } else {
         // ============================================== aux warps ==============================================
         const int aw = warp - kDecWarps;
@@ -369,7 +410,7 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
         const uint32_t vn_bytes = (uint32_t)((size_t)q.Gn * (TP + 4) * 8), raw_bytes = (uint32_t)(2 * (F + 1) * ROW);
         auto produce_vn = [&](int64_t tile, int b) {
             mbar_expect_tx(&vfull[b], vn_bytes);
-            tma_2d(sm + L.vn + (size_t)b * GnP * (TP + 4) * 8, &mapV, (int)(tile * TP), 0, &vfull[b]);
+            tma_2d(sm + L.vn + (size_t)b * L.vn_buf, &mapV, (int)(tile * TP), 0, &vfull[b]);
         };
         auto produce_raw = [&](int64_t tile, int s) {
             unsigned char* st = sm + L.raw + (size_t)s * L.stage;
@@ -418,8 +459,7 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
             aux_bar();
 
             double* sC = reinterpret_cast<double*>(sm + L.c) + (size_t)b * GnP * TP;
-#if LSMC_ABLATE != 6
-            if (aw == 0) {
+            if (aw == 0 && !AB_NO_XT) {
                 // ---- x~ = T^T x_{p-1} on the tensor pipe, then X~^T X~ ----
                 double* xt = reinterpret_cast<double*>(sm + L.xt) + (size_t)b * 8 * MT * TP;
                 const double* pm[KSTEPS];
@@ -457,7 +497,7 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
                 }
             }
             // ---- fitted continuation values C^[l][n] = beta_l . x_p[n] on the FP64 tensor pipe ----
-            {
+            if (!AB_NO_FIT) {
                 const double* pp[KSTEPS];
 #pragma unroll
                 for (int ks = 0; ks < KSTEPS; ks++) pp[ks] = resolve(descP[ks]) + g;
@@ -489,7 +529,6 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
                     }
                 }
             }
-#endif
             mbar_arrive(&cready[b]);
             if (++stage == kRawStages) { stage = 0; sphase ^= 1; }
         }
