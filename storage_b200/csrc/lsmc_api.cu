@@ -2,6 +2,7 @@
 // Replaces the body of LsmcStorageValuation.Calculate<T> (LSV.cs:97-616) behind plain pointers and sizes.
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <dlfcn.h>
 #include <limits>
@@ -180,10 +181,11 @@ void set_problem(lsmc_ctx* c, const lsmc_problem* problem) {
             "inventory grid / basis too large for the sweep kernel's shared memory");
     require((pl.max_grid + 7) / 8 + c->MT <= sweep_max_items(), LSMC_EUNSUPPORTED, "inventory grid has too many points for the sweep kernel (about 200 at most)");
     const int64_t n_tiles = (c->N + c->TP - 1) / c->TP;
-    c->Npad = (c->N + 839) / 840 * 840;   // every tile's bulk copy stays inside a row for all tile sizes (lcm of 56, 40, 24)
+    c->Npad = (c->N + 3359) / 3360 * 3360;   // a multiple of every sweep tile size (lcm of 56, 48, 40, 32, 24)
     c->sweep_blocks = (int)std::min<int64_t>(c->num_sms, n_tiles);
     c->TP4 = sweep4_tile(pl.max_grid, pl.K, pl.F, (int)pl.basis.ops.size());
     c->sweep4_blocks = c->TP4 ? (int)std::min<int64_t>(c->num_sms, (c->N + c->TP4 - 1) / c->TP4) : 0;
+    if (const char* e = getenv("LSMC_SWEEP")) { if (atoi(e) == 3) c->TP4 = c->sweep4_blocks = 0; }   // development: force the general sweep kernel
     c->fwd_blocks = (int)std::min<int64_t>((int64_t)c->num_sms * (pl.K <= 16 ? 3 : 1), (c->N + 255) / 256);   // all CTAs resident: each walks every period
     c->ncols_max = 8 * ((pl.max_grid + 7) / 8 + c->MT);
 
@@ -354,12 +356,22 @@ void backward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
             if (q.accum_mode == 1) q.precond = c->precond.p + (size_t)(p - 1 - s0) * precond_stride(pl.K);
         }
         CUDA_CHECK(cudaEventRecord(c->event(ev_base), s));
-        const bool pipelined = c->TP4 != 0 && sweep4_covers(q);
-        const int n_parts = pipelined ? c->sweep4_blocks : c->sweep_blocks;
-        if (pipelined) CUDA_CHECK(launch_sweep4(q, c->TP4, (int)pl.basis.ops.size(), c->sweep4_blocks, s));
+        const bool use4 = c->TP4 != 0 && sweep4_covers(q);
+        DevBuf<long long> trace_buf;
+        const char* trace_path = getenv("LSMC_TRACE");   // development: phase timestamps of one mid-horizon sweep
+        const bool trace_now = trace_path && use4 && p == P / 2;
+        if (trace_now) { trace_buf.alloc(16 * 64 * 8); CUDA_CHECK(cudaMemsetAsync(trace_buf.p, 0, 16 * 64 * 8 * sizeof(long long), s)); q.trace = trace_buf.p; }
+        const int n_parts = use4 ? c->sweep4_blocks : c->sweep_blocks;
+        if (use4) CUDA_CHECK(launch_sweep4(q, c->TP4, (int)pl.basis.ops.size(), c->sweep4_blocks, s));
         else CUDA_CHECK(launch_sweep(q, cfg, s));
         CUDA_CHECK(cudaEventRecord(c->event(ev_base + 1), s));
         ev_base += 2;
+        if (trace_now) {
+            std::vector<long long> h(16 * 64 * 8);
+            CUDA_CHECK(cudaMemcpyAsync(h.data(), trace_buf.p, h.size() * sizeof(long long), cudaMemcpyDeviceToHost, s));
+            CUDA_CHECK(cudaStreamSynchronize(s));
+            if (FILE* f = fopen(trace_path, "wb")) { fwrite(h.data(), sizeof(long long), h.size(), f); fclose(f); }
+        }
         c->tm.backward_sweep_launches++;
         c->tm.kernel_launches++;
         c->tm.sweep_bytes += (double)c->N * 8.0 * ((double)q.G + q.Gn + (q.mode == 0 && !is_current ? F + 1 : (q.mode == 1 ? 1 : 0)) + (q.accum_mode == 1 ? F + 1 : 0));

@@ -134,6 +134,7 @@ struct SweepParams {
     const double* precond;    // preconditioner of period p-1 (accum_mode 1): T [K][K] + flags [K]
     double* partial;          // [gridDim.x][8*MT][ncols] normal-equation partials
     int ncols;                // 8 * (ceil(G/8) + MT)
+    long long* trace;         // development (LSMC_TRACE): per-warp phase timestamps of CTA 0, [16][64][8]; NULL otherwise
 };
 
 struct PrecondParams {

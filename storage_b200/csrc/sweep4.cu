@@ -168,9 +168,14 @@ __device__ __forceinline__ void decision_loop(const SweepParams& q, const Layout
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, it++) {
         const int b = it & 1;
         const uint32_t par = (uint32_t)((it >> 1) & 1);
+        // development (LSMC_TRACE): phase timestamps of CTA 0, read by scripts/trace_report.py
+        long long* tr = (q.trace && blockIdx.x == 0 && it < 64 && (threadIdx.x & 31) == 0) ? q.trace + ((size_t)(threadIdx.x >> 5) * 64 + it) * 8 : nullptr;
+        if (tr) tr[0] = clock64();
         mbar_wait(&P.cready[b], par);                   // C^ and x~ of this tile are in place
+        if (tr) tr[1] = clock64();
         mbar_wait(&P.rfull[stage], (uint32_t)sphase);   // spot row (landed long ago; makes the async-proxy writes visible here)
         mbar_wait(&P.vfull[b], par);                    // V_next tile
+        if (tr) tr[2] = clock64();
         const double* sC = reinterpret_cast<const double*>(P.sm + L.c) + (size_t)b * GnP * TP + 2 * t;
         const unsigned char* pV = P.sm + L.vn + (size_t)b * L.vn_buf + 16 * t;
         const double* pS = reinterpret_cast<const double*>(P.sm + L.raw + (size_t)stage * L.stage + L.o_sp) + 2 * t;
@@ -250,6 +255,7 @@ __device__ __forceinline__ void decision_loop(const SweepParams& q, const Layout
             phaseB(8 * (u - 1), pb0, pb1, pc0, pc1, pk0, pk1);
         }
         phaseB(8 * (NIT - 1), best0, best1, bc0, bc1, k0, k1);
+        if (tr) tr[3] = clock64();
         mbar_arrive(&P.dfree[b]);
         if (++stage == kRawStages) { stage = 0; sphase ^= 1; }
     }
@@ -427,20 +433,25 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
         if (aw == 0 && lane == 0 && (int64_t)blockIdx.x < n_tiles) produce_raw(blockIdx.x, 0);
         for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, it++) {
             const int b = it & 1;
+            long long* tr = (q.trace && blockIdx.x == 0 && it < 64 && lane == 0) ? q.trace + ((size_t)warp * 64 + it) * 8 : nullptr;
+            if (tr) tr[0] = clock64();
             // buffers b (V_next, C^, x~) were last used by tile it-2: wait until every decision warp has left it
             if (it >= 2) mbar_wait(&dfree[b], (uint32_t)(((it >> 1) + 1) & 1));
+            if (tr) tr[1] = clock64();
             if (aw == 0 && lane == 0) {
                 produce_vn(tile, b);
                 const int64_t nxt = tile + gridDim.x;
                 if (nxt < n_tiles) produce_raw(nxt, stage + 1 == kRawStages ? 0 : stage + 1);
             }
             mbar_wait(&rfull[stage], (uint32_t)sphase);
+            if (tr) tr[2] = clock64();
             const uint32_t rawoff = (uint32_t)(L.raw + (size_t)stage * L.stage);
             const uint32_t onesoff = (tile == n_tiles - 1) ? (uint32_t)(L.ones_last - L.ones) : 0u;
             auto resolve = [&](uint32_t d) -> const double* {
                 return reinterpret_cast<const double*>(sm + (d & kOffMask) + ((d & kRel) ? rawoff : 0u) + ((d & kOnes) ? onesoff : 0u));
             };
             aux_bar();   // the previous tile's readers of the product rows are done
+            if (tr) tr[5] = clock64();
 
             // ---- product nodes of the basis monomials: warp 14 period p, warp 15 period p-1 (lane = path) ----
             if (aw != 0) {
@@ -456,7 +467,9 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
                     }
                 }
             }
+            if (tr) tr[6] = clock64();
             aux_bar();
+            if (tr) tr[3] = clock64();
 
             double* sC = reinterpret_cast<double*>(sm + L.c) + (size_t)b * GnP * TP;
             if (aw == 0 && !AB_NO_XT) {
@@ -529,6 +542,7 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
                     }
                 }
             }
+            if (tr) tr[4] = clock64();
             mbar_arrive(&cready[b]);
             if (++stage == kRawStages) { stage = 0; sphase ^= 1; }
         }
