@@ -90,6 +90,19 @@ def measured_peak_gbs():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def ncu_traffic(config, n_local):
+    """dram__bytes_read.sum + dram__bytes_write.sum per sweep launch from the committed `ncu --set full` capture of this
+    workload (profiles/r01_sweep4_traffic.json); None when no capture exists for the configuration being run."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_sweep4_traffic.json")) as f:
+            for row in json.load(f)["captures"]:
+                if row["config"] == config and int(row["paths_per_gpu"]) == int(n_local):
+                    return float(row["dram_bytes_per_launch"])
+    except Exception:
+        pass
+    return None
+
+
 def problem_h2d_bytes(pb):
     total = 0
     for name in pb._F64 + pb._I32:
@@ -177,9 +190,10 @@ def main():
 
     n_local = args.paths_per_gpu or DEFAULT_PATHS[args.config]
     n_global = n_local * world
-    pb = build_config(args.config, num_sims=n_local)
-    pb.n_sims_global = n_global
-    pb.sim_offset = rank * n_local
+    from storage_b200.sharding import shard_problem
+    pb, shard = shard_problem(build_config(args.config, num_sims=n_global), world, rank)   # weak scaling: n_local paths on every rank
+    assert shard.count == n_local or n_local % 2, shard
+    n_local = shard.count
     T = pb.n_periods - 1
 
     ctx = _native.Context(local_rank)
@@ -203,15 +217,17 @@ def main():
     sampler = ClockSampler(local_rank)
     sampler.start()
     t0 = time.perf_counter()
-    sweep_ms = sweep_launches = launches = sweep_bytes = dev_ms = 0.0
+    sweep_ms = sweep_launches = launches = sweep_bytes = dev_ms = span_ms = 0.0
     for _ in range(args.steps):
         launches0 = ctx.timings()["kernel_launches"]
         device_step()
         tm = ctx.timings()
         sweep_ms += tm["backward_sweep_kernel_ms"]; sweep_launches += tm["backward_sweep_launches"]
         sweep_bytes += tm["sweep_bytes"]; dev_ms += tm["total_ms"]; launches += tm["kernel_launches"] - launches0
+        span_ms += tm["span_ms"]     # CUDA events on the library's stream: start of regression sim -> end of forward pass
     barrier()
-    elapsed = time.perf_counter() - t0
+    wall = time.perf_counter() - t0
+    elapsed = span_ms / 1e3
     clocks = sampler.summary()
     res_dev = ctx.get_results(_abi.Results(pb.n_periods, pb.n_sim_periods, n_local, pv_by_sim=False))
     phase = ctx.timings()
@@ -227,10 +243,12 @@ def main():
     barrier()
     e2e_elapsed = time.perf_counter() - t1
 
-    times = torch.tensor([elapsed, e2e_elapsed], dtype=torch.float64, device="cuda")
+    times = torch.tensor([elapsed, e2e_elapsed, wall], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
-    elapsed, e2e_elapsed = float(times[0]), float(times[1])
+    elapsed, e2e_elapsed, wall = float(times[0]), float(times[1]), float(times[2])
+    if not elapsed > 0.0:
+        raise SystemExit("bench.py: the library reported no device-event span for the timed steps")
 
     if rank == 0:
         ms_per_step = 1e3 * elapsed / args.steps
@@ -243,21 +261,26 @@ def main():
             "dtype": "f64", "data": "synthetic",
             "config": {"workload": CONFIG_TEXT[args.config], "config": args.config, "paths_per_gpu": n_local, "paths_total": n_global,
                        "periods": T, "factors": pb.n_factors, "basis_functions": pb.n_basis, "inventory_grid_points": 100,
-                       "rng": "device Philox4x32-10, antithetic", "timing": "wall clock between device synchronisations + barrier, max over ranks",
+                       "rng": "device Philox4x32-10, antithetic",
+                       "timing": "CUDA events on the library's stream (regression-sim start -> forward end of each step, summed over the K steps), "
+                                 "max over ranks; wall_ms_per_step is the host clock between barrier+synchronize on both sides",
                        "l2": "inputs larger than L2 (sim panels %.1f GB, value surfaces %.1f GB per GPU)" % (
                            8e-9 * n_local * pb.n_sim_periods * (pb.n_factors + 2), 16e-9 * n_local * 101)},
             "npv": res_dev.npv, "npv_std_error": res_dev.npv_std_error,
-            "device_ms_per_step": dev_ms / args.steps,
+            "wall_ms_per_step": 1e3 * wall / args.steps, "phase_sum_ms_per_step": dev_ms / args.steps,
             "phase_ms": {k: phase[k] for k in ("regression_sim_ms", "backward_ms", "valuation_sim_ms", "forward_ms")},
             "e2e": {"value": n_global * T / (e2e_elapsed / args.steps), "unit": "path-steps/s",
                     "h2d_bytes_per_step": problem_h2d_bytes(pb), "d2h_bytes_per_step": results_d2h_bytes(e2e_res),
                     "ms_per_step": 1e3 * e2e_elapsed / args.steps, "api": "lsmc_calculate (include/lsmc_b200.h) with host buffers"},
             "gpu_launches": int(launches),
             "clocks": clocks,
-            "roofline": {"kernel": "sweep_kernel (fused decision sweep + DMMA normal equations)", "bound": "hbm", "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+            "roofline": {"kernel": "sweep4_kernel (fused decision sweep + regression fit + DMMA normal equations, one launch per period)",
+                         "bound": "hbm", "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic(args.config, n_local), "peak_source": peak_src,
                          "launches": int(sweep_launches), "avg_launch_ms": sweep_ms / max(1.0, sweep_launches),
-                         "share_of_step": sweep_ms / max(1e-9, dev_ms)},
+                         "algorithmic_bytes_per_launch": sweep_bytes / max(1.0, sweep_launches),
+                         "share_of_step": sweep_ms / max(1e-9, span_ms),
+                         "note": "FP64 pipe (DFMA+DMMA share it, 64 lanes/clk/SM measured) is the co-binding roof: see DESIGN.md 4.1"},
         }
         if not args.no_cpu_baseline:
             cpu_paths = args.cpu_paths or {"c1": 1000, "c2": 20000, "c3": 8192, "c4": 2048, "c5": 4096}[args.config]

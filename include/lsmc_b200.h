@@ -169,6 +169,8 @@ typedef struct lsmc_timings {
     int64_t backward_sweep_launches;
     int64_t kernel_launches;           /* all kernels launched since lsmc_set_problem */
     double sweep_bytes;                /* algorithmic HBM bytes moved by the sweep kernels */
+    double span_ms;                    /* one CUDA-event interval from the start of the regression simulation to the end of the
+                                          forward pass on the context's stream (phase gaps included); 0 until all four phases ran */
 } lsmc_timings;
 
 typedef struct lsmc_ctx lsmc_ctx;

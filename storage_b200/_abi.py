@@ -60,7 +60,7 @@ class LsmcTimings(C.Structure):
     _fields_ = [("regression_sim_ms", C.c_double), ("backward_ms", C.c_double), ("valuation_sim_ms", C.c_double),
                 ("forward_ms", C.c_double), ("total_ms", C.c_double), ("backward_sweep_kernel_ms", C.c_double),
                 ("backward_solve_kernel_ms", C.c_double), ("backward_sweep_launches", C.c_int64),
-                ("kernel_launches", C.c_int64), ("sweep_bytes", C.c_double)]
+                ("kernel_launches", C.c_int64), ("sweep_bytes", C.c_double), ("span_ms", C.c_double)]
 
 
 PROGRESS_CB = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_double)

@@ -519,6 +519,9 @@ void forward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
     CUDA_CHECK(cudaEventElapsedTime(&ms, c->ev[4], c->ev[5])); c->tm.valuation_sim_ms = ms;
     CUDA_CHECK(cudaEventElapsedTime(&ms, c->ev[6], c->ev[7])); c->tm.forward_ms = ms;
     c->tm.total_ms = c->tm.regression_sim_ms + c->tm.backward_ms + c->tm.valuation_sim_ms + c->tm.forward_ms;
+    c->tm.span_ms = 0.0;
+    if (c->ev.size() > 7 && c->ev[0] && c->ev[7] && cudaEventElapsedTime(&ms, c->ev[0], c->ev[7]) == cudaSuccess && ms > 0.f) c->tm.span_ms = ms;
+    else (void)cudaGetLastError();   // regression set injected / simulated before an earlier forward pass: no span
     c->forward_done = true;
     if (cb) cb(user, 1.0);   // LSV.cs:604
 }
