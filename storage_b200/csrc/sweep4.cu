@@ -21,6 +21,7 @@
 // The warps of one SM sub-partition are 4 decision warps, or 3 decision warps + 1 aux warp: the FP64 pipe — which,
 // not HBM, is the tighter bound of this kernel — carries about the same load on all four.
 #include <cuda.h>
+#include <type_traits>
 
 #include "kernels.h"
 
@@ -68,6 +69,7 @@ constexpr int kAuxWarps = 3;
 constexpr int kRawStages = 3;
 constexpr int kMaxProd = 32;           // product nodes of the basis program
 constexpr int kLutBytes = 24 * 16 + 24 * 8;
+constexpr int kElemReg = 6;          // product elements per aux lane kept as register descriptors
 constexpr int kFitTiles = 6;           // C^ row blocks per fit warp (warps 14, 15; warp 13 takes the 13th)
 
 __host__ __device__ inline size_t al128(size_t b) { return (b + 127) & ~(size_t)127; }
@@ -296,6 +298,7 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
     __shared__ uint64_t vfull[2], cready[2], dfree[2], rfull[kRawStages];
     __shared__ uint32_t sNode[2][3 + kMaxFactors + kMaxProd];   // row descriptor of every node, per period (0: p, 1: p-1)
     __shared__ uint32_t sOpA[2][kMaxProd], sOpB[2][kMaxProd], sOpD[2][kMaxProd];
+    __shared__ int sWaveEnd[kMaxProd + 1], sNWaves;   // product nodes in waves of mutually independent multiplies
 
     const int NT = (q.G + 7) >> 3;                 // decision warps in use
     const int64_t n_tiles = (q.N + TP - 1) / TP;
@@ -326,6 +329,16 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
         for (int b = 0; b < 2; b++) { mbar_init(&vfull[b], 1); mbar_init(&cready[b], kAuxWarps * 32); mbar_init(&dfree[b], NT * 32); }
         for (int s = 0; s < kRawStages; s++) mbar_init(&rfull[s], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        // a wave ends before the first node that reads a node of the same wave (host_plan.cpp compile_basis emits operands first)
+        int nw = 0, w0 = 0;
+        for (int o = 0; o < n_prod; o++) {
+            const BasisOpDev op = bd->ops[o];
+            bool dep = false;
+            for (int e = w0; e < o; e++) dep = dep || bd->ops[e].dst == op.a || bd->ops[e].dst == op.b;
+            if (dep) { sWaveEnd[nw++] = o; w0 = o; }
+        }
+        if (n_prod > 0) sWaveEnd[nw++] = n_prod;
+        sNWaves = nw;
     }
     __syncthreads();
 
@@ -380,39 +393,8 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
     } else {
         // ============================================== aux warps ==============================================
         const int aw = warp - kDecWarps;
+        const int alane = aw * 32 + lane;
         const int n_mt = GnP >> 3;                      // 8-row blocks of fitted values
-        // fit blocks: warp 14 -> 0..5, warp 15 -> 6..11, warp 13 -> 12
-        const int mt_base = aw == 0 ? 2 * kFitTiles : (aw - 1) * kFitTiles;
-        const int mt_cnt = max(0, min(n_mt - mt_base, aw == 0 ? 1 : kFitTiles));
-        // beta fragments (DMMA A operand: A[g][t] = beta[8 mt + g][4 ks + t]) stay in registers for the whole launch
-        double bfrag[kFitTiles][KSTEPS];
-#pragma unroll
-        for (int mi = 0; mi < kFitTiles; mi++)
-#pragma unroll
-            for (int ks = 0; ks < KSTEPS; ks++)
-                bfrag[mi][ks] = (mi < mt_cnt) ? __ldg(q.beta + (size_t)(8 * (mt_base + mi) + g) * q.ldb + 4 * ks + t) : 0.0;
-        // descriptors of the basis rows this lane feeds as DMMA B operand: B[t][g] = x[4 ks + t][8 nt + g]
-        uint32_t descP[KSTEPS], descM[KSTEPS];
-#pragma unroll
-        for (int ks = 0; ks < KSTEPS; ks++) {
-            const int k = 4 * ks + t;
-            descP[ks] = (k < K) ? sNode[0][bd->node_of_basis[k]] : (uint32_t)L.zero;
-            descM[ks] = (k < K) ? sNode[1][bd->node_of_basis[k]] : (uint32_t)L.zero;
-        }
-        // warp 13: T^T fragments (A[g][t] = T[4 ks + t][8 m + g]) and the Gram accumulators
-        double tfrag[MT][KSTEPS];
-        double xacc[2][MT][MT][2];   // two sets (even / odd iterations) halve the dependent DMMA chains
-#pragma unroll
-        for (int m = 0; m < MT; m++) {
-#pragma unroll
-            for (int ks = 0; ks < KSTEPS; ks++) {
-                const int i2 = 4 * ks + t, j2 = 8 * m + g;
-                tfrag[m][ks] = (aw == 0 && i2 < K && j2 < K) ? __ldg(q.precond + (size_t)i2 * K + j2) : 0.0;
-            }
-#pragma unroll
-            for (int n = 0; n < MT; n++) xacc[0][m][n][0] = xacc[0][m][n][1] = xacc[1][m][n][0] = xacc[1][m][n][1] = 0.0;
-        }
-
         const uint32_t vn_bytes = (uint32_t)((size_t)q.Gn * (TP + 4) * 8), raw_bytes = (uint32_t)(2 * (F + 1) * ROW);
         auto produce_vn = [&](int64_t tile, int b) {
             mbar_expect_tx(&vfull[b], vn_bytes);
@@ -427,133 +409,217 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
             tma_2d(st + L.o_sm, &mapSm, c0, 0, &rfull[s]);
             tma_2d(st + L.o_fm, &mapFm, c0, 0, &rfull[s]);
         };
-
-        int stage = 0, sphase = 0;
-        int it = 0;
-        if (aw == 0 && lane == 0 && (int64_t)blockIdx.x < n_tiles) produce_raw(blockIdx.x, 0);
-        for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, it++) {
-            const int b = it & 1;
-            long long* tr = (q.trace && blockIdx.x == 0 && it < 64 && lane == 0) ? q.trace + ((size_t)warp * 64 + it) * 8 : nullptr;
-            if (tr) tr[0] = clock64();
-            // buffers b (V_next, C^, x~) were last used by tile it-2: wait until every decision warp has left it
-            if (it >= 2) mbar_wait(&dfree[b], (uint32_t)(((it >> 1) + 1) & 1));
-            if (tr) tr[1] = clock64();
-            if (aw == 0 && lane == 0) {
-                produce_vn(tile, b);
-                const int64_t nxt = tile + gridDim.x;
-                if (nxt < n_tiles) produce_raw(nxt, stage + 1 == kRawStages ? 0 : stage + 1);
-            }
-            mbar_wait(&rfull[stage], (uint32_t)sphase);
-            if (tr) tr[2] = clock64();
-            const uint32_t rawoff = (uint32_t)(L.raw + (size_t)stage * L.stage);
-            const uint32_t onesoff = (tile == n_tiles - 1) ? (uint32_t)(L.ones_last - L.ones) : 0u;
-            auto resolve = [&](uint32_t d) -> const double* {
-                return reinterpret_cast<const double*>(sm + (d & kOffMask) + ((d & kRel) ? rawoff : 0u) + ((d & kOnes) ? onesoff : 0u));
-            };
-            aux_bar();   // the previous tile's readers of the product rows are done
-            if (tr) tr[5] = clock64();
-
-            // ---- product nodes of the basis monomials: warp 14 period p, warp 15 period p-1 (lane = path) ----
-            if (aw != 0) {
-                const int sel = aw - 1;
-                for (int o = 0; o < n_prod; o++) {
-                    const double* pa = resolve(sOpA[sel][o]);
-                    const double* pb = resolve(sOpB[sel][o]);
-                    double* pd = reinterpret_cast<double*>(sm + sOpD[sel][o]);
+        // Product nodes of the basis monomials (both periods): when they form one wave of mutually independent
+        // multiplies, every aux lane keeps its (period, node, path) elements as packed descriptors in registers
+        // (operand offsets / 8 in 15 bits each + "relative to the raw stage" flags; destination byte offset), so a tile's
+        // products are one round of independent loads, multiplies and stores.  Lanes without an element multiply the
+        // zero row into itself.
+        const int n_waves = sNWaves, tot_el = 2 * n_prod * TP;
+        bool fastprod = n_waves <= 1 && tot_el <= 96 * kElemReg;
+        for (int o = 0; o < n_prod; o++) fastprod = fastprod && !((sOpA[0][o] | sOpB[0][o]) & kOnes);
+        uint32_t eAB[kElemReg], eD[kElemReg];
 #pragma unroll
-                    for (int c = 0; c < (TP + 31) / 32; c++) {
-                        const int path = lane + 32 * c;
-                        if (path < TP) pd[path] = mul_rn(pa[path], pb[path]);
+        for (int e = 0; e < kElemReg; e++) {
+            const int idx = alane + 96 * e;
+            uint32_t da = (uint32_t)L.zero, db = (uint32_t)L.zero, dd = (uint32_t)L.zero;
+            if (fastprod && idx < tot_el) {
+                const int pair = idx / TP, path = idx - pair * TP;
+                const int sel = pair >= n_prod ? 1 : 0, o = pair - sel * n_prod;
+                da = sOpA[sel][o] + 8u * path; db = sOpB[sel][o] + 8u * path; dd = sOpD[sel][o] + 8u * path;
+            }
+            eAB[e] = ((da & kOffMask) >> 3) | ((da & kRel) ? 0x8000u : 0u) | (((db & kOffMask) >> 3) << 16) | ((db & kRel) ? 0x80000000u : 0u);
+            eD[e] = dd;
+        }
+
+        // One tile loop per role, so that the register-resident fragments of one role are not live in the other.
+        auto run = [&](auto role) {
+            constexpr int ROLE = decltype(role)::value;   // 0: warp 13 (copies, x~, Gram, last fit block); 1: warps 14, 15 (fit)
+            // fit blocks: warp 14 -> 0..5, warp 15 -> 6..11, warp 13 -> 12
+            constexpr int NB = ROLE == 0 ? 1 : kFitTiles;
+            const int mt_base = ROLE == 0 ? 2 * kFitTiles : (aw - 1) * kFitTiles;
+            const int mt_cnt = max(0, min(n_mt - mt_base, NB));
+            // beta fragments (DMMA A operand: A[g][t] = beta[8 mt + g][4 ks + t]) stay in registers for the whole launch
+            double bfrag[NB][KSTEPS];
+#pragma unroll
+            for (int mi = 0; mi < NB; mi++)
+#pragma unroll
+                for (int ks = 0; ks < KSTEPS; ks++)
+                    bfrag[mi][ks] = (mi < mt_cnt) ? __ldg(q.beta + (size_t)(8 * (mt_base + mi) + g) * q.ldb + 4 * ks + t) : 0.0;
+            // descriptors of the basis rows this lane feeds as DMMA B operand: B[t][g] = x[4 ks + t][8 nt + g]
+            uint32_t descP[KSTEPS], descM[KSTEPS];
+#pragma unroll
+            for (int ks = 0; ks < KSTEPS; ks++) {
+                const int k = 4 * ks + t;
+                descP[ks] = (k < K) ? sNode[0][bd->node_of_basis[k]] : (uint32_t)L.zero;
+                descM[ks] = (k < K && ROLE == 0) ? sNode[1][bd->node_of_basis[k]] : (uint32_t)L.zero;
+            }
+            // warp 13: T^T fragments (A[g][t] = T[4 ks + t][8 m + g]) and the Gram accumulators
+            constexpr int MTX = ROLE == 0 ? MT : 1;
+            double tfrag[MTX][KSTEPS];
+            double xacc[MTX][MTX][2];
+#pragma unroll
+            for (int m = 0; m < MTX; m++) {
+#pragma unroll
+                for (int ks = 0; ks < KSTEPS; ks++) {
+                    const int i2 = 4 * ks + t, j2 = 8 * m + g;
+                    tfrag[m][ks] = (ROLE == 0 && i2 < K && j2 < K) ? __ldg(q.precond + (size_t)i2 * K + j2) : 0.0;
+                }
+#pragma unroll
+                for (int n = 0; n < MTX; n++) xacc[m][n][0] = xacc[m][n][1] = 0.0;
+            }
+
+            int stage = 0, sphase = 0;
+            int it = 0;
+            if (ROLE == 0 && lane == 0 && (int64_t)blockIdx.x < n_tiles) produce_raw(blockIdx.x, 0);
+            for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, it++) {
+                const int b = it & 1;
+                long long* tr = (q.trace && blockIdx.x == 0 && it < 64 && lane == 0) ? q.trace + ((size_t)warp * 64 + it) * 8 : nullptr;
+                if (tr) tr[0] = clock64();
+                // buffers b (V_next, C^, x~) were last used by tile it-2: wait until every decision warp has left it
+                if (it >= 2) mbar_wait(&dfree[b], (uint32_t)(((it >> 1) + 1) & 1));
+                if (tr) tr[1] = clock64();
+                if (ROLE == 0 && lane == 0) {
+                    produce_vn(tile, b);
+                    const int64_t nxt = tile + gridDim.x;
+                    if (nxt < n_tiles) produce_raw(nxt, stage + 1 == kRawStages ? 0 : stage + 1);
+                }
+                mbar_wait(&rfull[stage], (uint32_t)sphase);
+                if (tr) tr[2] = clock64();
+                const uint32_t rawoff = (uint32_t)(L.raw + (size_t)stage * L.stage);
+                const uint32_t onesoff = (tile == n_tiles - 1) ? (uint32_t)(L.ones_last - L.ones) : 0u;
+                auto resolve = [&](uint32_t d) -> const double* {
+                    return reinterpret_cast<const double*>(sm + (d & kOffMask) + ((d & kRel) ? rawoff : 0u) + ((d & kOnes) ? onesoff : 0u));
+                };
+                aux_bar();   // the previous tile's readers of the product rows are done
+                if (tr) tr[5] = clock64();
+
+                // ---- product nodes ----
+                if (fastprod) {
+                    double va[kElemReg], vb[kElemReg];
+#pragma unroll
+                    for (int e = 0; e < kElemReg; e++) {
+                        const uint32_t w = eAB[e];
+                        va[e] = *reinterpret_cast<const double*>(sm + ((w & 0x7fffu) << 3) + ((w & 0x8000u) ? rawoff : 0u));
+                        vb[e] = *reinterpret_cast<const double*>(sm + (((w >> 16) & 0x7fffu) << 3) + ((w & 0x80000000u) ? rawoff : 0u));
+                    }
+#pragma unroll
+                    for (int e = 0; e < kElemReg; e++) *reinterpret_cast<double*>(sm + eD[e]) = mul_rn(va[e], vb[e]);
+                } else {
+                    // general programs: wave by wave, the 96 aux lanes share the (period, node, path) elements of a wave
+                    int o0 = 0;
+                    for (int w = 0; w < n_waves; w++) {
+                        const int o1 = sWaveEnd[w], nw = o1 - o0, total = 2 * nw * TP;
+                        for (int idx = alane; idx < total; idx += 96) {
+                            const int pair = idx / TP, path = idx - pair * TP;
+                            const int sel = pair >= nw ? 1 : 0, o = o0 + pair - sel * nw;
+                            reinterpret_cast<double*>(sm + sOpD[sel][o])[path] = mul_rn(resolve(sOpA[sel][o])[path], resolve(sOpB[sel][o])[path]);
+                        }
+                        o0 = o1;
+                        if (w + 1 < n_waves) aux_bar();
                     }
                 }
-            }
-            if (tr) tr[6] = clock64();
-            aux_bar();
-            if (tr) tr[3] = clock64();
+                if (tr) tr[6] = clock64();
+                aux_bar();
+                if (tr) tr[3] = clock64();
 
-            double* sC = reinterpret_cast<double*>(sm + L.c) + (size_t)b * GnP * TP;
-            if (aw == 0 && !AB_NO_XT) {
-                // ---- x~ = T^T x_{p-1} on the tensor pipe, then X~^T X~ ----
-                double* xt = reinterpret_cast<double*>(sm + L.xt) + (size_t)b * 8 * MT * TP;
-                const double* pm[KSTEPS];
-#pragma unroll
-                for (int ks = 0; ks < KSTEPS; ks++) pm[ks] = resolve(descM[ks]) + g;
-#pragma unroll
-                for (int nt = 0; nt < TP / 8; nt++) {
-                    double bop[KSTEPS], cx[MT][2];
-#pragma unroll
-                    for (int ks = 0; ks < KSTEPS; ks++) bop[ks] = pm[ks][8 * nt];
-#pragma unroll
-                    for (int m = 0; m < MT; m++) cx[m][0] = cx[m][1] = 0.0;
-#pragma unroll
-                    for (int ks = 0; ks < KSTEPS; ks++)
-#pragma unroll
-                        for (int m = 0; m < MT; m++) dmma8x8x4(cx[m][0], cx[m][1], tfrag[m][ks], bop[ks]);
-#pragma unroll
-                    for (int m = 0; m < MT; m++)
-                        *reinterpret_cast<double2*>(xt + (size_t)(8 * m + g) * TP + 8 * nt + 2 * t) = make_double2(cx[m][0], cx[m][1]);
-                }
-                __syncwarp();
-                const double* px = xt + (size_t)g * TP + 2 * t;
-#pragma unroll
-                for (int u8 = 0; u8 < TP; u8 += 8) {
-                    double2 f2[MT];
-#pragma unroll
-                    for (int m = 0; m < MT; m++) f2[m] = lds128(px + (size_t)8 * m * TP + u8);
-#pragma unroll
-                    for (int m = 0; m < MT; m++)
-#pragma unroll
-                        for (int n = 0; n < MT; n++) {
-                            dmma8x8x4(xacc[0][m][n][0], xacc[0][m][n][1], f2[m].x, f2[n].x);
-                            dmma8x8x4(xacc[1][m][n][0], xacc[1][m][n][1], f2[m].y, f2[n].y);
-                        }
-                }
-            }
-            // ---- fitted continuation values C^[l][n] = beta_l . x_p[n] on the FP64 tensor pipe ----
-            if (!AB_NO_FIT) {
+                double* sC = reinterpret_cast<double*>(sm + L.c) + (size_t)b * GnP * TP;
                 const double* pp[KSTEPS];
 #pragma unroll
                 for (int ks = 0; ks < KSTEPS; ks++) pp[ks] = resolve(descP[ks]) + g;
                 double* crow = sC + (size_t)(8 * mt_base + g) * TP + 2 * t;
-                if (aw != 0) {
-                    // six row blocks per warp: independent accumulator chains issued back to back, stores predicated
+                if constexpr (ROLE == 0) {
+                    if (!AB_NO_XT) {
+                        // ---- x~ = T^T x_{p-1} on the tensor pipe, then X~^T X~ ----
+                        double* xt = reinterpret_cast<double*>(sm + L.xt) + (size_t)b * 8 * MT * TP;
+                        const double* pm[KSTEPS];
+#pragma unroll
+                        for (int ks = 0; ks < KSTEPS; ks++) pm[ks] = resolve(descM[ks]) + g;
+                        double bnx[KSTEPS];   // B operands one step ahead of their use
+#pragma unroll
+                        for (int ks = 0; ks < KSTEPS; ks++) bnx[ks] = pm[ks][0];
+#pragma unroll
+                        for (int nt = 0; nt < TP / 8; nt++) {
+                            double bop[KSTEPS], cx[MT][2];
+#pragma unroll
+                            for (int ks = 0; ks < KSTEPS; ks++) { bop[ks] = bnx[ks]; if (nt + 1 < TP / 8) bnx[ks] = pm[ks][8 * (nt + 1)]; }
+#pragma unroll
+                            for (int m = 0; m < MT; m++) cx[m][0] = cx[m][1] = 0.0;
+#pragma unroll
+                            for (int ks = 0; ks < KSTEPS; ks++)
+#pragma unroll
+                                for (int m = 0; m < MT; m++) dmma8x8x4(cx[m][0], cx[m][1], tfrag[m][ks], bop[ks]);
+#pragma unroll
+                            for (int m = 0; m < MT; m++)
+                                *reinterpret_cast<double2*>(xt + (size_t)(8 * m + g) * TP + 8 * nt + 2 * t) = make_double2(cx[m][0], cx[m][1]);
+                        }
+                        __syncwarp();
+                        const double* px = xt + (size_t)g * TP + 2 * t;
+#pragma unroll
+                        for (int u8 = 0; u8 < TP; u8 += 8) {
+                            double2 f2[MT];
+#pragma unroll
+                            for (int m = 0; m < MT; m++) f2[m] = lds128(px + (size_t)8 * m * TP + u8);
+#pragma unroll
+                            for (int m = 0; m < MT; m++)
+#pragma unroll
+                                for (int n = 0; n < MT; n++) {
+                                    dmma8x8x4(xacc[m][n][0], xacc[m][n][1], f2[m].x, f2[n].x);
+                                    dmma8x8x4(xacc[m][n][0], xacc[m][n][1], f2[m].y, f2[n].y);
+                                }
+                        }
+                    }
+                    // ---- the last block of fitted values ----
+                    if (!AB_NO_FIT && mt_cnt > 0) {
+                        double bnx[KSTEPS];
+#pragma unroll
+                        for (int ks = 0; ks < KSTEPS; ks++) bnx[ks] = pp[ks][0];
+#pragma unroll
+                        for (int nt = 0; nt < TP / 8; nt++) {
+                            double bop[KSTEPS], c0 = 0.0, c1 = 0.0;
+#pragma unroll
+                            for (int ks = 0; ks < KSTEPS; ks++) { bop[ks] = bnx[ks]; if (nt + 1 < TP / 8) bnx[ks] = pp[ks][8 * (nt + 1)]; }
+#pragma unroll
+                            for (int ks = 0; ks < KSTEPS; ks++) dmma8x8x4(c0, c1, bfrag[0][ks], bop[ks]);
+                            *reinterpret_cast<double2*>(crow + 8 * nt) = make_double2(c0, c1);
+                        }
+                    }
+                } else if (!AB_NO_FIT) {
+                    // ---- fitted continuation values C^[l][n] = beta_l . x_p[n] on the FP64 tensor pipe: six row blocks per
+                    //      warp, independent accumulator chains issued back to back, stores predicated ----
+                    double bnx[KSTEPS];
+#pragma unroll
+                    for (int ks = 0; ks < KSTEPS; ks++) bnx[ks] = pp[ks][0];
 #pragma unroll
                     for (int nt = 0; nt < TP / 8; nt++) {
-                        double bop[KSTEPS], cf[kFitTiles][2];
+                        double bop[KSTEPS], cf[NB][2];
 #pragma unroll
-                        for (int ks = 0; ks < KSTEPS; ks++) bop[ks] = pp[ks][8 * nt];
+                        for (int ks = 0; ks < KSTEPS; ks++) { bop[ks] = bnx[ks]; if (nt + 1 < TP / 8) bnx[ks] = pp[ks][8 * (nt + 1)]; }
 #pragma unroll
-                        for (int mi = 0; mi < kFitTiles; mi++) cf[mi][0] = cf[mi][1] = 0.0;
+                        for (int mi = 0; mi < NB; mi++) cf[mi][0] = cf[mi][1] = 0.0;
 #pragma unroll
                         for (int ks = 0; ks < KSTEPS; ks++)
 #pragma unroll
-                            for (int mi = 0; mi < kFitTiles; mi++) dmma8x8x4(cf[mi][0], cf[mi][1], bfrag[mi][ks], bop[ks]);
+                            for (int mi = 0; mi < NB; mi++) dmma8x8x4(cf[mi][0], cf[mi][1], bfrag[mi][ks], bop[ks]);
 #pragma unroll
-                        for (int mi = 0; mi < kFitTiles; mi++)
+                        for (int mi = 0; mi < NB; mi++)
                             if (mi < mt_cnt) *reinterpret_cast<double2*>(crow + (size_t)8 * mi * TP + 8 * nt) = make_double2(cf[mi][0], cf[mi][1]);
                     }
-                } else if (mt_cnt > 0) {
-#pragma unroll
-                    for (int nt = 0; nt < TP / 8; nt++) {
-                        double c0 = 0.0, c1 = 0.0;
-#pragma unroll
-                        for (int ks = 0; ks < KSTEPS; ks++) dmma8x8x4(c0, c1, bfrag[0][ks], pp[ks][8 * nt]);
-                        *reinterpret_cast<double2*>(crow + 8 * nt) = make_double2(c0, c1);
-                    }
                 }
+                if (tr) tr[4] = clock64();
+                mbar_arrive(&cready[b]);
+                if (++stage == kRawStages) { stage = 0; sphase ^= 1; }
             }
-            if (tr) tr[4] = clock64();
-            mbar_arrive(&cready[b]);
-            if (++stage == kRawStages) { stage = 0; sphase ^= 1; }
-        }
-        if (aw == 0) {
-            double* po = q.partial + (size_t)blockIdx.x * (8 * MT) * q.ncols;
+            if constexpr (ROLE == 0) {
+                double* po = q.partial + (size_t)blockIdx.x * (8 * MT) * q.ncols;
 #pragma unroll
-            for (int m = 0; m < MT; m++)
+                for (int m = 0; m < MT; m++)
 #pragma unroll
-                for (int n = 0; n < MT; n++)
-                    *reinterpret_cast<double2*>(po + (size_t)(8 * m + g) * q.ncols + 8 * (NT + n) + 2 * t) = make_double2(xacc[0][m][n][0] + xacc[1][m][n][0], xacc[0][m][n][1] + xacc[1][m][n][1]);
-        }
+                    for (int n = 0; n < MT; n++)
+                        *reinterpret_cast<double2*>(po + (size_t)(8 * m + g) * q.ncols + 8 * (NT + n) + 2 * t) = make_double2(xacc[m][n][0], xacc[m][n][1]);
+            }
+        };
+        if (aw == 0) run(std::integral_constant<int, 0>{});
+        else run(std::integral_constant<int, 1>{});
     }
 }
 
