@@ -13,7 +13,7 @@ $CMD > $OUT/plain_$TAG.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -s 1480 -c 1500 --csv --log-file $OUT/launches_$TAG.csv $CMD > $OUT/ncu_launch_$TAG.log 2>&1
 echo "launch list exit $?"
 $CMD > $OUT/plain_$TAG.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:sweep_kernel -s 500 -c 2 -o $OUT/sweep_$TAG -f $CMD > $OUT/ncu_sweep_$TAG.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:"sweep4_kernel|sweep_kernel" -s 500 -c 2 -o $OUT/sweep_$TAG -f $CMD > $OUT/ncu_sweep_$TAG.log 2>&1
 echo "sweep capture exit $?"
 $CMD > $OUT/plain_$TAG.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:"forward_kernel|simulate_kernel" -s 1 -c 3 -o $OUT/fwdsim_$TAG -f $CMD > $OUT/ncu_fwdsim_$TAG.log 2>&1

@@ -376,17 +376,27 @@ __device__ __forceinline__ double spline_dev(const double* x, const double* y, i
     return add_rn(y0, mul_rn(sub_rn(v, x0), slope));
 }
 
-// StorageHelper.BisectInventorySpace (SH.cs:280-314); returns false when outside the grid.
-__device__ __forceinline__ bool bisect_dev(const double* grid, int n, double inv, double tol, int& lo, int& hi) {
-    if (n == 1 && fabs(inv - __ldg(grid)) <= tol) { lo = hi = 0; return true; }
+#ifndef LSMC_FWD_MINB
+#define LSMC_FWD_MINB 3
+#endif
+constexpr int kFwdThreads = 256;
+
+// All periods [p0, p1) in one launch: a thread owns its paths for the whole pass (no cross-path dependence in the forward
+// simulation, LSV.cs:426-480), the per-period descriptors come from a device array.  Per period the CTA stages the
+// coefficient rows beta[Gn][K] (odd pitch: the rows a warp's lanes need are scattered over the grid) and the next grid in
+// shared memory; basis-program nodes live in a per-thread column of shared memory, the regressor row and the column sums
+// in registers (KT = compile-time bound of K; EXACT: K == KT).
+// StorageHelper.BisectInventorySpace (SH.cs:280-314) on the staged grid; returns false when outside the grid.
+__device__ __forceinline__ bool bisect_sm(const double* grid, int n, double inv, double tol, int& lo, int& hi) {
+    if (n == 1 && fabs(inv - grid[0]) <= tol) { lo = hi = 0; return true; }
     int left = 0, right = n - 1;
     const int top = right;
     while (right > left) {
         int mid = (left + right) >> 1;
-        double gm = __ldg(grid + mid);
+        double gm = grid[mid];
         if (fabs(inv - gm) <= tol) { lo = hi = mid; return true; }
         if (gm > inv) { right = mid; continue; }
-        double gn = __ldg(grid + mid + 1);
+        double gn = grid[mid + 1];
         if (inv <= gn) { lo = mid; hi = mid + 1; return true; }
         if (fabs(inv - gn) <= tol) { lo = hi = mid + 1; return true; }
         if (mid + 1 == top) return false;
@@ -395,16 +405,13 @@ __device__ __forceinline__ bool bisect_dev(const double* grid, int n, double inv
     return false;
 }
 
-constexpr int kFwdMaxDec = 16;
-constexpr int kFwdThreads = 256;
+__host__ __device__ constexpr int fwd_beta_pitch(int KT) { return KT | 1; }
 
-// All periods [p0, p1) in one launch: a thread owns its paths for the whole pass (no cross-path dependence in the forward
-// simulation, LSV.cs:426-480), the per-period descriptors come from a device array, basis-program nodes live in a
-// per-thread column of shared memory and the regressor row / column sums in registers (KT = compile-time bound of K).
-template <int KT>
-__global__ void __launch_bounds__(kFwdThreads, KT <= 16 ? 3 : 1) forward_kernel(const ForwardParams* __restrict__ pp, int p0, int p1) {
-    extern __shared__ double fsm[];   // [n_nodes][blockDim] node columns, [K][blockDim] column sums, [warps][nsum] reduction scratch
+template <int KT, bool EXACT>
+__global__ void __launch_bounds__(kFwdThreads, KT <= 16 ? LSMC_FWD_MINB : 1) forward_kernel(const ForwardParams* __restrict__ pp, int p0, int p1, int max_grid) {
+    extern __shared__ double fsm[];   // [n_nodes][blockDim] node columns, [max_grid][BP] beta, [max_grid] grid, [warps][nsum] reduction scratch
     __shared__ ForwardParams sq;
+    constexpr int BP = fwd_beta_pitch(KT);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
     for (int p = p0; p < p1; p++) {
         __syncthreads();
@@ -412,14 +419,23 @@ __global__ void __launch_bounds__(kFwdThreads, KT <= 16 ? 3 : 1) forward_kernel(
         __syncthreads();
         const ForwardParams& q = sq;
         const BasisDev* __restrict__ bd = q.basis;
-        const int K = q.K, nsum = kFwdSums + K;
+        const int K = EXACT ? KT : q.K, nsum = kFwdSums + K;
         double* nodes = fsm + tid;                                   // node j at nodes[j * blockDim.x]
-        double* xsum = nodes + (size_t)bd->n_nodes * blockDim.x;      // column k at xsum[k * blockDim.x]
-        double* red = fsm + (size_t)(bd->n_nodes + K) * blockDim.x;  // [warps][nsum]
-        double sums[kFwdSums];
+        double* beta_s = fsm + (size_t)bd->n_nodes * blockDim.x;     // row l at beta_s[l * BP]
+        double* grid_s = beta_s + (size_t)max_grid * BP;
+        double* red = grid_s + max_grid;                             // [warps][nsum]
+        {
+            const int Gn = q.Gn, nk = q.cont_mode == 1 ? 1 : K;
+            for (int l = warp; l < Gn; l += nwarps)
+                for (int k = lane; k < nk; k += 32) beta_s[l * BP + k] = __ldg(q.beta + (size_t)l * q.ldb + k);
+            for (int l = tid; l < Gn; l += blockDim.x) grid_s[l] = __ldg(q.next_grid + l);
+        }
+        __syncthreads();
+        double sums[kFwdSums], xsum[KT];
 #pragma unroll
         for (int i = 0; i < kFwdSums; i++) sums[i] = 0.0;
-        for (int k = 0; k < K; k++) xsum[(size_t)k * blockDim.x] = 0.0;
+#pragma unroll
+        for (int k = 0; k < KT; k++) xsum[k] = 0.0;
 
         const int64_t stride = (int64_t)gridDim.x * blockDim.x;
         for (int64_t n = (int64_t)blockIdx.x * blockDim.x + tid; n < q.N; n += stride) {
@@ -436,7 +452,7 @@ __global__ void __launch_bounds__(kFwdThreads, KT <= 16 ? 3 : 1) forward_kernel(
 #pragma unroll
                 for (int k = 0; k < KT; k++) {
                     xrow[k] = (k < K) ? nodes[(size_t)bd->node_of_basis[k] * blockDim.x] : 0.0;
-                    if (k < K) xsum[(size_t)k * blockDim.x] += xrow[k];
+                    if (k < K) xsum[k] += xrow[k];
                 }
             }
             // CmdtyStorage.GetInjectWithdrawRange (CmdtyStorage.cs:86-100)
@@ -451,36 +467,32 @@ __global__ void __launch_bounds__(kFwdThreads, KT <= 16 ? 3 : 1) forward_kernel(
             }
             const double loss = mul_rn(q.loss_pct, v);
             // bang-bang decision set (SH.cs:109-197)
-            double dec[kFwdMaxDec];
+            // volume of decision d computed on demand (no per-thread array)
             int nd;
+            double w, jn, stepw = 0.0, stepj = 0.0;
+            bool one_sided;
             {
                 const double base = sub_rn(v, loss);
                 const double afterW = add_rn(rmin, base), afterJ = add_rn(rmax, base);
-                double w, jn;
                 if (afterW > q.next_max) { if (!(sub_rn(afterW, q.next_max) < q.tol)) atomicExch(q.error_flag, 3); w = sub_rn(q.next_max, base); }
                 else w = afterW > q.next_min ? rmin : sub_rn(q.next_min, base);
                 if (afterJ < q.next_min) { if (!(sub_rn(q.next_min, afterJ) < q.tol)) atomicExch(q.error_flag, 3); jn = sub_rn(q.next_min, base); }
                 else jn = afterJ < q.next_max ? rmax : sub_rn(q.next_max, base);
                 const int ex = q.extra;
-                if (ex == 0) {   // the common case stays in registers
-                    dec[0] = w;
-                    if (w >= 0.0 || jn <= 0.0) { nd = 2; dec[1] = jn; dec[2] = jn; }
-                    else { nd = 3; dec[1] = 0.0; dec[2] = jn; }
-                } else if (w >= 0.0 || jn <= 0.0) {
-                    nd = ex + 2;
-                    dec[0] = w;
-                    const double step = (jn - w) / (ex + 1);
-                    for (int i = 0; i < ex; i++) dec[1 + i] = add_rn(mul_rn((double)(i + 1), step), w);
-                    dec[nd - 1] = jn;
-                } else {
-                    nd = 2 * ex + 3;
-                    dec[0] = w;
-                    const double stepw = (0.0 - w) / (ex + 1), stepj = (jn - 0.0) / (ex + 1);
-                    for (int i = 0; i < ex; i++) { dec[1 + i] = add_rn(mul_rn((double)(i + 1), stepw), w); dec[ex + 2 + i] = add_rn(mul_rn((double)(i + 1), stepj), 0.0); }
-                    dec[ex + 1] = 0.0;
-                    dec[nd - 1] = jn;
-                }
+                one_sided = (w >= 0.0 || jn <= 0.0);
+                if (ex == 0) nd = one_sided ? 2 : 3;
+                else if (one_sided) { nd = ex + 2; stepw = (jn - w) / (ex + 1); }
+                else { nd = 2 * ex + 3; stepw = (0.0 - w) / (ex + 1); stepj = (jn - 0.0) / (ex + 1); }
             }
+            auto volume_of = [&](int d) -> double {
+                const int ex = q.extra;
+                if (d == 0) return w;
+                if (d == nd - 1) return jn;
+                if (one_sided) return add_rn(mul_rn((double)d, stepw), w);
+                if (d <= ex) return add_rn(mul_rn((double)d, stepw), w);
+                if (d == ex + 1) return 0.0;
+                return add_rn(mul_rn((double)(d - ex - 1), stepj), 0.0);
+            };
             const double inv_cost_npv = q.inv_cost == 0.0 ? 0.0 : mul_rn(mul_rn(v, q.inv_cost), q.inv_cost_df);
             double best = 0.0, best_imm = 0.0, best_cons = 0.0, best_vol = 0.0;
             int best_d = 0;
@@ -492,19 +504,19 @@ __global__ void __launch_bounds__(kFwdThreads, KT <= 16 ? 3 : 1) forward_kernel(
                 const double cost = vol > 0.0 ? mul_rn(mul_rn(q.inj_cost, vol), q.inj_df) : mul_rn(mul_rn(q.wd_cost, fabs(-vol)), q.wd_df);
                 const double imm = sub_rn(add_rn(sub_rn(a, cost), c), inv_cost_npv);
                 int lo, hi;
-                if (!bisect_dev(q.next_grid, q.Gn, after, q.tol, lo, hi)) { atomicExch(q.error_flag, 4); lo = hi = 0; }
+                if (!bisect_sm(grid_s, q.Gn, after, q.tol, lo, hi)) { atomicExch(q.error_flag, 4); lo = hi = 0; }
                 auto fitted = [&](int l) {
-                    const double* b = q.beta + (size_t)l * q.ldb;
-                    if (q.cont_mode == 1) return __ldg(b);
+                    const double* b = beta_s + l * BP;
+                    if (q.cont_mode == 1) return b[0];
                     double acc = 0.0;
 #pragma unroll
-                    for (int k = 0; k < KT; k++) if (k < K) acc = fma(xrow[k], __ldg(b + k), acc);
+                    for (int k = 0; k < KT; k++) if (k < K) acc = fma(xrow[k], b[k], acc);
                     return acc;
                 };
                 double cont;
                 if (lo == hi) cont = fitted(lo);
                 else {
-                    const double gl = __ldg(q.next_grid + lo), gu = __ldg(q.next_grid + hi);
+                    const double gl = grid_s[lo], gu = grid_s[hi];
                     const double wl = sub_rn(gu, after) / sub_rn(gu, gl);
                     const double wu = sub_rn(1.0, wl);
                     cont = add_rn(mul_rn(fitted(lo), wl), mul_rn(fitted(hi), wu));
@@ -512,12 +524,12 @@ __global__ void __launch_bounds__(kFwdThreads, KT <= 16 ? 3 : 1) forward_kernel(
                 const double tot = add_rn(imm, cont);
                 if (d == 0 || tot > best) { best = tot; best_imm = imm; best_cons = cons; best_vol = vol; best_d = d; }
             };
-            if (q.extra == 0) {
-                consider(0, dec[0]);
-                consider(1, dec[1]);
-                if (nd == 3) consider(2, dec[2]);
+            if (q.extra == 0) {   // the common case: withdraw, (nothing,) inject
+                consider(0, w);
+                consider(1, nd == 3 ? 0.0 : jn);
+                if (nd == 3) consider(2, jn);
             } else {
-                for (int d = 0; d < nd; d++) consider(d, dec[d]);
+                for (int d = 0; d < nd; d++) consider(d, volume_of(d));
             }
             const double next_inv = sub_rn(add_rn(v, best_vol), loss);
             q.inventory[n] = next_inv;
@@ -537,7 +549,7 @@ __global__ void __launch_bounds__(kFwdThreads, KT <= 16 ? 3 : 1) forward_kernel(
 #pragma unroll
         for (int i = 0; i < kFwdSums + KT; i++) {
             if (i < nsum) {
-                double val = i < kFwdSums ? sums[i < kFwdSums ? i : 0] : xsum[(size_t)(i >= kFwdSums ? i - kFwdSums : 0) * blockDim.x];
+                double val = i < kFwdSums ? sums[i < kFwdSums ? i : 0] : xsum[i >= kFwdSums ? i - kFwdSums : 0];
 #pragma unroll
                 for (int off = 16; off > 0; off >>= 1) val += __shfl_xor_sync(0xffffffffu, val, off);
                 if (lane == 0) red[warp * nsum + i] = val;
@@ -552,16 +564,21 @@ __global__ void __launch_bounds__(kFwdThreads, KT <= 16 ? 3 : 1) forward_kernel(
     }
 }
 
-void launch_forward(const ForwardParams* pp, int p0, int p1, int K, int n_nodes, int blocks, cudaStream_t stream) {
-    const size_t smem = sizeof(double) * ((size_t)(n_nodes + K) * kFwdThreads + (size_t)(kFwdThreads / 32) * (kFwdSums + K));
-    if (K <= 4) forward_kernel<4><<<blocks, kFwdThreads, smem, stream>>>(pp, p0, p1);
-    else if (K <= 8) forward_kernel<8><<<blocks, kFwdThreads, smem, stream>>>(pp, p0, p1);
-    else if (K <= 12) forward_kernel<12><<<blocks, kFwdThreads, smem, stream>>>(pp, p0, p1);
-    else if (K <= 16) forward_kernel<16><<<blocks, kFwdThreads, smem, stream>>>(pp, p0, p1);
-    else {
-        static size_t configured = 0;
-        if (smem > configured) { cudaFuncSetAttribute(forward_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); configured = smem; }
-        forward_kernel<64><<<blocks, kFwdThreads, smem, stream>>>(pp, p0, p1);
+template <int KT, bool EXACT>
+static void launch_forward_t(const ForwardParams* pp, int p0, int p1, int K, int n_nodes, int max_grid, int blocks, cudaStream_t stream) {
+    const size_t smem = sizeof(double) * ((size_t)n_nodes * kFwdThreads + (size_t)max_grid * (fwd_beta_pitch(KT) + 1) + (size_t)(kFwdThreads / 32) * (kFwdSums + K));
+    static size_t configured = 0;
+    if (smem > 48 * 1024 && smem > configured) { cudaFuncSetAttribute(forward_kernel<KT, EXACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); configured = smem; }
+    forward_kernel<KT, EXACT><<<blocks, kFwdThreads, smem, stream>>>(pp, p0, p1, max_grid);
+}
+
+void launch_forward(const ForwardParams* pp, int p0, int p1, int K, int n_nodes, int max_grid, int blocks, cudaStream_t stream) {
+    switch (K) {
+#define EXACT_K(k) case k: launch_forward_t<k, true>(pp, p0, p1, K, n_nodes, max_grid, blocks, stream); return;
+        EXACT_K(1) EXACT_K(2) EXACT_K(3) EXACT_K(4) EXACT_K(5) EXACT_K(6) EXACT_K(7) EXACT_K(8) EXACT_K(9) EXACT_K(10)
+        EXACT_K(11) EXACT_K(12) EXACT_K(13) EXACT_K(14) EXACT_K(15) EXACT_K(16)
+#undef EXACT_K
+        default: launch_forward_t<64, false>(pp, p0, p1, K, n_nodes, max_grid, blocks, stream); return;
     }
 }
 

@@ -464,11 +464,11 @@ void forward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
     }
     c->fwd_params.upload(hq, s);
     if (!cb) {   // the whole pass in one launch
-        launch_forward(c->fwd_params.p, 0, P - 1, K, pl.basis.n_nodes, c->fwd_blocks, s);
+        launch_forward(c->fwd_params.p, 0, P - 1, K, pl.basis.n_nodes, pl.max_grid, c->fwd_blocks, s);
         c->tm.kernel_launches++;
     } else {     // one launch per period so that progress / cancellation keep the reference's cadence (LSV.cs:488-490)
         for (int p = 0; p < P - 1; p++) {
-            launch_forward(c->fwd_params.p, p, p + 1, K, pl.basis.n_nodes, c->fwd_blocks, s);
+            launch_forward(c->fwd_params.p, p, p + 1, K, pl.basis.n_nodes, pl.max_grid, c->fwd_blocks, s);
             c->tm.kernel_launches++;
             progress += fwd_step;
             CUDA_CHECK(cudaStreamSynchronize(s));
