@@ -125,6 +125,8 @@ def cpu_sample(config, cpu_paths, kind_note=""):
     from storage_b200._abi import Rng
     from storage_b200.configs import build_config
     pb = build_config(config, num_sims=cpu_paths)
+    # all host cores, whatever OMP_NUM_THREADS says (torchrun exports OMP_NUM_THREADS=1 to every rank)
+    oracle.set_num_threads(len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1))
     t0 = time.perf_counter()
     out = oracle.calculate(pb, Rng.philox(11), Rng.philox(22), decision_index=False, triggers=True)
     dt = time.perf_counter() - t0

@@ -10,7 +10,7 @@ python bench.py --steps 5 --warmup 3 > $OUT/bench_$TAG.json 2> $OUT/bench_$TAG.e
 echo "bench exit $?"; cat $OUT/bench_$TAG.json
 CMD="python bench.py --steps 1 --warmup 1 --no-cpu-baseline"
 $CMD > $OUT/plain_$TAG.log 2>&1 &&
-ncu --metrics gpu__time_duration.sum --clock-control none -s 1480 -c 1500 --csv --log-file $OUT/launches_$TAG.csv $CMD > $OUT/ncu_launch_$TAG.log 2>&1
+ncu --metrics gpu__time_duration.sum --clock-control none -s 1106 -c 1106 --csv --log-file $OUT/launches_$TAG.csv $CMD > $OUT/ncu_launch_$TAG.log 2>&1
 echo "launch list exit $?"
 $CMD > $OUT/plain_$TAG.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:"sweep4_kernel|sweep_kernel" -s 500 -c 2 -o $OUT/sweep_$TAG -f $CMD > $OUT/ncu_sweep_$TAG.log 2>&1
