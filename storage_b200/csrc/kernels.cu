@@ -405,14 +405,87 @@ __device__ __forceinline__ bool bisect_sm(const double* grid, int n, double inv,
     return false;
 }
 
+// The same result as bisect_sm in O(1) on a grid whose intervals are all wider than 2 tol: find the interval with
+// grid[m] < inv <= grid[m+1] from the fixed spacing (guess + fix-up), then apply the bisection's tolerance rules.  The one
+// path-dependent case of SH.cs:280-314 — inv within tol at or below grid[i] gives (i, i) when the bisection probes i before
+// i-1 and (i-1, i) otherwise — is a function of (n, i) alone, tabulated per period in probe_first[] (fwd_probe_first).
+__device__ __forceinline__ bool locate_sm(const double* grid, const unsigned char* probe_first, int n, double g0, double inv_h,
+                                          double inv, double tol, int& lo, int& hi) {
+    const int top = n - 1;
+    if (n == 1) { lo = hi = 0; return fabs(inv - grid[0]) <= tol; }
+    int m = (int)((inv - g0) * inv_h);
+    m = min(max(m, 0), top - 1);
+    while (m > 0 && grid[m] >= inv) m--;
+    while (m < top - 1 && grid[m + 1] < inv) m++;
+    const double gl = grid[m], gu = grid[m + 1];
+    if (inv <= gl) { lo = hi = 0; return fabs(inv - gl) <= tol; }          // m == 0: at or below the first point
+    if (inv > gu) { lo = hi = top; return fabs(inv - gu) <= tol; }         // m == top-1: above the last point
+    if (fabs(inv - gu) <= tol) { hi = m + 1; lo = probe_first[m + 1] ? m + 1 : m; return true; }
+    if (fabs(inv - gl) <= tol) { lo = hi = m; return true; }
+    lo = m; hi = m + 1;
+    return true;
+}
+
+// probe_first[i]: does the bisection of SH.cs:280-314, searching a value just below grid[i], probe index i before i-1?
+__device__ __forceinline__ unsigned char fwd_probe_first(int n, int i) {
+    int left = 0, right = n - 1;
+    while (right > left) {
+        const int mid = (left + right) >> 1;
+        if (mid == i) return 1;
+        if (mid > i) right = mid;
+        else { if (mid == i - 1) return 0; left = mid; }
+    }
+    return 0;
+}
+
+// Result of the bisection of SH.cs:280-314 for every target of one comparison class.  A target t is classified by the grid
+// interval that holds it — m with grid[m] < t <= grid[m+1]; m = -1: t <= grid[0]; m = n-1: t > grid[n-1] — and by which of
+// the points grid[m], grid[m+1], grid[n-2], grid[n-1] it is within the tolerance of (bits 0..3 of flags).  On grids whose
+// intervals are all wider than twice the tolerance, except possibly the last one (FixedSpacingStateSpaceGridCalc.cs:45-62
+// accumulates steps and then clamps to the maximum, which can leave a last interval of one rounding error), no other point
+// can be within the tolerance, so every comparison the bisection makes is determined by the class and its control flow can
+// be replayed without the target: lo | hi << 8, or 0xffff where it reports "outside the grid".
+__device__ __forceinline__ uint16_t fwd_class_result(int n, int m, int flags) {
+    const int top = n - 1;
+    auto near = [&](int x) {
+        return (x == top - 1 && (flags & 4)) || (x == top && (flags & 8)) || (x == m && (flags & 1)) || (x == m + 1 && (flags & 2));
+    };
+    if (n == 1) return near(0) ? (uint16_t)0 : (uint16_t)0xffff;
+    int left = 0, right = top;
+    for (int guard = 0; guard < 64 && right > left; guard++) {
+        const int mid = (left + right) >> 1;
+        if (near(mid)) return (uint16_t)(mid | (mid << 8));
+        if (mid >= m + 1) { right = mid; continue; }                                   // grid[mid] > t
+        if (mid + 1 >= m + 1) return (uint16_t)(mid | ((mid + 1) << 8));               // t <= grid[mid + 1]
+        if (near(mid + 1)) return (uint16_t)((mid + 1) | ((mid + 1) << 8));
+        if (mid + 1 == top) return (uint16_t)0xffff;
+        left = mid;
+    }
+    return (uint16_t)0xffff;
+}
+
 __host__ __device__ constexpr int fwd_beta_pitch(int KT) { return KT | 1; }
+constexpr int kFwdPillars = 16;
+constexpr int kFwdMaxGrid = 127;   // forward_fast_kernel: class table of (grid points + 1) x 16 entries   // piecewise-linear ratchet tables up to this size are staged in shared memory
 
 template <int KT, bool EXACT>
 __global__ void __launch_bounds__(kFwdThreads, KT <= 16 ? LSMC_FWD_MINB : 1) forward_kernel(const ForwardParams* __restrict__ pp, int p0, int p1, int max_grid) {
     extern __shared__ double fsm[];   // [n_nodes][blockDim] node columns, [max_grid][BP] beta, [max_grid] grid, [warps][nsum] reduction scratch
     __shared__ ForwardParams sq;
+    __shared__ uint32_t s_ops[kMaxOps];              // basis program: dst | a << 8 | b << 16
+    __shared__ uint8_t s_node_of_basis[64];
+    __shared__ unsigned char s_probe_first[256];
+    __shared__ double s_cx[kFwdPillars], s_clo[kFwdPillars], s_chi[kFwdPillars], s_slo[kFwdPillars], s_shi[kFwdPillars];
     constexpr int BP = fwd_beta_pitch(KT);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
+    {
+        const BasisDev* __restrict__ bd0 = pp[p0].basis;
+        for (int o = tid; o < bd0->n_ops; o += blockDim.x) {
+            const BasisOpDev op = bd0->ops[o];
+            s_ops[o] = (uint32_t)op.dst | ((uint32_t)op.a << 8) | ((uint32_t)op.b << 16);
+        }
+        for (int k = tid; k < 64; k += blockDim.x) s_node_of_basis[k] = (uint8_t)bd0->node_of_basis[k];
+    }
     for (int p = p0; p < p1; p++) {
         __syncthreads();
         if (tid == 0) sq = pp[p];
@@ -420,17 +493,36 @@ __global__ void __launch_bounds__(kFwdThreads, KT <= 16 ? LSMC_FWD_MINB : 1) for
         const ForwardParams& q = sq;
         const BasisDev* __restrict__ bd = q.basis;
         const int K = EXACT ? KT : q.K, nsum = kFwdSums + K;
+        const int n_ops = bd->n_ops;
         double* nodes = fsm + tid;                                   // node j at nodes[j * blockDim.x]
         double* beta_s = fsm + (size_t)bd->n_nodes * blockDim.x;     // row l at beta_s[l * BP]
         double* grid_s = beta_s + (size_t)max_grid * BP;
         double* red = grid_s + max_grid;                             // [warps][nsum]
+        const int Gn = q.Gn;
+        int narrow = 0;   // an interval of the next grid within 2 tol (or more rows than the table holds): plain bisection
         {
-            const int Gn = q.Gn, nk = q.cont_mode == 1 ? 1 : K;
+            const int nk = q.cont_mode == 1 ? 1 : K;
             for (int l = warp; l < Gn; l += nwarps)
                 for (int k = lane; k < nk; k += 32) beta_s[l * BP + k] = __ldg(q.beta + (size_t)l * q.ldb + k);
-            for (int l = tid; l < Gn; l += blockDim.x) grid_s[l] = __ldg(q.next_grid + l);
+            for (int l = tid; l < Gn; l += blockDim.x) {
+                grid_s[l] = __ldg(q.next_grid + l);
+                if (l < 256) s_probe_first[l] = fwd_probe_first(Gn, l);
+                if (l + 1 < Gn && !(__ldg(q.next_grid + l + 1) - __ldg(q.next_grid + l) > 2.0 * q.tol)) narrow = 1;
+            }
+            if (Gn > 256) narrow = 1;
+            if (q.c_kind == LSMC_CONSTRAINT_PIECEWISE_LINEAR && q.c_n <= kFwdPillars && tid < q.c_n) {
+                const double x0 = __ldg(q.c_x + tid), l0 = __ldg(q.c_lo + tid), h0 = __ldg(q.c_hi + tid);
+                s_cx[tid] = x0; s_clo[tid] = l0; s_chi[tid] = h0;
+                if (tid + 1 < q.c_n) {   // slopes as spline_dev forms them
+                    const double dx = __ldg(q.c_x + tid + 1) - x0;
+                    s_slo[tid] = (__ldg(q.c_lo + tid + 1) - l0) / dx;
+                    s_shi[tid] = (__ldg(q.c_hi + tid + 1) - h0) / dx;
+                }
+            }
         }
-        __syncthreads();
+        const bool fast_locate = __syncthreads_or(narrow) == 0;
+        const bool staged_pillars = q.c_kind == LSMC_CONSTRAINT_PIECEWISE_LINEAR && q.c_n <= kFwdPillars && q.c_n >= 2;
+        const double g0 = grid_s[0], inv_h = Gn > 1 ? 1.0 / (grid_s[1] - grid_s[0]) : 0.0;
         double sums[kFwdSums], xsum[KT];
 #pragma unroll
         for (int i = 0; i < kFwdSums; i++) sums[i] = 0.0;
@@ -445,13 +537,13 @@ __global__ void __launch_bounds__(kFwdThreads, KT <= 16 ? LSMC_FWD_MINB : 1) for
             if (q.cont_mode == 0) {
                 nodes[0] = 0.0; nodes[(size_t)blockDim.x] = 1.0; nodes[(size_t)2 * blockDim.x] = s;
                 for (int f = 0; f < q.F; f++) nodes[(size_t)(3 + f) * blockDim.x] = __ldcs(q.fac + (size_t)f * q.Npad + n);
-                for (int o = 0; o < bd->n_ops; o++) {
-                    const BasisOpDev op = bd->ops[o];
-                    nodes[(size_t)op.dst * blockDim.x] = mul_rn(nodes[(size_t)op.a * blockDim.x], nodes[(size_t)op.b * blockDim.x]);
+                for (int o = 0; o < n_ops; o++) {
+                    const uint32_t op = s_ops[o];
+                    nodes[(size_t)(op & 0xffu) * blockDim.x] = mul_rn(nodes[(size_t)((op >> 8) & 0xffu) * blockDim.x], nodes[(size_t)(op >> 16) * blockDim.x]);
                 }
 #pragma unroll
                 for (int k = 0; k < KT; k++) {
-                    xrow[k] = (k < K) ? nodes[(size_t)bd->node_of_basis[k] * blockDim.x] : 0.0;
+                    xrow[k] = (k < K) ? nodes[(size_t)s_node_of_basis[k] * blockDim.x] : 0.0;
                     if (k < K) xsum[k] += xrow[k];
                 }
             }
@@ -459,6 +551,13 @@ __global__ void __launch_bounds__(kFwdThreads, KT <= 16 ? LSMC_FWD_MINB : 1) for
             if (v < q.min_inv - q.slack_lo || v > q.max_inv + q.slack_hi) atomicExch(q.error_flag, 1);
             double rmin, rmax;
             if (q.c_kind == LSMC_CONSTRAINT_CONSTANT) { rmin = __ldg(q.c_lo); rmax = __ldg(q.c_hi); }
+            else if (staged_pillars) {   // spline_dev on the staged table: segment by counting, slopes precomputed
+                int k = 0;
+                for (int i = 1; i < q.c_n - 1; i++) k += (s_cx[i] <= v) ? 1 : 0;
+                const double dxv = sub_rn(v, s_cx[k]);
+                rmax = add_rn(s_chi[k], mul_rn(dxv, s_shi[k]));
+                rmin = add_rn(s_clo[k], mul_rn(dxv, s_slo[k]));
+            }
             else if (q.c_kind == LSMC_CONSTRAINT_PIECEWISE_LINEAR) { rmax = spline_dev(q.c_x, q.c_hi, q.c_n, v); rmin = spline_dev(q.c_x, q.c_lo, q.c_n, v); }
             else {
                 if (v < __ldg(q.c_x) - q.slack_hi || v > __ldg(q.c_x + q.c_n - 1) + q.slack_hi) atomicExch(q.error_flag, 2);
@@ -504,7 +603,9 @@ __global__ void __launch_bounds__(kFwdThreads, KT <= 16 ? LSMC_FWD_MINB : 1) for
                 const double cost = vol > 0.0 ? mul_rn(mul_rn(q.inj_cost, vol), q.inj_df) : mul_rn(mul_rn(q.wd_cost, fabs(-vol)), q.wd_df);
                 const double imm = sub_rn(add_rn(sub_rn(a, cost), c), inv_cost_npv);
                 int lo, hi;
-                if (!bisect_sm(grid_s, q.Gn, after, q.tol, lo, hi)) { atomicExch(q.error_flag, 4); lo = hi = 0; }
+                const bool found = fast_locate ? locate_sm(grid_s, s_probe_first, Gn, g0, inv_h, after, q.tol, lo, hi)
+                                               : bisect_sm(grid_s, Gn, after, q.tol, lo, hi);
+                if (!found) { atomicExch(q.error_flag, 4); lo = hi = 0; }
                 auto fitted = [&](int l) {
                     const double* b = beta_s + l * BP;
                     if (q.cont_mode == 1) return b[0];
@@ -564,6 +665,233 @@ __global__ void __launch_bounds__(kFwdThreads, KT <= 16 ? LSMC_FWD_MINB : 1) for
     }
 }
 
+// -------------------------------------------------------------------------------------------------
+// K4, straight-line form for the common shape (no extra decisions, K <= 16, fixed-spacing grids: checked on the host,
+// lsmc_api.cu forward_fast_ok).  Same arithmetic as forward_kernel; the three bang-bang candidates are evaluated without a
+// data-dependent branch (a one-sided set repeats its last candidate, which a strict '>' never selects), the grid lookup is
+// locate_sm with selects instead of loops, both bracketing fitted values are always formed — so the compiler can
+// interleave the candidates' dependent chains (grid loads -> division -> K-long FMA chains).
+// -------------------------------------------------------------------------------------------------
+#ifndef LSMC_FWDF_MINB
+#define LSMC_FWDF_MINB 2
+#endif
+
+template <int KT>
+__global__ void __launch_bounds__(kFwdThreads, LSMC_FWDF_MINB) forward_fast_kernel(const ForwardParams* __restrict__ pp, int p0, int p1, int max_grid) {
+    extern __shared__ double fsm[];   // same carve-up as forward_kernel
+    __shared__ ForwardParams sq;
+    __shared__ uint32_t s_ops[kMaxOps];
+    __shared__ uint8_t s_node_of_basis[64];
+    __shared__ uint16_t s_class[(kFwdMaxGrid + 1) * 16];
+    __shared__ double s_cx[kFwdPillars], s_clo[kFwdPillars], s_chi[kFwdPillars], s_slo[kFwdPillars], s_shi[kFwdPillars];
+    constexpr int K = KT, BP = fwd_beta_pitch(KT), nsum = kFwdSums + K;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int nwarps = kFwdThreads / 32;
+    constexpr int bdim = kFwdThreads;
+    {
+        const BasisDev* __restrict__ bd0 = pp[p0].basis;
+        for (int o = tid; o < bd0->n_ops; o += bdim) {
+            const BasisOpDev op = bd0->ops[o];
+            s_ops[o] = (uint32_t)op.dst | ((uint32_t)op.a << 8) | ((uint32_t)op.b << 16);
+        }
+        for (int k = tid; k < 64; k += bdim) s_node_of_basis[k] = (uint8_t)bd0->node_of_basis[k];
+    }
+    for (int p = p0; p < p1; p++) {
+        __syncthreads();
+        if (tid == 0) sq = pp[p];
+        __syncthreads();
+        const ForwardParams& q = sq;
+        const BasisDev* __restrict__ bd = q.basis;
+        const int n_ops = bd->n_ops, F = q.F;
+        double* nodes = fsm + tid;
+        double* beta_s = fsm + (size_t)bd->n_nodes * bdim;
+        double* grid_s = beta_s + (size_t)max_grid * BP;
+        double* red = grid_s + max_grid;
+        const int Gn = q.Gn, top = Gn - 1;
+        const bool fitted_mode = q.cont_mode == 0;
+        {
+            for (int l = warp; l < Gn; l += nwarps)
+                for (int k = lane; k < K; k += 32)   // current period: the stored means as a constant-only "fit"
+                    beta_s[l * BP + k] = fitted_mode ? __ldg(q.beta + (size_t)l * q.ldb + k) : (k == 0 ? __ldg(q.beta + (size_t)l * q.ldb) : 0.0);
+            for (int l = tid; l < Gn; l += bdim) grid_s[l] = __ldg(q.next_grid + l);
+            for (int e = tid; e < (Gn + 1) * 16; e += bdim) s_class[e] = fwd_class_result(Gn, (e >> 4) - 1, e & 15);
+            if (q.c_kind == LSMC_CONSTRAINT_PIECEWISE_LINEAR && q.c_n <= kFwdPillars && tid < q.c_n) {
+                const double x0 = __ldg(q.c_x + tid), l0 = __ldg(q.c_lo + tid), h0 = __ldg(q.c_hi + tid);
+                s_cx[tid] = x0; s_clo[tid] = l0; s_chi[tid] = h0;
+                if (tid + 1 < q.c_n) {   // slopes as spline_dev forms them
+                    const double dx = __ldg(q.c_x + tid + 1) - x0;
+                    s_slo[tid] = (__ldg(q.c_lo + tid + 1) - l0) / dx;
+                    s_shi[tid] = (__ldg(q.c_hi + tid + 1) - h0) / dx;
+                }
+            }
+        }
+        __syncthreads();
+        const bool staged_pillars = q.c_kind == LSMC_CONSTRAINT_PIECEWISE_LINEAR && q.c_n <= kFwdPillars && q.c_n >= 2;
+        const double g0 = grid_s[0], inv_h = Gn > 1 ? 1.0 / (grid_s[1] - grid_s[0]) : 0.0;
+        const double g_top = grid_s[top], g_pre = grid_s[max(top - 1, 0)];
+        // period constants in registers
+        const double df = q.df, tol = q.tol, loss_pct = q.loss_pct, next_min = q.next_min, next_max = q.next_max;
+        const double cons_inj = q.cons_inj, cons_wd = q.cons_wd, inj_cost = q.inj_cost, wd_cost = q.wd_cost, inj_df = q.inj_df, wd_df = q.wd_df;
+        const double inv_cost = q.inv_cost, inv_cost_df = q.inv_cost_df;
+        const bool spot_is_const = q.spot_is_const != 0;
+        const double spot_const = q.spot_const;
+        const double* __restrict__ spot_row = q.spot;
+        const double* __restrict__ fac_rows = q.fac;
+        double* __restrict__ inv_state = q.inventory;
+        double* __restrict__ pv_state = q.pv_by_sim;
+        const int64_t N = q.N, Npad = q.Npad;
+        const int c_kind = q.c_kind, c_n = q.c_n;
+        const bool any_panel = q.o_inventory || q.o_volume || q.o_consumed || q.o_loss || q.o_net || q.o_pv || q.o_decision;
+
+        double sums[kFwdSums], xsum[KT];
+#pragma unroll
+        for (int i = 0; i < kFwdSums; i++) sums[i] = 0.0;
+#pragma unroll
+        for (int k = 0; k < KT; k++) xsum[k] = 0.0;
+
+        const int64_t stride = (int64_t)gridDim.x * bdim;
+        for (int64_t n = (int64_t)blockIdx.x * bdim + tid; n < N; n += stride) {
+            const double s = spot_is_const ? spot_const : __ldcs(spot_row + n);
+            const double v = inv_state[n];
+            const double pv_old = pv_state[n];
+            double xrow[KT];
+            if (fitted_mode) {
+                nodes[0] = 0.0; nodes[bdim] = 1.0; nodes[2 * bdim] = s;
+                for (int f = 0; f < F; f++) nodes[(3 + f) * bdim] = __ldcs(fac_rows + (size_t)f * Npad + n);
+                for (int o = 0; o < n_ops; o++) {
+                    const uint32_t op = s_ops[o];
+                    nodes[(op & 0xffu) * bdim] = mul_rn(nodes[((op >> 8) & 0xffu) * bdim], nodes[(op >> 16) * bdim]);
+                }
+#pragma unroll
+                for (int k = 0; k < KT; k++) { xrow[k] = nodes[(unsigned)s_node_of_basis[k] * bdim]; xsum[k] += xrow[k]; }
+            } else {
+#pragma unroll
+                for (int k = 0; k < KT; k++) xrow[k] = k == 0 ? 1.0 : 0.0;
+            }
+            // CmdtyStorage.GetInjectWithdrawRange (CmdtyStorage.cs:86-100)
+            if (v < q.min_inv - q.slack_lo || v > q.max_inv + q.slack_hi) atomicExch(q.error_flag, 1);
+            double rmin, rmax;
+            if (staged_pillars) {   // spline_dev on the staged table: segment by counting, slopes precomputed
+                int k = 0;
+                for (int i = 1; i < c_n - 1; i++) k += (s_cx[i] <= v) ? 1 : 0;
+                const double dxv = sub_rn(v, s_cx[k]);
+                rmax = add_rn(s_chi[k], mul_rn(dxv, s_shi[k]));
+                rmin = add_rn(s_clo[k], mul_rn(dxv, s_slo[k]));
+            } else if (c_kind == LSMC_CONSTRAINT_CONSTANT) { rmin = __ldg(q.c_lo); rmax = __ldg(q.c_hi); }
+            else if (c_kind == LSMC_CONSTRAINT_PIECEWISE_LINEAR) { rmax = spline_dev(q.c_x, q.c_hi, c_n, v); rmin = spline_dev(q.c_x, q.c_lo, c_n, v); }
+            else {
+                if (v < __ldg(q.c_x) - q.slack_hi || v > __ldg(q.c_x + c_n - 1) + q.slack_hi) atomicExch(q.error_flag, 2);
+                int idx = min(max(last_at_or_below(q.c_x, c_n, v), 0), c_n - 1);
+                rmin = __ldg(q.c_lo + idx); rmax = __ldg(q.c_hi + idx);
+            }
+            const double loss = mul_rn(loss_pct, v);
+            // bang-bang decision set (SH.cs:109-197), extra decisions == 0
+            double w, jn;
+            {
+                const double base = sub_rn(v, loss);
+                const double afterW = add_rn(rmin, base), afterJ = add_rn(rmax, base);
+                if (afterW > next_max && !(sub_rn(afterW, next_max) < tol)) atomicExch(q.error_flag, 3);
+                if (afterJ < next_min && !(sub_rn(next_min, afterJ) < tol)) atomicExch(q.error_flag, 3);
+                w = afterW > next_max ? sub_rn(next_max, base) : (afterW > next_min ? rmin : sub_rn(next_min, base));
+                jn = afterJ < next_min ? sub_rn(next_min, base) : (afterJ < next_max ? rmax : sub_rn(next_max, base));
+            }
+            const bool one_sided = (w >= 0.0 || jn <= 0.0);
+            const double inv_cost_npv = inv_cost == 0.0 ? 0.0 : mul_rn(mul_rn(v, inv_cost), inv_cost_df);
+            double vol[3], tot[3], imm[3], cons[3];
+            vol[0] = w; vol[1] = one_sided ? jn : 0.0; vol[2] = jn;
+            bool all_found = true;
+#pragma unroll
+            for (int d = 0; d < 3; d++) {
+                const double vd = vol[d];
+                const double after = sub_rn(add_rn(v, vd), loss);
+                const bool pos = vd > 0.0;
+                const double avol = fabs(vd);
+                cons[d] = mul_rn(pos ? cons_inj : cons_wd, avol);
+                const double a = mul_rn(mul_rn(-vd, s), df);
+                const double c = mul_rn(mul_rn(-cons[d], s), df);
+                const double cost = mul_rn(mul_rn(pos ? inj_cost : wd_cost, avol), pos ? inj_df : wd_df);
+                imm[d] = sub_rn(add_rn(sub_rn(a, cost), c), inv_cost_npv);
+                // the bisection's result in O(1): interval by guess + one correction, comparison class, class table
+                int m = (int)((after - g0) * inv_h);
+                m = min(max(m, 0), max(top - 1, 0));
+                const double ga = grid_s[max(m - 1, 0)], gb = grid_s[m], gc = grid_s[min(m + 1, top)], gd = grid_s[min(m + 2, top)];
+                const bool down = after <= gb, up = !down && after > gc;
+                m = down ? m - 1 : (up ? m + 1 : m);
+                double gl = down ? ga : (up ? gc : gb);
+                double gu = down ? gb : (up ? gd : gc);
+                const bool below = after <= g0, above = after > g_top;
+                m = below ? -1 : (above ? top : m);
+                gl = above ? g_top : gl;
+                gu = below ? g0 : gu;
+                const int flags = ((!below && fabs(after - gl) <= tol) ? 1 : 0) | ((!above && fabs(after - gu) <= tol) ? 2 : 0) |
+                                  ((top >= 1 && fabs(after - g_pre) <= tol) ? 4 : 0) | ((fabs(after - g_top) <= tol) ? 8 : 0);
+                const unsigned cls = s_class[(m + 1) * 16 + flags];
+                const bool found = cls != 0xffffu;
+                const int lo = found ? (int)(cls & 0xffu) : 0, hi = found ? (int)(cls >> 8) : 0;
+                gl = grid_s[lo]; gu = grid_s[hi];
+                all_found = all_found && found;
+                const double* bl = beta_s + lo * BP;
+                const double* bh = beta_s + hi * BP;
+                double f_lo = 0.0, f_hi = 0.0;
+#pragma unroll
+                for (int k = 0; k < KT; k++) { f_lo = fma(xrow[k], bl[k], f_lo); f_hi = fma(xrow[k], bh[k], f_hi); }
+                const double wl = sub_rn(gu, after) / sub_rn(gu, gl);
+                const double wu = sub_rn(1.0, wl);
+                const double cont = lo == hi ? f_lo : add_rn(mul_rn(f_lo, wl), mul_rn(f_hi, wu));
+                tot[d] = add_rn(imm[d], cont);
+            }
+            if (!all_found) atomicExch(q.error_flag, 4);
+            // first strictly greatest (SH.cs:206-222)
+            const bool t1 = tot[1] > tot[0];
+            double best = t1 ? tot[1] : tot[0];
+            double best_imm = t1 ? imm[1] : imm[0], best_cons = t1 ? cons[1] : cons[0], best_vol = t1 ? vol[1] : vol[0];
+            int best_d = t1 ? 1 : 0;
+            const bool t2 = tot[2] > best;
+            best_imm = t2 ? imm[2] : best_imm; best_cons = t2 ? cons[2] : best_cons; best_vol = t2 ? vol[2] : best_vol;
+            best_d = t2 ? 2 : best_d;
+            const double next_inv = sub_rn(add_rn(v, best_vol), loss);
+            inv_state[n] = next_inv;
+            pv_state[n] = add_rn(pv_old, best_imm);
+            const double net = sub_rn(-best_vol, best_cons);
+            sums[0] += v; sums[1] += best_vol; sums[2] += best_cons; sums[3] += loss; sums[4] += net; sums[5] += best_imm;
+            sums[6] += mul_rn(-(add_rn(best_vol, best_cons)), s);
+            if (any_panel) {
+                if (q.o_inventory) __stcs(q.o_inventory + n, v);
+                if (q.o_volume) __stcs(q.o_volume + n, best_vol);
+                if (q.o_consumed) __stcs(q.o_consumed + n, best_cons);
+                if (q.o_loss) __stcs(q.o_loss + n, loss);
+                if (q.o_net) __stcs(q.o_net + n, net);
+                if (q.o_pv) __stcs(q.o_pv + n, best_imm);
+                if (q.o_decision) q.o_decision[n] = (int8_t)best_d;
+            }
+        }
+        // block reduction (fixed order)
+#pragma unroll
+        for (int i = 0; i < kFwdSums + KT; i++) {
+            double val = i < kFwdSums ? sums[i < kFwdSums ? i : 0] : xsum[i >= kFwdSums ? i - kFwdSums : 0];
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) val += __shfl_xor_sync(0xffffffffu, val, off);
+            if (lane == 0) red[warp * nsum + i] = val;
+        }
+        __syncthreads();
+        for (int i = tid; i < nsum; i += bdim) {
+            double totv = 0.0;
+            for (int w = 0; w < nwarps; w++) totv += red[w * nsum + i];
+            q.sums[(size_t)blockIdx.x * nsum + i] = totv;
+        }
+    }
+}
+
+template <int KT>
+static void launch_forward_fast_t(const ForwardParams* pp, int p0, int p1, int n_nodes, int max_grid, int blocks, cudaStream_t stream) {
+    const size_t smem = sizeof(double) * ((size_t)n_nodes * kFwdThreads + (size_t)max_grid * (fwd_beta_pitch(KT) + 1) + (size_t)(kFwdThreads / 32) * (kFwdSums + KT));
+    static size_t configured = 0;
+    if (smem > 48 * 1024 && smem > configured) { cudaFuncSetAttribute(forward_fast_kernel<KT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); configured = smem; }
+    forward_fast_kernel<KT><<<blocks, kFwdThreads, smem, stream>>>(pp, p0, p1, max_grid);
+}
+
+int forward_fast_blocks_per_sm() { return LSMC_FWDF_MINB; }
+
 template <int KT, bool EXACT>
 static void launch_forward_t(const ForwardParams* pp, int p0, int p1, int K, int n_nodes, int max_grid, int blocks, cudaStream_t stream) {
     const size_t smem = sizeof(double) * ((size_t)n_nodes * kFwdThreads + (size_t)max_grid * (fwd_beta_pitch(KT) + 1) + (size_t)(kFwdThreads / 32) * (kFwdSums + K));
@@ -572,11 +900,28 @@ static void launch_forward_t(const ForwardParams* pp, int p0, int p1, int K, int
     forward_kernel<KT, EXACT><<<blocks, kFwdThreads, smem, stream>>>(pp, p0, p1, max_grid);
 }
 
-void launch_forward(const ForwardParams* pp, int p0, int p1, int K, int n_nodes, int max_grid, int blocks, cudaStream_t stream) {
+void launch_forward(const ForwardParams* pp, int p0, int p1, int K, int n_nodes, int max_grid, int blocks, bool fast, cudaStream_t stream) {
+    if (fast) {
+        switch (K) {
+#define FAST_K(k) case k: launch_forward_fast_t<k>(pp, p0, p1, n_nodes, max_grid, blocks, stream); return;
+#ifdef LSMC_FAST_BUILD
+            FAST_K(3) FAST_K(10)
+#else
+            FAST_K(1) FAST_K(2) FAST_K(3) FAST_K(4) FAST_K(5) FAST_K(6) FAST_K(7) FAST_K(8) FAST_K(9) FAST_K(10)
+            FAST_K(11) FAST_K(12) FAST_K(13) FAST_K(14) FAST_K(15) FAST_K(16)
+#endif
+#undef FAST_K
+            default: break;
+        }
+    }
     switch (K) {
 #define EXACT_K(k) case k: launch_forward_t<k, true>(pp, p0, p1, K, n_nodes, max_grid, blocks, stream); return;
+#ifdef LSMC_FAST_BUILD
+        EXACT_K(3) EXACT_K(10)
+#else
         EXACT_K(1) EXACT_K(2) EXACT_K(3) EXACT_K(4) EXACT_K(5) EXACT_K(6) EXACT_K(7) EXACT_K(8) EXACT_K(9) EXACT_K(10)
         EXACT_K(11) EXACT_K(12) EXACT_K(13) EXACT_K(14) EXACT_K(15) EXACT_K(16)
+#endif
 #undef EXACT_K
         default: launch_forward_t<64, false>(pp, p0, p1, K, n_nodes, max_grid, blocks, stream); return;
     }

@@ -80,6 +80,7 @@ struct lsmc_ctx {
     Plan plan;
     int64_t N = 0, Npad = 0, Nglobal = 0;
     int TP = 56, nbuf = 2, MT = 1, ldb = 4, sweep_blocks = 0, fwd_blocks = 0, ncols_max = 0;
+    bool fwd_fast = false;   // straight-line forward kernel (forward_fast_ok)
     int TP4 = 0, sweep4_blocks = 0;   // pipelined sweep (sweep4.cu): tile size (0 = shape not covered) and persistent CTAs
     uint32_t outputs = 0;       // bit0 per-sim panels, bit1 decision index
     bool keep_values = false;
@@ -164,6 +165,31 @@ void check_device_error_flag(lsmc_ctx* c) {
     }
 }
 
+// The straight-line forward kernel (kernels.cu forward_fast_kernel) covers: no extra decisions, K <= 16, and next-period
+// grids on which its O(1) lookup provably equals the bisection of SH.cs:280-314 (kernels.cu fwd_class_result): at most 127
+// points; every interval but the last wider than twice the tolerance (the last one only has to be positive: accumulating
+// the step and clamping to the maximum, FixedSpacingStateSpaceGridCalc.cs:45-62, can leave one of a rounding error); all
+// points but the last within a quarter step of fixed spacing, so that the index guess is off by at most one.
+bool forward_fast_ok(const Plan& pl, const lsmc_problem& pb) {
+    if (pb.extra_decisions != 0 || pl.K > 16 || pl.max_dec > 3) return false;
+    const double tol = pb.numerical_tolerance;
+    if (!(tol >= 0.0)) return false;
+    for (int p = 1; p < pl.P; p++) {
+        const int n = pl.grid_size(p);
+        const double* g = pl.grid_of(p);
+        if (n > 127) return false;
+        if (n < 2) continue;
+        const double h = g[1] - g[0];
+        if (!(h > 0.0) || !std::isfinite(1.0 / h)) return false;
+        if (!(g[n - 1] > g[n - 2]) || !(g[n - 1] - g[n - 2] <= 1.25 * h)) return false;
+        for (int l = 0; l + 1 < n; l++) {
+            if (l + 2 < n && !(g[l + 1] - g[l] > 2.0 * tol)) return false;
+            if (!(std::fabs(g[l] - (g[0] + l * h)) <= 0.25 * h)) return false;
+        }
+    }
+    return true;
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 void set_problem(lsmc_ctx* c, const lsmc_problem* problem) {
     require(problem != nullptr, LSMC_EINVAL, "problem is null");
@@ -186,7 +212,9 @@ void set_problem(lsmc_ctx* c, const lsmc_problem* problem) {
     c->TP4 = sweep4_tile(pl.max_grid, pl.K, pl.F, (int)pl.basis.ops.size());
     c->sweep4_blocks = c->TP4 ? (int)std::min<int64_t>(c->num_sms, (c->N + c->TP4 - 1) / c->TP4) : 0;
     if (const char* e = getenv("LSMC_SWEEP")) { if (atoi(e) == 3) c->TP4 = c->sweep4_blocks = 0; }   // development: force the general sweep kernel
-    c->fwd_blocks = (int)std::min<int64_t>((int64_t)c->num_sms * (pl.K <= 16 ? 3 : 1), (c->N + 255) / 256);   // all CTAs resident: each walks every period
+    c->fwd_fast = forward_fast_ok(pl, pb);
+    if (const char* e = getenv("LSMC_FORWARD")) { if (atoi(e) == 0) c->fwd_fast = false; if (atoi(e) == 2) c->fwd_fast = true; }   // development: force the general forward kernel
+    c->fwd_blocks = (int)std::min<int64_t>((int64_t)c->num_sms * (c->fwd_fast ? forward_fast_blocks_per_sm() : (pl.K <= 16 ? 3 : 1)), (c->N + 255) / 256);   // all CTAs resident: each walks every period
     c->ncols_max = 8 * ((pl.max_grid + 7) / 8 + c->MT);
 
     cudaStream_t s = c->stream;
@@ -464,11 +492,11 @@ void forward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
     }
     c->fwd_params.upload(hq, s);
     if (!cb) {   // the whole pass in one launch
-        launch_forward(c->fwd_params.p, 0, P - 1, K, pl.basis.n_nodes, pl.max_grid, c->fwd_blocks, s);
+        launch_forward(c->fwd_params.p, 0, P - 1, K, pl.basis.n_nodes, pl.max_grid, c->fwd_blocks, c->fwd_fast, s);
         c->tm.kernel_launches++;
     } else {     // one launch per period so that progress / cancellation keep the reference's cadence (LSV.cs:488-490)
         for (int p = 0; p < P - 1; p++) {
-            launch_forward(c->fwd_params.p, p, p + 1, K, pl.basis.n_nodes, pl.max_grid, c->fwd_blocks, s);
+            launch_forward(c->fwd_params.p, p, p + 1, K, pl.basis.n_nodes, pl.max_grid, c->fwd_blocks, c->fwd_fast, s);
             c->tm.kernel_launches++;
             progress += fwd_step;
             CUDA_CHECK(cudaStreamSynchronize(s));

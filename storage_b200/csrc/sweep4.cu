@@ -68,7 +68,7 @@ constexpr int kDecWarps = 13;          // grid rows <= 104
 constexpr int kAuxWarps = 3;
 constexpr int kRawStages = 3;
 constexpr int kMaxProd = 32;           // product nodes of the basis program
-constexpr int kLutBytes = 24 * 16 + 24 * 8;
+constexpr int kLutBytes = 4 * 128;        // 24 entries {w_lo, row_lo, row_hi} of 16 bytes, bank-conflict-free placement
 constexpr int kElemReg = 6;          // product elements per aux lane kept as register descriptors
 constexpr int kFitTiles = 6;           // C^ row blocks per fit warp (warps 14, 15; warp 13 takes the 13th)
 
@@ -100,7 +100,7 @@ __host__ __device__ inline Layout4 layout4(int TP, int Gn, int K, int F, int n_p
     L.zero = o; o += al128(row);
     L.ones = o; o += al128(row);
     L.ones_last = o; o += al128(row);
-    L.lut = o;  o += (size_t)kDecWarps * kLutBytes;   // per decision warp: (w_lo, w_hi)[3][8] then (row_lo, row_hi)[3][8]
+    L.lut = o;  o += (size_t)kDecWarps * kLutBytes;   // per decision warp: {w_lo, byte offsets of row_lo / row_hi} per (decision, row)
     L.total = o;
     return L;
 }
@@ -163,8 +163,9 @@ __device__ __forceinline__ void decision_loop(const SweepParams& q, const Layout
     for (int r = 0; r < (KS > 0 ? KS : 1); r++) accS[r] = 0.0;
     const int i = 8 * j + g;
     double* const vrow = q.Vout + (size_t)(R.row_ok ? i : 0) * q.Npad + 2 * t;
-    const unsigned char* const lutw = P.sm + L.lut + (size_t)j * kLutBytes + g * 16;           // + 128 k
-    const unsigned char* const luto = P.sm + L.lut + (size_t)j * kLutBytes + 24 * 16 + g * 8;   // + 64 k
+    // entry (k, g) at 128 (g >> 1) + 16 (g & 1) + 32 k: the <= 6 entries a quarter warp (rows 2q, 2q+1) can ask for lie in
+    // distinct banks, so a 128-bit lookup is conflict free whatever the decisions are
+    const unsigned char* const lute = P.sm + L.lut + (size_t)j * kLutBytes + 128 * (g >> 1) + 16 * (g & 1);   // + 32 k
 
     int stage = 0, sphase = 0, it = 0;
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, it++) {
@@ -222,14 +223,14 @@ __device__ __forceinline__ void decision_loop(const SweepParams& q, const Layout
             k0 = a2 ? 2 : k0; k1 = b2 ? 2 : k1;
         };
         auto phaseB = [&](const int u8, const double bst0, const double bst1, const double bcc0, const double bcc1, const int kk0, const int kk1) {
-            const double2 w0 = *reinterpret_cast<const double2*>(lutw + 128 * kk0);
-            const double2 w1 = *reinterpret_cast<const double2*>(lutw + 128 * kk1);
-            const int2 o0 = *reinterpret_cast<const int2*>(luto + 64 * kk0);
-            const int2 o1 = *reinterpret_cast<const int2*>(luto + 64 * kk1);
-            const double vl0 = *reinterpret_cast<const double*>(pV + o0.x + 8 * u8), vh0 = *reinterpret_cast<const double*>(pV + o0.y + 8 * u8);
-            const double vl1 = *reinterpret_cast<const double*>(pV + o1.x + 8 * u8 + 8), vh1 = *reinterpret_cast<const double*>(pV + o1.y + 8 * u8 + 8);
-            const double act0 = add_rn(mul_rn(vh0, w0.y), mul_rn(vl0, w0.x));
-            const double act1 = add_rn(mul_rn(vh1, w1.y), mul_rn(vl1, w1.x));
+            const int4 e0 = *reinterpret_cast<const int4*>(lute + 32 * kk0);
+            const int4 e1 = *reinterpret_cast<const int4*>(lute + 32 * kk1);
+            const double vl0 = *reinterpret_cast<const double*>(pV + e0.z + 8 * u8), vh0 = *reinterpret_cast<const double*>(pV + e0.w + 8 * u8);
+            const double vl1 = *reinterpret_cast<const double*>(pV + e1.z + 8 * u8 + 8), vh1 = *reinterpret_cast<const double*>(pV + e1.w + 8 * u8 + 8);
+            // w_hi = 1 - w_lo exactly as host_plan.cpp build_tables forms it (LSV.cs:277: wu = 1 - wl)
+            const double wl0 = __hiloint2double(e0.y, e0.x), wl1 = __hiloint2double(e1.y, e1.x);
+            const double act0 = add_rn(mul_rn(vh0, sub_rn(1.0, wl0)), mul_rn(vl0, wl0));
+            const double act1 = add_rn(mul_rn(vh1, sub_rn(1.0, wl1)), mul_rn(vl1, wl1));
             double v0 = add_rn(bst0, add_rn(-bcc0, act0));
             double v1 = add_rn(bst1, add_rn(-bcc1, act1));
             // lanes of rows beyond the grid compute on row 0 (valid memory, finite values) and contribute zeros
@@ -372,10 +373,10 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
         }
         // the warp's selection table: (w_lo, w_hi) and byte offsets of the interpolation rows in the V_next tile, per (decision, row)
         if (t < 3) {
-            unsigned char* lut = sm + L.lut + (size_t)j * kLutBytes;
-            reinterpret_cast<double2*>(lut)[t * 8 + g] = make_double2(t == 0 ? R.wl[0] : t == 1 ? R.wl[1] : R.wl[2], t == 0 ? R.wh[0] : t == 1 ? R.wh[1] : R.wh[2]);
+            unsigned char* ent = sm + L.lut + (size_t)j * kLutBytes + 128 * (g >> 1) + 16 * (g & 1) + 32 * t;
+            const double wl = t == 0 ? R.wl[0] : t == 1 ? R.wl[1] : R.wl[2];
             const int rl = t == 0 ? R.rL[0] : t == 1 ? R.rL[1] : R.rL[2], rh = t == 0 ? R.rH[0] : t == 1 ? R.rH[1] : R.rH[2];
-            reinterpret_cast<int2*>(lut + 24 * 16)[t * 8 + g] = make_int2(rl * (TP + 4) * 8, rh * (TP + 4) * 8);
+            *reinterpret_cast<int4*>(ent) = make_int4(__double2loint(wl), __double2hiint(wl), rl * (TP + 4) * 8, rh * (TP + 4) * 8);
         }
         __syncwarp();
         const Pipe4 P{sm, vfull, cready, dfree, rfull};
