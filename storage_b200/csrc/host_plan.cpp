@@ -421,7 +421,12 @@ void build_plan(const lsmc_problem& problem, Plan& plan) {
                 const double after = v + dv - loss;
                 // linear scan with the hard-coded 1e-8 of LSV.cs:261-299
                 bool placed = false;
-                for (int g = 0; g < Gn && !placed; g++) {
+                // every point more than `margin` below `after` fails both tests of the scan, so it may start just before
+                // the first point that is not (same result as starting at 0; the grids are ascending)
+                const double margin = 1E-6 + std::fabs(after) * 1E-12;
+                int g_start = (int)(std::lower_bound(next, next + Gn, after - margin) - next) - 1;
+                if (g_start < 0) g_start = 0;
+                for (int g = g_start; g < Gn && !placed; g++) {
                     if (std::fabs(next[g] - after) < 1E-8) {
                         tb.lo[e] = tb.hi[e] = g; tb.w_lo[e] = 1.0; tb.w_hi[e] = 0.0; placed = true;
                     } else if (next[g] > after) {

@@ -58,8 +58,57 @@ __global__ void __launch_bounds__(256) simulate_kernel(SimParams sp) {
     }
 }
 
+// Antithetic device-RNG form: one thread per pair of partner paths (2m, 2m+1).  The partner's draws are the exact
+// negatives, so its factors are the exact negatives too (every operation of the OU update is odd in the draws): one
+// Philox + Box-Muller evaluation and one state vector serve both paths, only the exponential is evaluated twice.
+// Bit-identical to simulate_kernel on the same seed.
+template <int F>
+__global__ void __launch_bounds__(256) simulate_pair_kernel(SimParams sp) {
+    const int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t n = 2 * m;
+    if (n >= sp.N) return;
+    double x[F];
+#pragma unroll
+    for (int f = 0; f < F; f++) x[f] = 0.0;
+    const uint64_t draw = (uint64_t)((sp.sim_offset + n) >> 1);
+    for (int j = 0; j < sp.S; j++) {
+        double z[F + 1];
+#pragma unroll
+        for (int f = 0; f < F; f += 2) philox_normal_pair(sp.seed, draw, (uint32_t)j, (uint32_t)(f / 2), z[f], z[f + 1]);
+        const double* L = sp.chol + (size_t)j * F * F;
+        double acc = 0.0;
+#pragma unroll
+        for (int f = 0; f < F; f++) {
+            double eps = mul_rn(__ldg(L + f * F), z[0]);
+#pragma unroll
+            for (int b = 1; b <= f; b++) eps = add_rn(eps, mul_rn(__ldg(L + f * F + b), z[b]));
+            x[f] = add_rn(mul_rn(__ldg(sp.decay + (size_t)j * F + f), x[f]), eps);
+        }
+#pragma unroll
+        for (int f = 0; f < F; f++) {
+            double term = mul_rn(__ldg(sp.vol + (size_t)j * F + f), x[f]);
+            acc = (f == 0) ? term : add_rn(acc, term);
+            __stcs(reinterpret_cast<double2*>(sp.fac + ((size_t)j * F + f) * sp.Npad + n), make_double2(x[f], -x[f]));
+        }
+        const double drift = __ldg(sp.drift + j), fwd = __ldg(sp.fwd + j);
+        const double s0 = mul_rn(fwd, det_exp(sub_rn(acc, drift)));
+        const double s1 = mul_rn(fwd, det_exp(sub_rn(-acc, drift)));
+        __stcs(reinterpret_cast<double2*>(sp.spot + (size_t)j * sp.Npad + n), make_double2(s0, s1));
+    }
+}
+
 void launch_simulate(const SimParams& sp, cudaStream_t stream) {
     const int threads = 256;
+    const bool pairs = sp.mode == LSMC_RNG_PHILOX && sp.antithetic && (sp.N % 2 == 0) && (sp.sim_offset % 2 == 0) && (sp.Npad % 2 == 0);
+    if (pairs) {
+        const int blocks = (int)((sp.N / 2 + threads - 1) / threads);
+        switch (sp.F) {
+#define CASE(f) case f: simulate_pair_kernel<f><<<blocks, threads, 0, stream>>>(sp); break;
+            CASE(1) CASE(2) CASE(3) CASE(4) CASE(5) CASE(6) CASE(7) CASE(8)
+#undef CASE
+        }
+        return;
+    }
     const int blocks = (int)((sp.N + threads - 1) / threads);
     switch (sp.F) {
 #define CASE(f) case f: simulate_kernel<f><<<blocks, threads, 0, stream>>>(sp); break;

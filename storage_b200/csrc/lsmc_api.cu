@@ -1,5 +1,6 @@
 // lsmc_api.cu — the C ABI (include/lsmc_b200.h): context, device memory, per-period orchestration.
 // Replaces the body of LsmcStorageValuation.Calculate<T> (LSV.cs:97-616) behind plain pointers and sizes.
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -194,7 +195,9 @@ bool forward_fast_ok(const Plan& pl, const lsmc_problem& pb) {
 void set_problem(lsmc_ctx* c, const lsmc_problem* problem) {
     require(problem != nullptr, LSMC_EINVAL, "problem is null");
     c->has_problem = false;
+    const auto tp0 = std::chrono::steady_clock::now();
     build_plan(*problem, c->plan);
+    if (getenv("LSMC_VERBOSE")) fprintf(stderr, "set_problem: build_plan %.2f ms\n", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tp0).count());
     Plan& pl = c->plan;
     const lsmc_problem& pb = pl.problem.pb;
     c->N = pb.n_sims;
@@ -219,11 +222,17 @@ void set_problem(lsmc_ctx* c, const lsmc_problem* problem) {
 
     cudaStream_t s = c->stream;
     const size_t S = pl.S, F = pl.F, Np = (size_t)c->Npad;
-    for (int set = 0; set < 2; set++) { c->spot[set].alloc(S * Np); CUDA_CHECK(cudaMemsetAsync(c->spot[set].p, 0, S * Np * sizeof(double), s)); }
-    c->fac.alloc(S * F * Np); CUDA_CHECK(cudaMemsetAsync(c->fac.p, 0, S * F * Np * sizeof(double), s));
+    // Only the pad columns [N, Npad) of every row have to be finite zeros (the last tile of a sweep reads them, and a
+    // NaN there would poison the normal equations); columns [0, N) are always written before they are read.
+    auto zero_pad = [&](double* base, size_t rows) {
+        const size_t pad = Np - (size_t)c->N;
+        if (pad && rows) CUDA_CHECK(cudaMemset2DAsync(base + c->N, Np * sizeof(double), 0, pad * sizeof(double), rows, s));
+    };
+    for (int set = 0; set < 2; set++) { c->spot[set].alloc(S * Np); zero_pad(c->spot[set].p, S); }
+    c->fac.alloc(S * F * Np); zero_pad(c->fac.p, S * F);
     c->Vbuf.alloc((size_t)2 * pl.max_grid * Np);
-    CUDA_CHECK(cudaMemsetAsync(c->Vbuf.p, 0, (size_t)2 * pl.max_grid * Np * sizeof(double), s));
-    if (c->keep_values) c->Vall.alloc((size_t)pl.P * pl.max_grid * Np);
+    zero_pad(c->Vbuf.p, (size_t)2 * pl.max_grid);
+    if (c->keep_values) { c->Vall.alloc((size_t)pl.P * pl.max_grid * Np); zero_pad(c->Vall.p, (size_t)pl.P * pl.max_grid); }
     c->beta_all.alloc((size_t)(pl.P - 1) * c->beta_stride());
     CUDA_CHECK(cudaMemsetAsync(c->beta_all.p, 0, c->beta_all.n * sizeof(double), s));
     c->grid.upload(pl.grid, s);
@@ -792,12 +801,19 @@ int lsmc_calculate(lsmc_ctx* ctx, const lsmc_problem* problem, const lsmc_rng* r
         if (results->inventory || results->inject_withdraw || results->consumed || results->loss || results->net_volume || results->pv) mask |= 1;
         if (results->decision_index) mask |= 2;
         ctx->outputs = mask;
+        const bool verbose = getenv("LSMC_VERBOSE") != nullptr;   // development: host-side time of each stage
+        auto now = [] { return std::chrono::steady_clock::now(); };
+        auto ms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+        const auto t0 = now();
         set_problem(ctx, problem);
+        const auto t1 = now();
         simulate(ctx, 0, regression_rng);
         backward(ctx, progress, user);
         simulate(ctx, 1, valuation_rng);
         forward(ctx, progress, user);
+        const auto t2 = now();
         get_results(ctx, results);
+        if (verbose) fprintf(stderr, "lsmc_calculate: set_problem %.2f ms, simulate+backward+forward %.2f ms, get_results %.2f ms\n", ms(t0, t1), ms(t1, t2), ms(t2, now()));
     });
 }
 
