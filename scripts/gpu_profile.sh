@@ -16,5 +16,5 @@ $CMD > $OUT/plain_$TAG.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:"sweep4_kernel|sweep_kernel" -s 500 -c 2 -o $OUT/sweep_$TAG -f $CMD > $OUT/ncu_sweep_$TAG.log 2>&1
 echo "sweep capture exit $?"
 $CMD > $OUT/plain_$TAG.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:"forward_kernel|simulate_kernel" -s 1 -c 3 -o $OUT/fwdsim_$TAG -f $CMD > $OUT/ncu_fwdsim_$TAG.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:"forward_fast_kernel|forward_kernel|simulate_pair_kernel|simulate_kernel" -s 1 -c 3 -o $OUT/fwdsim_$TAG -f $CMD > $OUT/ncu_fwdsim_$TAG.log 2>&1
 echo "fwd/sim capture exit $?"

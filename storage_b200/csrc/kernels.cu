@@ -400,9 +400,11 @@ void launch_solve(const SolveParams& sp, cudaStream_t stream) {
     else if (sp.K <= 12) solve_kernel<12><<<1, 128, smem, stream>>>(sp);
     else if (sp.K <= 16) solve_kernel<16><<<1, 128, smem, stream>>>(sp);
     else {
+#ifndef LSMC_FAST_BUILD
         static bool configured = false;
         if (!configured) { cudaFuncSetAttribute(solve_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * (3 * 64 * 64 + 64))); configured = true; }
         solve_kernel<64><<<1, 128, smem, stream>>>(sp);
+#endif
     }
 }
 
@@ -514,6 +516,7 @@ __device__ __forceinline__ uint16_t fwd_class_result(int n, int m, int flags) {
 }
 
 __host__ __device__ constexpr int fwd_beta_pitch(int KT) { return KT | 1; }
+__host__ __device__ constexpr int fwd_fast_beta_pitch(int KT) { return (KT + 1) & ~1; }   // rows 16-byte aligned: coefficients read in pairs
 constexpr int kFwdPillars = 16;
 constexpr int kFwdMaxGrid = 127;   // forward_fast_kernel: class table of (grid points + 1) x 16 entries   // piecewise-linear ratchet tables up to this size are staged in shared memory
 
@@ -724,27 +727,33 @@ __global__ void __launch_bounds__(kFwdThreads, KT <= 16 ? LSMC_FWD_MINB : 1) for
 #ifndef LSMC_FWDF_MINB
 #define LSMC_FWDF_MINB 2
 #endif
+#ifndef LSMC_FWDF_THREADS
+#define LSMC_FWDF_THREADS 256
+#endif
+constexpr int kFwdFastThreads = LSMC_FWDF_THREADS;
 
 template <int KT>
-__global__ void __launch_bounds__(kFwdThreads, LSMC_FWDF_MINB) forward_fast_kernel(const ForwardParams* __restrict__ pp, int p0, int p1, int max_grid) {
-    extern __shared__ double fsm[];   // same carve-up as forward_kernel
+__global__ void __launch_bounds__(kFwdFastThreads, LSMC_FWDF_MINB) forward_fast_kernel(const ForwardParams* __restrict__ pp, int p0, int p1, int max_grid) {
+    extern __shared__ __align__(16) unsigned char fsm_fast[];   // same carve-up as forward_kernel (16-byte aligned beta rows)
+    double* const fsm = reinterpret_cast<double*>(fsm_fast);
     __shared__ ForwardParams sq;
-    __shared__ uint32_t s_ops[kMaxOps];
-    __shared__ uint8_t s_node_of_basis[64];
+    __shared__ uint4 s_ops[kMaxOps];                 // basis program as element offsets into the thread's node column: dst, a, b
+    __shared__ uint32_t s_basis_off[64];             // node column offset of basis function k
     __shared__ uint16_t s_class[(kFwdMaxGrid + 1) * 16];
     __shared__ double s_cx[kFwdPillars], s_clo[kFwdPillars], s_chi[kFwdPillars], s_slo[kFwdPillars], s_shi[kFwdPillars];
-    constexpr int K = KT, BP = fwd_beta_pitch(KT), nsum = kFwdSums + K;
+    constexpr int K = KT, BP = fwd_fast_beta_pitch(KT), nsum = kFwdSums + K;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    constexpr int nwarps = kFwdThreads / 32;
-    constexpr int bdim = kFwdThreads;
+    constexpr int nwarps = kFwdFastThreads / 32;
+    constexpr int bdim = kFwdFastThreads;
     {
         const BasisDev* __restrict__ bd0 = pp[p0].basis;
         for (int o = tid; o < bd0->n_ops; o += bdim) {
             const BasisOpDev op = bd0->ops[o];
-            s_ops[o] = (uint32_t)op.dst | ((uint32_t)op.a << 8) | ((uint32_t)op.b << 16);
+            s_ops[o] = make_uint4((uint32_t)op.dst * bdim, (uint32_t)op.a * bdim, (uint32_t)op.b * bdim, 0u);
         }
-        for (int k = tid; k < 64; k += bdim) s_node_of_basis[k] = (uint8_t)bd0->node_of_basis[k];
+        for (int k = tid; k < 64; k += bdim) s_basis_off[k] = (uint32_t)bd0->node_of_basis[k] * bdim;
     }
+    int class_n = -1;
     for (int p = p0; p < p1; p++) {
         __syncthreads();
         if (tid == 0) sq = pp[p];
@@ -763,10 +772,15 @@ __global__ void __launch_bounds__(kFwdThreads, LSMC_FWDF_MINB) forward_fast_kern
                 for (int k = lane; k < K; k += 32)   // current period: the stored means as a constant-only "fit"
                     beta_s[l * BP + k] = fitted_mode ? __ldg(q.beta + (size_t)l * q.ldb + k) : (k == 0 ? __ldg(q.beta + (size_t)l * q.ldb) : 0.0);
             for (int l = tid; l < Gn; l += bdim) grid_s[l] = __ldg(q.next_grid + l);
-            for (int e = tid; e < (Gn + 1) * 16; e += bdim) s_class[e] = fwd_class_result(Gn, (e >> 4) - 1, e & 15);
+            if (Gn != class_n)   // the table is a function of the number of grid points alone
+                for (int e = tid; e < (Gn + 1) * 16; e += bdim) s_class[e] = fwd_class_result(Gn, (e >> 4) - 1, e & 15);
+            class_n = Gn;
+            if (q.c_kind == LSMC_CONSTRAINT_PIECEWISE_LINEAR && q.c_n <= kFwdPillars && tid < kFwdPillars && tid >= q.c_n - 1)
+                s_cx[tid] = __longlong_as_double(0x7ff0000000000000LL);   // interior pillars end at c_n - 2: the count below stops there
             if (q.c_kind == LSMC_CONSTRAINT_PIECEWISE_LINEAR && q.c_n <= kFwdPillars && tid < q.c_n) {
                 const double x0 = __ldg(q.c_x + tid), l0 = __ldg(q.c_lo + tid), h0 = __ldg(q.c_hi + tid);
-                s_cx[tid] = x0; s_clo[tid] = l0; s_chi[tid] = h0;
+                if (tid < q.c_n - 1) s_cx[tid] = x0;
+                s_clo[tid] = l0; s_chi[tid] = h0;
                 if (tid + 1 < q.c_n) {   // slopes as spline_dev forms them
                     const double dx = __ldg(q.c_x + tid + 1) - x0;
                     s_slo[tid] = (__ldg(q.c_lo + tid + 1) - l0) / dx;
@@ -806,13 +820,17 @@ __global__ void __launch_bounds__(kFwdThreads, LSMC_FWDF_MINB) forward_fast_kern
             double xrow[KT];
             if (fitted_mode) {
                 nodes[0] = 0.0; nodes[bdim] = 1.0; nodes[2 * bdim] = s;
-                for (int f = 0; f < F; f++) nodes[(3 + f) * bdim] = __ldcs(fac_rows + (size_t)f * Npad + n);
+                {
+                    const double* fp = fac_rows + n;
+                    double* np = nodes + 3 * bdim;
+                    for (int f = 0; f < F; f++, fp += Npad, np += bdim) *np = __ldcs(fp);
+                }
                 for (int o = 0; o < n_ops; o++) {
-                    const uint32_t op = s_ops[o];
-                    nodes[(op & 0xffu) * bdim] = mul_rn(nodes[((op >> 8) & 0xffu) * bdim], nodes[(op >> 16) * bdim]);
+                    const uint4 op = s_ops[o];
+                    nodes[op.x] = mul_rn(nodes[op.y], nodes[op.z]);
                 }
 #pragma unroll
-                for (int k = 0; k < KT; k++) { xrow[k] = nodes[(unsigned)s_node_of_basis[k] * bdim]; xsum[k] += xrow[k]; }
+                for (int k = 0; k < KT; k++) { xrow[k] = nodes[s_basis_off[k]]; xsum[k] += xrow[k]; }
             } else {
 #pragma unroll
                 for (int k = 0; k < KT; k++) xrow[k] = k == 0 ? 1.0 : 0.0;
@@ -822,7 +840,9 @@ __global__ void __launch_bounds__(kFwdThreads, LSMC_FWDF_MINB) forward_fast_kern
             double rmin, rmax;
             if (staged_pillars) {   // spline_dev on the staged table: segment by counting, slopes precomputed
                 int k = 0;
-                for (int i = 1; i < c_n - 1; i++) k += (s_cx[i] <= v) ? 1 : 0;
+#pragma unroll
+                for (int i = 1; i <= 6; i++) k += (s_cx[i] <= v) ? 1 : 0;   // entries from c_n - 1 on are +inf
+                for (int i = 7; i < c_n - 1; i++) k += (s_cx[i] <= v) ? 1 : 0;
                 const double dxv = sub_rn(v, s_cx[k]);
                 rmax = add_rn(s_chi[k], mul_rn(dxv, s_shi[k]));
                 rmin = add_rn(s_clo[k], mul_rn(dxv, s_slo[k]));
@@ -883,7 +903,12 @@ __global__ void __launch_bounds__(kFwdThreads, LSMC_FWDF_MINB) forward_fast_kern
                 const double* bh = beta_s + hi * BP;
                 double f_lo = 0.0, f_hi = 0.0;
 #pragma unroll
-                for (int k = 0; k < KT; k++) { f_lo = fma(xrow[k], bl[k], f_lo); f_hi = fma(xrow[k], bh[k], f_hi); }
+                for (int k = 0; k + 1 < KT; k += 2) {   // coefficient pairs (rows are 16-byte aligned), same summation order
+                    const double2 cl = *reinterpret_cast<const double2*>(bl + k), ch = *reinterpret_cast<const double2*>(bh + k);
+                    f_lo = fma(xrow[k], cl.x, f_lo); f_hi = fma(xrow[k], ch.x, f_hi);
+                    f_lo = fma(xrow[k + 1], cl.y, f_lo); f_hi = fma(xrow[k + 1], ch.y, f_hi);
+                }
+                if (KT & 1) { f_lo = fma(xrow[KT - 1], bl[KT - 1], f_lo); f_hi = fma(xrow[KT - 1], bh[KT - 1], f_hi); }
                 const double wl = sub_rn(gu, after) / sub_rn(gu, gl);
                 const double wu = sub_rn(1.0, wl);
                 const double cont = lo == hi ? f_lo : add_rn(mul_rn(f_lo, wl), mul_rn(f_hi, wu));
@@ -933,13 +958,14 @@ __global__ void __launch_bounds__(kFwdThreads, LSMC_FWDF_MINB) forward_fast_kern
 
 template <int KT>
 static void launch_forward_fast_t(const ForwardParams* pp, int p0, int p1, int n_nodes, int max_grid, int blocks, cudaStream_t stream) {
-    const size_t smem = sizeof(double) * ((size_t)n_nodes * kFwdThreads + (size_t)max_grid * (fwd_beta_pitch(KT) + 1) + (size_t)(kFwdThreads / 32) * (kFwdSums + KT));
+    const size_t smem = sizeof(double) * ((size_t)n_nodes * kFwdFastThreads + (size_t)max_grid * (fwd_fast_beta_pitch(KT) + 1) + (size_t)(kFwdFastThreads / 32) * (kFwdSums + KT));
     static size_t configured = 0;
     if (smem > 48 * 1024 && smem > configured) { cudaFuncSetAttribute(forward_fast_kernel<KT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); configured = smem; }
-    forward_fast_kernel<KT><<<blocks, kFwdThreads, smem, stream>>>(pp, p0, p1, max_grid);
+    forward_fast_kernel<KT><<<blocks, kFwdFastThreads, smem, stream>>>(pp, p0, p1, max_grid);
 }
 
 int forward_fast_blocks_per_sm() { return LSMC_FWDF_MINB; }
+int forward_fast_threads() { return kFwdFastThreads; }
 
 template <int KT, bool EXACT>
 static void launch_forward_t(const ForwardParams* pp, int p0, int p1, int K, int n_nodes, int max_grid, int blocks, cudaStream_t stream) {
@@ -972,7 +998,11 @@ void launch_forward(const ForwardParams* pp, int p0, int p1, int K, int n_nodes,
         EXACT_K(11) EXACT_K(12) EXACT_K(13) EXACT_K(14) EXACT_K(15) EXACT_K(16)
 #endif
 #undef EXACT_K
+#ifndef LSMC_FAST_BUILD
         default: launch_forward_t<64, false>(pp, p0, p1, K, n_nodes, max_grid, blocks, stream); return;
+#else
+        default: return;
+#endif
     }
 }
 

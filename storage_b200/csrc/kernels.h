@@ -49,6 +49,7 @@ void launch_reduce_partials(const double* partial, int n_parts, int n_elem, doub
 void launch_solve(const SolveParams& sp, cudaStream_t stream);
 void launch_forward(const ForwardParams* device_params, int p0, int p1, int K, int n_nodes, int max_grid, int blocks, bool fast, cudaStream_t stream);
 int forward_fast_blocks_per_sm();
+int forward_fast_threads();
 void launch_reduce_rows(const double* in, int n_rows, int n_blocks, int n_cols, double* out, cudaStream_t stream);
 void launch_final(const FinalParams& q, int blocks, cudaStream_t stream);
 void launch_fill(double* p, int64_t n, double v, cudaStream_t stream);

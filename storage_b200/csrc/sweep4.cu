@@ -54,6 +54,9 @@ __device__ __forceinline__ void tma_2d(void* dst, const CUtensorMap* map, int c0
 __device__ __forceinline__ void aux_bar() { asm volatile("bar.sync 1, 96;" ::: "memory"); }
 __device__ __forceinline__ double2 lds128(const double* p) { return *reinterpret_cast<const double2*>(p); }
 
+#ifndef LSMC_SEL_REG   // 1: weights / row offsets of the chosen decision by register selects; 0: from the warp's table in shared memory
+#define LSMC_SEL_REG 0
+#endif
 #ifndef LSMC_ABLATE   // development only: timing ablations (results are wrong when != 0)
 #define LSMC_ABLATE 0
 #endif
@@ -167,6 +170,12 @@ __device__ __forceinline__ void decision_loop(const SweepParams& q, const Layout
     // distinct banks, so a 128-bit lookup is conflict free whatever the decisions are
     const unsigned char* const lute = P.sm + L.lut + (size_t)j * kLutBytes + 128 * (g >> 1) + 16 * (g & 1);   // + 32 k
 
+#if LSMC_SEL_REG
+    // byte offsets of the interpolation rows of each decision in the V_next tile (pitch TP + 4), lo | hi << 16
+    const uint32_t voff0 = (uint32_t)(R.rL[0] * (TP + 4) * 8) | ((uint32_t)(R.rH[0] * (TP + 4) * 8) << 16);
+    const uint32_t voff1 = (uint32_t)(R.rL[1] * (TP + 4) * 8) | ((uint32_t)(R.rH[1] * (TP + 4) * 8) << 16);
+    const uint32_t voff2 = (uint32_t)(R.rL[2] * (TP + 4) * 8) | ((uint32_t)(R.rH[2] * (TP + 4) * 8) << 16);
+#endif
     int stage = 0, sphase = 0, it = 0;
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, it++) {
         const int b = it & 1;
@@ -191,7 +200,12 @@ __device__ __forceinline__ void decision_loop(const SweepParams& q, const Layout
         double* out = vrow + tile * TP;
 
         double best0, best1, bc0, bc1;   // carried from phase A to phase B
+#if LSMC_SEL_REG
+        double sw0, sw1;                 // w_lo of the chosen decision
+        uint32_t k0, k1;                 // byte offsets of its interpolation rows in the V_next tile: lo | hi << 16
+#else
         int k0, k1;
+#endif
         auto phaseA = [&](const int u8) {
             const double2 s2 = lds128(pS + u8);
             double c0[3], c1[3], x0[3], x1[3];
@@ -216,12 +230,29 @@ __device__ __forceinline__ void decision_loop(const SweepParams& q, const Layout
             const bool a1 = x0[1] > x0[0], b1 = x1[1] > x1[0];
             best0 = a1 ? x0[1] : x0[0]; best1 = b1 ? x1[1] : x1[0];
             bc0 = a1 ? c0[1] : c0[0]; bc1 = b1 ? c1[1] : c1[0];
+#if LSMC_SEL_REG
+            k0 = a1 ? voff1 : voff0; k1 = b1 ? voff1 : voff0;
+            sw0 = a1 ? R.wl[1] : R.wl[0]; sw1 = b1 ? R.wl[1] : R.wl[0];
+#else
             k0 = a1 ? 1 : 0; k1 = b1 ? 1 : 0;
+#endif
             const bool a2 = x0[2] > best0, b2 = x1[2] > best1;
             best0 = a2 ? x0[2] : best0; best1 = b2 ? x1[2] : best1;
             bc0 = a2 ? c0[2] : bc0; bc1 = b2 ? c1[2] : bc1;
+#if LSMC_SEL_REG
+            k0 = a2 ? voff2 : k0; k1 = b2 ? voff2 : k1;
+            sw0 = a2 ? R.wl[2] : sw0; sw1 = b2 ? R.wl[2] : sw1;
+#else
             k0 = a2 ? 2 : k0; k1 = b2 ? 2 : k1;
+#endif
         };
+#if LSMC_SEL_REG
+        auto phaseB = [&](const int u8, const double bst0, const double bst1, const double bcc0, const double bcc1, const uint32_t kk0, const uint32_t kk1,
+                          const double wl0, const double wl1) {
+            const double vl0 = *reinterpret_cast<const double*>(pV + (kk0 & 0xffffu) + 8 * u8), vh0 = *reinterpret_cast<const double*>(pV + (kk0 >> 16) + 8 * u8);
+            const double vl1 = *reinterpret_cast<const double*>(pV + (kk1 & 0xffffu) + 8 * u8 + 8), vh1 = *reinterpret_cast<const double*>(pV + (kk1 >> 16) + 8 * u8 + 8);
+            // w_hi = 1 - w_lo exactly as host_plan.cpp build_tables forms it (LSV.cs:277: wu = 1 - wl)
+#else
         auto phaseB = [&](const int u8, const double bst0, const double bst1, const double bcc0, const double bcc1, const int kk0, const int kk1) {
             const int4 e0 = *reinterpret_cast<const int4*>(lute + 32 * kk0);
             const int4 e1 = *reinterpret_cast<const int4*>(lute + 32 * kk1);
@@ -229,6 +260,7 @@ __device__ __forceinline__ void decision_loop(const SweepParams& q, const Layout
             const double vl1 = *reinterpret_cast<const double*>(pV + e1.z + 8 * u8 + 8), vh1 = *reinterpret_cast<const double*>(pV + e1.w + 8 * u8 + 8);
             // w_hi = 1 - w_lo exactly as host_plan.cpp build_tables forms it (LSV.cs:277: wu = 1 - wl)
             const double wl0 = __hiloint2double(e0.y, e0.x), wl1 = __hiloint2double(e1.y, e1.x);
+#endif
             const double act0 = add_rn(mul_rn(vh0, sub_rn(1.0, wl0)), mul_rn(vl0, wl0));
             const double act1 = add_rn(mul_rn(vh1, sub_rn(1.0, wl1)), mul_rn(vl1, wl1));
             double v0 = add_rn(bst0, add_rn(-bcc0, act0));
@@ -250,6 +282,16 @@ __device__ __forceinline__ void decision_loop(const SweepParams& q, const Layout
             }
         };
         phaseA(0);
+#if LSMC_SEL_REG
+#pragma unroll
+        for (int u = 1; u < NIT; u++) {
+            const double pb0 = best0, pb1 = best1, pc0 = bc0, pc1 = bc1, pw0 = sw0, pw1 = sw1;
+            const uint32_t pk0 = k0, pk1 = k1;
+            phaseA(8 * u);
+            phaseB(8 * (u - 1), pb0, pb1, pc0, pc1, pk0, pk1, pw0, pw1);
+        }
+        phaseB(8 * (NIT - 1), best0, best1, bc0, bc1, k0, k1, sw0, sw1);
+#else
 #pragma unroll
         for (int u = 1; u < NIT; u++) {
             const double pb0 = best0, pb1 = best1, pc0 = bc0, pc1 = bc1;
@@ -258,6 +300,7 @@ __device__ __forceinline__ void decision_loop(const SweepParams& q, const Layout
             phaseB(8 * (u - 1), pb0, pb1, pc0, pc1, pk0, pk1);
         }
         phaseB(8 * (NIT - 1), best0, best1, bc0, bc1, k0, k1);
+#endif
         if (tr) tr[3] = clock64();
         mbar_arrive(&P.dfree[b]);
         if (++stage == kRawStages) { stage = 0; sphase ^= 1; }
