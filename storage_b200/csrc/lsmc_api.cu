@@ -216,7 +216,7 @@ void set_problem(lsmc_ctx* c, const lsmc_problem* problem) {
     c->sweep4_blocks = c->TP4 ? (int)std::min<int64_t>(c->num_sms, (c->N + c->TP4 - 1) / c->TP4) : 0;
     if (const char* e = getenv("LSMC_SWEEP")) { if (atoi(e) == 3) c->TP4 = c->sweep4_blocks = 0; }   // development: force the general sweep kernel
     c->fwd_fast = forward_fast_ok(pl, pb);
-    if (const char* e = getenv("LSMC_FORWARD")) { if (atoi(e) == 0) c->fwd_fast = false; if (atoi(e) == 2) c->fwd_fast = true; }   // development: force the general forward kernel
+    if (const char* e = getenv("LSMC_FORWARD")) { if (atoi(e) == 0) c->fwd_fast = false; }   // development: force the general forward kernel
     const int fwd_threads = c->fwd_fast ? forward_fast_threads() : 256;
     c->fwd_blocks = (int)std::min<int64_t>((int64_t)c->num_sms * (c->fwd_fast ? forward_fast_blocks_per_sm() : (pl.K <= 16 ? 3 : 1)), (c->N + fwd_threads - 1) / fwd_threads);   // all CTAs resident: each walks every period
     c->ncols_max = 8 * ((pl.max_grid + 7) / 8 + c->MT);

@@ -194,6 +194,24 @@ def test_full_size_properties_c3(ctx):
     assert again.npv == res.npv and np.array_equal(again.deltas, res.deltas)      # deterministic reductions
 
 
+@pytest.mark.parametrize("config,paths", [("c3", 150_000), ("c2", 100_000), ("c5", 20_000), ("c1", 50_000)])
+def test_forward_straight_line_kernel_equals_the_bisecting_kernel(config, paths, monkeypatch):
+    """forward_fast_kernel's O(1) grid lookup (class table replaying SH.cs:280-314) against forward_kernel's bisection on
+    every path of a large run: decisions, inventories and PVs must be bit-identical."""
+    pb = build_config(config, num_sims=paths)
+    out = {}
+    for mode in ("1", "0"):   # LSMC_FORWARD=0 forces the general kernel (read in lsmc_set_problem)
+        monkeypatch.setenv("LSMC_FORWARD", mode)
+        with _native.Context(0) as c:
+            out[mode] = c.calculate(pb, Rng.philox(11), Rng.philox(22), panels=("inventory", "inject_withdraw", "pv"), decision_index=True)
+    fast, slow = out["1"], out["0"]
+    assert np.array_equal(fast.decision_index, slow.decision_index)
+    assert np.array_equal(fast.inventory, slow.inventory)
+    assert np.array_equal(fast.inject_withdraw, slow.inject_withdraw)
+    assert np.array_equal(fast.pv, slow.pv)
+    assert rel_err(fast.npv, slow.npv) < 1e-13   # block partition of the sums differs
+
+
 def test_discounted_deltas_identity(ctx):   # LSMCTest:846-869
     pb = reference_problem(num_sims=256, mean_reversion=16.5)
     a = ctx.calculate(pb, Rng.philox(11), Rng.philox(11))
