@@ -516,7 +516,6 @@ __device__ __forceinline__ uint16_t fwd_class_result(int n, int m, int flags) {
 }
 
 __host__ __device__ constexpr int fwd_beta_pitch(int KT) { return KT | 1; }
-__host__ __device__ constexpr int fwd_fast_beta_pitch(int KT) { return (KT + 1) & ~1; }   // rows 16-byte aligned: coefficients read in pairs
 constexpr int kFwdPillars = 16;
 constexpr int kFwdMaxGrid = 127;   // forward_fast_kernel: class table of (grid points + 1) x 16 entries   // piecewise-linear ratchet tables up to this size are staged in shared memory
 
@@ -741,7 +740,7 @@ __global__ void __launch_bounds__(kFwdFastThreads, LSMC_FWDF_MINB) forward_fast_
     __shared__ uint32_t s_basis_off[64];             // node column offset of basis function k
     __shared__ uint16_t s_class[(kFwdMaxGrid + 1) * 16];
     __shared__ double s_cx[kFwdPillars], s_clo[kFwdPillars], s_chi[kFwdPillars], s_slo[kFwdPillars], s_shi[kFwdPillars];
-    constexpr int K = KT, BP = fwd_fast_beta_pitch(KT), nsum = kFwdSums + K;
+    constexpr int K = KT, BP = fwd_beta_pitch(KT), nsum = kFwdSums + K;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int nwarps = kFwdFastThreads / 32;
     constexpr int bdim = kFwdFastThreads;
@@ -824,6 +823,11 @@ __global__ void __launch_bounds__(kFwdFastThreads, LSMC_FWDF_MINB) forward_fast_
                     const double* fp = fac_rows + n;
                     double* np = nodes + 3 * bdim;
                     for (int f = 0; f < F; f++, fp += Npad, np += bdim) *np = __ldcs(fp);
+                    if (n + stride < N) {   // the next path's rows on their way to L2 while this one is worked on
+                        const double* nx = fac_rows + n + stride;
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(spot_row + n + stride));
+                        for (int f = 0; f < F; f++, nx += Npad) asm volatile("prefetch.global.L2 [%0];" ::"l"(nx));
+                    }
                 }
                 for (int o = 0; o < n_ops; o++) {
                     const uint4 op = s_ops[o];
@@ -903,12 +907,7 @@ __global__ void __launch_bounds__(kFwdFastThreads, LSMC_FWDF_MINB) forward_fast_
                 const double* bh = beta_s + hi * BP;
                 double f_lo = 0.0, f_hi = 0.0;
 #pragma unroll
-                for (int k = 0; k + 1 < KT; k += 2) {   // coefficient pairs (rows are 16-byte aligned), same summation order
-                    const double2 cl = *reinterpret_cast<const double2*>(bl + k), ch = *reinterpret_cast<const double2*>(bh + k);
-                    f_lo = fma(xrow[k], cl.x, f_lo); f_hi = fma(xrow[k], ch.x, f_hi);
-                    f_lo = fma(xrow[k + 1], cl.y, f_lo); f_hi = fma(xrow[k + 1], ch.y, f_hi);
-                }
-                if (KT & 1) { f_lo = fma(xrow[KT - 1], bl[KT - 1], f_lo); f_hi = fma(xrow[KT - 1], bh[KT - 1], f_hi); }
+                for (int k = 0; k < KT; k++) { f_lo = fma(xrow[k], bl[k], f_lo); f_hi = fma(xrow[k], bh[k], f_hi); }
                 const double wl = sub_rn(gu, after) / sub_rn(gu, gl);
                 const double wu = sub_rn(1.0, wl);
                 const double cont = lo == hi ? f_lo : add_rn(mul_rn(f_lo, wl), mul_rn(f_hi, wu));
@@ -958,7 +957,7 @@ __global__ void __launch_bounds__(kFwdFastThreads, LSMC_FWDF_MINB) forward_fast_
 
 template <int KT>
 static void launch_forward_fast_t(const ForwardParams* pp, int p0, int p1, int n_nodes, int max_grid, int blocks, cudaStream_t stream) {
-    const size_t smem = sizeof(double) * ((size_t)n_nodes * kFwdFastThreads + (size_t)max_grid * (fwd_fast_beta_pitch(KT) + 1) + (size_t)(kFwdFastThreads / 32) * (kFwdSums + KT));
+    const size_t smem = sizeof(double) * ((size_t)n_nodes * kFwdFastThreads + (size_t)max_grid * (fwd_beta_pitch(KT) + 1) + (size_t)(kFwdFastThreads / 32) * (kFwdSums + KT));
     static size_t configured = 0;
     if (smem > 48 * 1024 && smem > configured) { cudaFuncSetAttribute(forward_fast_kernel<KT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); configured = smem; }
     forward_fast_kernel<KT><<<blocks, kFwdFastThreads, smem, stream>>>(pp, p0, p1, max_grid);
