@@ -313,6 +313,10 @@ __global__ void __launch_bounds__(128) solve_kernel(SolveParams sp) {
         A[e] = gv * dscale[r] * dscale[c];
     }
     __syncthreads();
+    // the thread's first right-hand side is fetched now: its latency hides behind the factorisation
+    double r0[KT];
+#pragma unroll
+    for (int k = 0; k < KT; k++) r0[k] = (k < K && tid < G) ? red[(size_t)k * ld + tid] : 0.0;
     // Cholesky by warp 0 (lane = row, rows lane and lane + 32): no block-wide barriers in the column loop
     if (tid < 32) {
         for (int j = 0; j < K; j++) {
@@ -334,11 +338,14 @@ __global__ void __launch_bounds__(128) solve_kernel(SolveParams sp) {
         }
     }
     __syncthreads();
+    double* invd = Tm + K * K;      // [K] reciprocals of the factor's diagonal: the substitutions multiply instead of dividing
+    for (int k = tid; k < K; k += blockDim.x) invd[k] = 1.0 / A[k * K + k];
+    __syncthreads();
     // each thread: one right-hand side at a time, vectors in registers (KT = compile-time bound of K)
     for (int i = tid; i < G; i += blockDim.x) {
         double x[KT], r[KT], y[KT];
 #pragma unroll
-        for (int k = 0; k < KT; k++) { r[k] = k < K ? red[(size_t)k * ld + i] : 0.0; x[k] = 0.0; y[k] = 0.0; }
+        for (int k = 0; k < KT; k++) { r[k] = (i == tid) ? r0[k] : (k < K ? red[(size_t)k * ld + i] : 0.0); x[k] = 0.0; y[k] = 0.0; }
 #pragma unroll 1
         for (int pass = 0; pass < 2; pass++) {
 #pragma unroll
@@ -347,7 +354,7 @@ __global__ void __launch_bounds__(128) solve_kernel(SolveParams sp) {
                     double s = r[k] * dscale[k];
 #pragma unroll
                     for (int m = 0; m < k; m++) s -= A[k * K + m] * y[m];
-                    y[k] = dropped[k] ? 0.0 : s / A[k * K + k];
+                    y[k] = dropped[k] ? 0.0 : s * invd[k];
                 }
             }
 #pragma unroll
@@ -356,7 +363,7 @@ __global__ void __launch_bounds__(128) solve_kernel(SolveParams sp) {
                     double s = y[k];
 #pragma unroll
                     for (int m = k + 1; m < KT; m++) if (m < K) s -= A[m * K + k] * y[m];
-                    y[k] = dropped[k] ? 0.0 : s / A[k * K + k];
+                    y[k] = dropped[k] ? 0.0 : s * invd[k];
                 }
             }
 #pragma unroll
@@ -394,7 +401,7 @@ __global__ void __launch_bounds__(128) solve_kernel(SolveParams sp) {
 }
 
 void launch_solve(const SolveParams& sp, cudaStream_t stream) {
-    size_t smem = sizeof(double) * ((size_t)3 * sp.K * sp.K + sp.K);
+    size_t smem = sizeof(double) * ((size_t)3 * sp.K * sp.K + 2 * sp.K);
     if (sp.K <= 4) solve_kernel<4><<<1, 128, smem, stream>>>(sp);
     else if (sp.K <= 8) solve_kernel<8><<<1, 128, smem, stream>>>(sp);
     else if (sp.K <= 12) solve_kernel<12><<<1, 128, smem, stream>>>(sp);
@@ -402,7 +409,7 @@ void launch_solve(const SolveParams& sp, cudaStream_t stream) {
     else {
 #ifndef LSMC_FAST_BUILD
         static bool configured = false;
-        if (!configured) { cudaFuncSetAttribute(solve_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * (3 * 64 * 64 + 64))); configured = true; }
+        if (!configured) { cudaFuncSetAttribute(solve_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * (3 * 64 * 64 + 2 * 64))); configured = true; }
         solve_kernel<64><<<1, 128, smem, stream>>>(sp);
 #endif
     }
