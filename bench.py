@@ -257,6 +257,14 @@ def main():
         value = n_global * T / (ms_per_step / 1e3)
         peak, peak_src = measured_peak_gbs()
         achieved = (sweep_bytes / 1e9) / (sweep_ms / 1e3) if sweep_ms > 0 else 0.0
+        # FP64 pipe occupancy of the sweep from first principles: 25 individually rounded operations per (grid row,
+        # path) for the decisions + one FMA lane-slot per (basis, row, path) each for the fit and for X~^T V + 2 K^2 per path
+        # (x~ and X~^T X~), against 64 FP64 lanes per clock per SM (DFMA and DMMA share them: profiles/r01_probe_fp64.txt)
+        G, K = 101, pb.n_basis
+        fp64_slots = float(n_local) * (25.0 * G + 2.0 * K * G + 2.0 * K * K)
+        sm_hz = 1e6 * float(clocks.get("sm_mhz") or clocks.get("sm_max_mhz") or 1965.0)
+        avg_launch_s = (sweep_ms / max(1.0, sweep_launches)) / 1e3
+        fp64_frac = fp64_slots / (64.0 * torch.cuda.get_device_properties(0).multi_processor_count * sm_hz * avg_launch_s) if avg_launch_s > 0 else 0.0
         line = {
             "metric": "lsmc_path_steps_per_sec", "value": value, "unit": "path-steps/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -281,7 +289,7 @@ def main():
                          "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic(args.config, n_local), "peak_source": peak_src,
                          "launches": int(sweep_launches), "avg_launch_ms": sweep_ms / max(1.0, sweep_launches),
                          "algorithmic_bytes_per_launch": sweep_bytes / max(1.0, sweep_launches),
-                         "share_of_step": sweep_ms / max(1e-9, span_ms),
+                         "share_of_step": sweep_ms / max(1e-9, span_ms), "fp64_pipe_frac": fp64_frac,
                          "note": "FP64 pipe (DFMA+DMMA share it, 64 lanes/clk/SM measured) is the co-binding roof: see DESIGN.md 4.1"},
         }
         if not args.no_cpu_baseline:
