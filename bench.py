@@ -37,6 +37,16 @@ CONFIG_TEXT = {
 DEFAULT_PATHS = {"c1": 1000, "c2": 100_000, "c3": 1_000_000, "c4": 500_000, "c5": 2_000_000}
 
 
+# The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner on the first
+# communicator), so file descriptor 1 is pointed at stderr for the whole run and the line goes to the saved descriptor.
+_REAL_STDOUT = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(line):
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -161,7 +171,7 @@ def run_reference(args):
                        "note": "reference C# cannot be built here (no dotnet/NuGet); this is the CPU oracle port of its algorithm, OpenMP on all host threads, bounded sample"},
             "cpu_baseline": base,
             "e2e": {"value": value, "unit": "path-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def main():
@@ -299,7 +309,7 @@ def main():
                 line["cpu_baseline"] = base
             except Exception as e:   # the oracle is a checker; its absence must not hide the GPU number
                 line["cpu_baseline"] = {"value": None, "unit": "path-steps/s", "cores": 0, "kind": "port", "sample": "failed: %s" % e}
-        print(json.dumps(line), flush=True)
+        emit(line)
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
