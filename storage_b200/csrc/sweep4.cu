@@ -54,8 +54,23 @@ __device__ __forceinline__ void tma_2d(void* dst, const CUtensorMap* map, int c0
 __device__ __forceinline__ void aux_bar() { asm volatile("bar.sync 1, 96;" ::: "memory"); }
 __device__ __forceinline__ double2 lds128(const double* p) { return *reinterpret_cast<const double2*>(p); }
 
-#ifndef LSMC_SEL_REG   // 1: weights / row offsets of the chosen decision by register selects; 0: from the warp's table in shared memory
-#define LSMC_SEL_REG 0
+// Unroll factor of the 8-path step loop of a decision warp's tile.  1 (rolled) is the measured optimum: with the whole
+// tile straight-line (7) ptxas sinks the seven V stores to the end of the block and holds their 28 registers, spills the
+// row pointers, and the launch is 9 % slower (0.570 -> 0.533 ms at 1M paths; 2: 0.548, 3: 0.580).
+#ifndef LSMC_STEP_UNROLL
+#define LSMC_STEP_UNROLL 1
+#endif
+constexpr int kStepUnroll = LSMC_STEP_UNROLL;
+#ifndef LSMC_STEP_PIPE
+#define LSMC_STEP_PIPE 1
+#endif
+#ifndef LSMC_STEP_PREFETCH
+#define LSMC_STEP_PREFETCH 0
+#endif
+// 1: weight / row offsets of the chosen decision by register selects; 0: from the warp's table in shared memory.  With the
+// rolled step loop the selects win (0.533 -> 0.518 ms); with the straight-line tile body they were a wash.
+#ifndef LSMC_SEL_REG
+#define LSMC_SEL_REG 1
 #endif
 #ifndef LSMC_ABLATE   // development only: timing ablations (results are wrong when != 0)
 #define LSMC_ABLATE 0
@@ -168,7 +183,7 @@ __device__ __forceinline__ void decision_loop(const SweepParams& q, const Layout
     double* const vrow = q.Vout + (size_t)(R.row_ok ? i : 0) * q.Npad + 2 * t;
     // entry (k, g) at 128 (g >> 1) + 16 (g & 1) + 32 k: the <= 6 entries a quarter warp (rows 2q, 2q+1) can ask for lie in
     // distinct banks, so a 128-bit lookup is conflict free whatever the decisions are
-    const unsigned char* const lute = P.sm + L.lut + (size_t)j * kLutBytes + 128 * (g >> 1) + 16 * (g & 1);   // + 32 k
+    [[maybe_unused]] const unsigned char* const lute = P.sm + L.lut + (size_t)j * kLutBytes + 128 * (g >> 1) + 16 * (g & 1);   // + 32 k
 
 #if LSMC_SEL_REG
     // byte offsets of the interpolation rows of each decision in the V_next tile (pitch TP + 4), lo | hi << 16
@@ -206,13 +221,20 @@ __device__ __forceinline__ void decision_loop(const SweepParams& q, const Layout
 #else
         int k0, k1;
 #endif
-        auto phaseA = [&](const int u8) {
-            const double2 s2 = lds128(pS + u8);
+        struct StepIn { double2 s2, cl[3], ch[3]; };   // spot and the bracketing fitted values of the three decisions, two paths
+        auto loadA = [&](const int u8, StepIn& in) {
+            in.s2 = lds128(pS + u8);
+            in.cl[0] = lds128(pL0 + u8); in.ch[0] = lds128(pH0 + u8);
+            in.cl[1] = lds128(pL1 + u8); in.ch[1] = lds128(pH1 + u8);
+            in.cl[2] = lds128(pL2 + u8); in.ch[2] = lds128(pH2 + u8);
+        };
+        auto computeA = [&](const StepIn& in) {
+            const double2 s2 = in.s2;
             double c0[3], c1[3], x0[3], x1[3];
 #pragma unroll
             for (int d = 0; d < 3; d++) {
-                const double2 cl = lds128((d == 0 ? pL0 : d == 1 ? pL1 : pL2) + u8);
-                const double2 ch = lds128((d == 0 ? pH0 : d == 1 ? pH1 : pH2) + u8);
+                const double2 cl = in.cl[d];
+                const double2 ch = in.ch[d];
                 c0[d] = add_rn(mul_rn(ch.x, R.wh[d]), mul_rn(cl.x, R.wl[d]));
                 c1[d] = add_rn(mul_rn(ch.y, R.wh[d]), mul_rn(cl.y, R.wl[d]));
                 if (d == 1 && ZERO1) { x0[d] = c0[d]; x1[d] = c1[d]; }
@@ -246,6 +268,7 @@ __device__ __forceinline__ void decision_loop(const SweepParams& q, const Layout
             k0 = a2 ? 2 : k0; k1 = b2 ? 2 : k1;
 #endif
         };
+        auto phaseA = [&](const int u8) { StepIn in; loadA(u8, in); computeA(in); };
 #if LSMC_SEL_REG
         auto phaseB = [&](const int u8, const double bst0, const double bst1, const double bcc0, const double bcc1, const uint32_t kk0, const uint32_t kk1,
                           const double wl0, const double wl1) {
@@ -281,9 +304,15 @@ __device__ __forceinline__ void decision_loop(const SweepParams& q, const Layout
                 accS[r] = fma(a2.y, v1, accS[r]);
             }
         };
+#if LSMC_SEL_REG && !LSMC_STEP_PIPE
+#pragma unroll (kStepUnroll)
+        for (int u = 0; u < NIT; u++) {
+            phaseA(8 * u);
+            phaseB(8 * u, best0, best1, bc0, bc1, k0, k1, sw0, sw1);
+        }
+#elif LSMC_SEL_REG
         phaseA(0);
-#if LSMC_SEL_REG
-#pragma unroll
+#pragma unroll (kStepUnroll)
         for (int u = 1; u < NIT; u++) {
             const double pb0 = best0, pb1 = best1, pc0 = bc0, pc1 = bc1, pw0 = sw0, pw1 = sw1;
             const uint32_t pk0 = k0, pk1 = k1;
@@ -291,8 +320,33 @@ __device__ __forceinline__ void decision_loop(const SweepParams& q, const Layout
             phaseB(8 * (u - 1), pb0, pb1, pc0, pc1, pk0, pk1, pw0, pw1);
         }
         phaseB(8 * (NIT - 1), best0, best1, bc0, bc1, k0, k1, sw0, sw1);
+#elif LSMC_STEP_PREFETCH
+        // rolled step loop with the next step's shared-memory operands fetched one step ahead (register double buffer)
+        {
+            StepIn cur, nxt;
+            loadA(0, cur);
+            loadA(8, nxt);
+            computeA(cur);
+#pragma unroll 1
+            for (int u = 1; u < NIT; u++) {
+                const double pb0 = best0, pb1 = best1, pc0 = bc0, pc1 = bc1;
+                const int pk0 = k0, pk1 = k1;
+                cur = nxt;
+                loadA(8 * min(u + 1, NIT - 1), nxt);
+                computeA(cur);
+                phaseB(8 * (u - 1), pb0, pb1, pc0, pc1, pk0, pk1);
+            }
+            phaseB(8 * (NIT - 1), best0, best1, bc0, bc1, k0, k1);
+        }
+#elif !LSMC_STEP_PIPE
+#pragma unroll (kStepUnroll)
+        for (int u = 0; u < NIT; u++) {
+            phaseA(8 * u);
+            phaseB(8 * u, best0, best1, bc0, bc1, k0, k1);
+        }
 #else
-#pragma unroll
+        phaseA(0);
+#pragma unroll (kStepUnroll)
         for (int u = 1; u < NIT; u++) {
             const double pb0 = best0, pb1 = best1, pc0 = bc0, pc1 = bc1;
             const int pk0 = k0, pk1 = k1;
@@ -730,12 +784,16 @@ template <int TP>
 static cudaError_t launch4_tp(const SweepParams& q, int n_prod, int blocks, cudaStream_t stream) {
     const int K = q.K;
     // whole blocks of 8 basis rows go through DMMA, a remainder of 1..3 rows through DFMA
+#ifdef LSMC_ALL_DMMA   // development: remainder rows through a padded DMMA block as well
+    const int MTD = (K + 7) / 8;
+#else
     const int MTD = (K % 8 != 0 && K % 8 <= 3) ? K / 8 : (K + 7) / 8;
+#endif
     const int KS = K - 8 * MTD > 0 ? K - 8 * MTD : 0;
     const int KSTEPS = (K + 3) / 4;
 #define SHAPE(m, s, k) if (MTD == m && KS == s && KSTEPS == k) return launch4_t<TP, m, s, k>(q, n_prod, blocks, stream);
 #ifdef LSMC_FAST_BUILD
-    SHAPE(0, 3, 1) SHAPE(1, 2, 3)
+    SHAPE(0, 3, 1) SHAPE(1, 2, 3) SHAPE(1, 0, 1) SHAPE(2, 0, 3)
 #else
     SHAPE(0, 1, 1) SHAPE(0, 2, 1) SHAPE(0, 3, 1) SHAPE(1, 0, 1) SHAPE(1, 0, 2) SHAPE(1, 1, 3) SHAPE(1, 2, 3) SHAPE(1, 3, 3)
     SHAPE(2, 0, 3) SHAPE(2, 0, 4)
