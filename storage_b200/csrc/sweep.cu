@@ -46,6 +46,10 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
 
 __device__ __forceinline__ double2 lds128(const double* p) { return *reinterpret_cast<const double2*>(p); }
 
+#ifndef LSMC_DECIDE_UNROLL
+#define LSMC_DECIDE_UNROLL 1
+#endif
+constexpr int kDecideUnroll = LSMC_DECIDE_UNROLL;
 constexpr int kSweepWarps = 16;
 constexpr int kWorkers = 15;
 
@@ -106,7 +110,7 @@ __device__ __forceinline__ void decide_item(const RowTable& R, const double* __r
     const double* pV = vn + 2 * t;
     const double* pX = sXT + (size_t)g * LD + 2 * t;
     double* out = vrow + 2 * t;
-#pragma unroll
+#pragma unroll (kDecideUnroll)   // rolled: see sweep4.cu LSMC_STEP_UNROLL
     for (int u = 0; u < TP / 8; u++) {
         double v[2] = {0.0, 0.0};
         if (R.row_ok) {

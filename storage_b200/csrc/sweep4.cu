@@ -62,7 +62,7 @@ __device__ __forceinline__ double2 lds128(const double* p) { return *reinterpret
 #endif
 constexpr int kStepUnroll = LSMC_STEP_UNROLL;
 #ifndef LSMC_STEP_PIPE
-#define LSMC_STEP_PIPE 1
+#define LSMC_STEP_PIPE 0
 #endif
 #ifndef LSMC_STEP_PREFETCH
 #define LSMC_STEP_PREFETCH 0
