@@ -606,11 +606,15 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
                     // general programs: wave by wave, the 96 aux lanes share the (period, node, path) elements of a wave
                     int o0 = 0;
                     for (int w = 0; w < n_waves; w++) {
-                        const int o1 = sWaveEnd[w], nw = o1 - o0, total = 2 * nw * TP;
-                        for (int idx = alane; idx < total; idx += 96) {
-                            const int pair = idx / TP, path = idx - pair * TP;
+                        // one (period, node) row per aux warp at a time: its descriptors are warp-uniform, lanes take the paths
+                        const int o1 = sWaveEnd[w], nw = o1 - o0;
+                        for (int pair = aw; pair < 2 * nw; pair += kAuxWarps) {
                             const int sel = pair >= nw ? 1 : 0, o = o0 + pair - sel * nw;
-                            reinterpret_cast<double*>(sm + sOpD[sel][o])[path] = mul_rn(resolve(sOpA[sel][o])[path], resolve(sOpB[sel][o])[path]);
+                            const double* pa = resolve(sOpA[sel][o]);
+                            const double* pb = resolve(sOpB[sel][o]);
+                            double* pd = reinterpret_cast<double*>(sm + sOpD[sel][o]);
+#pragma unroll
+                            for (int path = lane; path < TP; path += 32) pd[path] = mul_rn(pa[path], pb[path]);
                         }
                         o0 = o1;
                         if (w + 1 < n_waves) aux_bar();
