@@ -81,13 +81,20 @@ constexpr int kStepUnroll = LSMC_STEP_UNROLL;
 #define AB_NO_FIT (LSMC_ABLATE == 6 || LSMC_ABLATE == 7 || LSMC_ABLATE == 9)
 // 13: only decision warps 0..6 decide; 14: only warps 0, 4, 8, 12 (one sub-partition) decide
 
+// Pitch of the V_next tile in paths beyond TP.  0 with the 128-bit gathers of LSMC_SEL_REG (rows 448 bytes apart alternate between the two
+// halves of the banks, like the C^ tile: conflict free); 4 with the 64-bit gathers of the selection-table variant.
+#if LSMC_SEL_REG
+constexpr int kVPad = 0;
+#else
+constexpr int kVPad = 4;
+#endif
 constexpr int kWarps = 16;
 constexpr int kDecWarps = 13;          // grid rows <= 104
 constexpr int kAuxWarps = 3;
 constexpr int kRawStages = 3;
 constexpr int kMaxProd = 32;           // product nodes of the basis program
 constexpr int kLutBytes = 4 * 128;        // 24 entries {w_lo, row_lo, row_hi} of 16 bytes, bank-conflict-free placement
-constexpr int kElemReg = 6;          // product elements per aux lane kept as register descriptors
+constexpr int kElemReg = 8;          // product elements per aux lane kept as register descriptors
 constexpr int kFitTiles = 6;           // C^ row blocks per fit warp (warps 14, 15; warp 13 takes the 13th)
 
 __host__ __device__ inline size_t al128(size_t b) { return (b + 127) & ~(size_t)127; }
@@ -104,7 +111,7 @@ __host__ __device__ inline Layout4 layout4(int TP, int Gn, int K, int F, int n_p
     L.GnP = (Gn + 7) & ~7;
     L.MT = (K + 7) >> 3;
     L.LDP = TP + 4;
-    L.VP = TP + 4;
+    L.VP = TP + kVPad;
     const size_t row = (size_t)TP * 8;
     L.o_sp = 0; L.o_fp = al128(row); L.o_sm = L.o_fp + al128(F * row); L.o_fm = L.o_sm + al128(row);
     L.stage = L.o_fm + al128(F * row);
@@ -186,10 +193,10 @@ __device__ __forceinline__ void decision_loop(const SweepParams& q, const Layout
     [[maybe_unused]] const unsigned char* const lute = P.sm + L.lut + (size_t)j * kLutBytes + 128 * (g >> 1) + 16 * (g & 1);   // + 32 k
 
 #if LSMC_SEL_REG
-    // byte offsets of the interpolation rows of each decision in the V_next tile (pitch TP + 4), lo | hi << 16
-    const uint32_t voff0 = (uint32_t)(R.rL[0] * (TP + 4) * 8) | ((uint32_t)(R.rH[0] * (TP + 4) * 8) << 16);
-    const uint32_t voff1 = (uint32_t)(R.rL[1] * (TP + 4) * 8) | ((uint32_t)(R.rH[1] * (TP + 4) * 8) << 16);
-    const uint32_t voff2 = (uint32_t)(R.rL[2] * (TP + 4) * 8) | ((uint32_t)(R.rH[2] * (TP + 4) * 8) << 16);
+    // byte offsets of the interpolation rows of each decision in the V_next tile (pitch TP + kVPad), lo | hi << 16
+    const uint32_t voff0 = (uint32_t)(R.rL[0] * (TP + kVPad) * 8) | ((uint32_t)(R.rH[0] * (TP + kVPad) * 8) << 16);
+    const uint32_t voff1 = (uint32_t)(R.rL[1] * (TP + kVPad) * 8) | ((uint32_t)(R.rH[1] * (TP + kVPad) * 8) << 16);
+    const uint32_t voff2 = (uint32_t)(R.rL[2] * (TP + kVPad) * 8) | ((uint32_t)(R.rH[2] * (TP + kVPad) * 8) << 16);
 #endif
     int stage = 0, sphase = 0, it = 0;
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, it++) {
@@ -272,8 +279,14 @@ __device__ __forceinline__ void decision_loop(const SweepParams& q, const Layout
 #if LSMC_SEL_REG
         auto phaseB = [&](const int u8, const double bst0, const double bst1, const double bcc0, const double bcc1, const uint32_t kk0, const uint32_t kk1,
                           const double wl0, const double wl1) {
-            const double vl0 = *reinterpret_cast<const double*>(pV + (kk0 & 0xffffu) + 8 * u8), vh0 = *reinterpret_cast<const double*>(pV + (kk0 >> 16) + 8 * u8);
-            const double vl1 = *reinterpret_cast<const double*>(pV + (kk1 & 0xffffu) + 8 * u8 + 8), vh1 = *reinterpret_cast<const double*>(pV + (kk1 >> 16) + 8 * u8 + 8);
+            // 128-bit gathers: the rows of path 0's decision serve path 1 too when both paths chose the same decision
+            const double2 gl0 = *reinterpret_cast<const double2*>(pV + (kk0 & 0xffffu) + 8 * u8), gh0 = *reinterpret_cast<const double2*>(pV + (kk0 >> 16) + 8 * u8);
+            double2 gl1 = gl0, gh1 = gh0;
+            if (kk1 != kk0) {
+                gl1 = *reinterpret_cast<const double2*>(pV + (kk1 & 0xffffu) + 8 * u8);
+                gh1 = *reinterpret_cast<const double2*>(pV + (kk1 >> 16) + 8 * u8);
+            }
+            const double vl0 = gl0.x, vh0 = gh0.x, vl1 = gl1.y, vh1 = gh1.y;
             // w_hi = 1 - w_lo exactly as host_plan.cpp build_tables forms it (LSV.cs:277: wu = 1 - wl)
 #else
         auto phaseB = [&](const int u8, const double bst0, const double bst1, const double bcc0, const double bcc1, const int kk0, const int kk1) {
@@ -473,7 +486,7 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
             unsigned char* ent = sm + L.lut + (size_t)j * kLutBytes + 128 * (g >> 1) + 16 * (g & 1) + 32 * t;
             const double wl = t == 0 ? R.wl[0] : t == 1 ? R.wl[1] : R.wl[2];
             const int rl = t == 0 ? R.rL[0] : t == 1 ? R.rL[1] : R.rL[2], rh = t == 0 ? R.rH[0] : t == 1 ? R.rH[1] : R.rH[2];
-            *reinterpret_cast<int4*>(ent) = make_int4(__double2loint(wl), __double2hiint(wl), rl * (TP + 4) * 8, rh * (TP + 4) * 8);
+            *reinterpret_cast<int4*>(ent) = make_int4(__double2loint(wl), __double2hiint(wl), rl * (TP + kVPad) * 8, rh * (TP + kVPad) * 8);
         }
         __syncwarp();
         const Pipe4 P{sm, vfull, cready, dfree, rfull};
@@ -493,7 +506,7 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
         const int aw = warp - kDecWarps;
         const int alane = aw * 32 + lane;
         const int n_mt = GnP >> 3;                      // 8-row blocks of fitted values
-        const uint32_t vn_bytes = (uint32_t)((size_t)q.Gn * (TP + 4) * 8), raw_bytes = (uint32_t)(2 * (F + 1) * ROW);
+        const uint32_t vn_bytes = (uint32_t)((size_t)q.Gn * (TP + kVPad) * 8), raw_bytes = (uint32_t)(2 * (F + 1) * ROW);
         auto produce_vn = [&](int64_t tile, int b) {
             mbar_expect_tx(&vfull[b], vn_bytes);
             tma_2d(sm + L.vn + (size_t)b * L.vn_buf, &mapV, (int)(tile * TP), 0, &vfull[b]);
@@ -776,7 +789,7 @@ static cudaError_t launch4_t(const SweepParams& q, int n_prod, int blocks, cudaS
         configured = smem;
     }
     CUtensorMap mv, msp, mfp, msm, mfm;
-    if (!make_map(&mv, q.Vnext, q.Npad, q.Gn, TP + 4, q.Gn) || !make_map(&msp, q.spot_p, q.Npad, 1, TP, 1) ||
+    if (!make_map(&mv, q.Vnext, q.Npad, q.Gn, TP + kVPad, q.Gn) || !make_map(&msp, q.spot_p, q.Npad, 1, TP, 1) ||
         !make_map(&mfp, q.fac_p, q.Npad, q.F, TP, q.F) || !make_map(&msm, q.spot_m, q.Npad, 1, TP, 1) ||
         !make_map(&mfm, q.fac_m, q.Npad, q.F, TP, q.F))
         return cudaErrorInvalidValue;
