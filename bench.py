@@ -209,10 +209,7 @@ def main():
     T = pb.n_periods - 1
 
     ctx = _native.Context(local_rank)
-    if world > 1:
-        uid = [_native.Context.comm_unique_id() if rank == 0 else None]
-        dist.broadcast_object_list(uid, src=0)
-        ctx.comm_init(rank, world, uid[0])
+    _native.comm_setup(ctx, rank, world, dist)
     reg, val = Rng.philox(11), Rng.philox(22)
 
     def device_step():

@@ -187,6 +187,16 @@ class Context:
         return out
 
 
+def comm_setup(ctx, rank, world, dist):
+    """Join `ctx` to the communicator of a one-process-per-GPU job: rank 0 creates the NCCL unique id and broadcasts it
+    through the caller's torch.distributed process group (`dist`; any backend, only Python objects travel)."""
+    if world <= 1:
+        return
+    uid = [Context.comm_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(uid, src=0)
+    ctx.comm_init(rank, world, uid[0])
+
+
 def _make_cb(on_progress):
     if on_progress is None:
         return _abi.PROGRESS_CB(0)

@@ -35,9 +35,13 @@ def _ratchet_storage(start, end, years=1, **kw):   # README.md:100-125 shape
     return CmdtyStorage('D', start, end, 0.1, 0.25, ratchets=ratchets, ratchet_interp=RatchetInterp.LINEAR, **kw)
 
 
-def build_config(name, num_sims=None, start_inventory=None):
-    """Returns a flattened Problem for config 'c1'..'c5' (BASELINE.json configs[0..4])."""
+def build_config(name, num_sims=None, start_inventory=None, basis=None, end=None, storage=None):
+    """Returns a flattened Problem for config 'c1'..'c5' (BASELINE.json configs[0..4]).
+
+    `basis`, `end` and `storage` override the config's basis-function string, storage end date and storage object
+    (parity-test variants of the named shapes: other K, shorter horizons, other constraint kinds)."""
     name = name.lower()
+    basis_override, end_override, storage_override = basis, end, storage
     if name == 'c1':    # README simple storage, three-factor seasonal, 1k paths
         N = num_sims or 1000
         start, end, val = '2021-04-01', '2022-04-01', '2021-04-01'
@@ -72,6 +76,14 @@ def build_config(name, num_sims=None, start_inventory=None):
         raise ValueError("unknown config " + name)
     if start_inventory is not None:
         inv = start_inventory
+    if basis_override is not None:
+        basis = basis_override
+    if storage_override is not None:
+        st = storage_override
+    elif end_override is not None:
+        if name not in ('c3', 'c4'):
+            raise ValueError("end override is only wired for the ratchet configs")
+        st = _ratchet_storage(start, end_override, years=2 if name == 'c4' else 1, inventory_loss=0.0005, cmdty_consumed_inject=0.01)
     freq = st.freq
     pfreq = st.start.freq
     index = pd.period_range(st.start, st.end, freq=pfreq)

@@ -7,7 +7,25 @@
 //   K4 forward_kernel        forward inventory / cash-flow simulation of one period (LSV.cs:426-480)
 #include "kernels.h"
 
+#include <map>
+#include <mutex>
+#include <utility>
+
 namespace lsmc {
+
+cudaError_t ensure_dynamic_smem(const void* kernel, size_t bytes) {
+    static std::mutex mu;   // (no shortcut below 48 KB: the default limit counts the kernel's static shared memory too)
+    static std::map<std::pair<const void*, int>, size_t> granted;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    std::lock_guard<std::mutex> lock(mu);
+    size_t& have = granted[std::make_pair(kernel, dev)];
+    if (bytes <= have) return cudaSuccess;
+    e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    if (e == cudaSuccess) have = bytes;
+    return e;
+}
 
 // =================================================================================================
 // K1: simulation.  One thread per path, the time loop runs in registers; stores are coalesced across the warp
@@ -246,8 +264,7 @@ int precond_rows(int K, int64_t N) {
 
 void launch_precond(const PrecondParams& q, cudaStream_t stream) {
     const size_t smem = sizeof(double) * ((size_t)q.K * q.nsub + (size_t)q.K * q.K + q.K + 32);
-    static size_t configured = 0;
-    if (smem > configured) { cudaFuncSetAttribute(precond_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); configured = smem; }
+    if (ensure_dynamic_smem((const void*)precond_kernel, smem) != cudaSuccess) return;   // the launch error surfaces through cudaGetLastError
     precond_kernel<<<q.S, 512, smem, stream>>>(q);
 }
 
@@ -408,8 +425,7 @@ void launch_solve(const SolveParams& sp, cudaStream_t stream) {
     else if (sp.K <= 16) solve_kernel<16><<<1, 128, smem, stream>>>(sp);
     else {
 #ifndef LSMC_FAST_BUILD
-        static bool configured = false;
-        if (!configured) { cudaFuncSetAttribute(solve_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * (3 * 64 * 64 + 2 * 64))); configured = true; }
+        if (ensure_dynamic_smem((const void*)solve_kernel<64>, smem) != cudaSuccess) return;
         solve_kernel<64><<<1, 128, smem, stream>>>(sp);
 #endif
     }
@@ -965,9 +981,14 @@ __global__ void __launch_bounds__(kFwdFastThreads, LSMC_FWDF_MINB) forward_fast_
 template <int KT>
 static void launch_forward_fast_t(const ForwardParams* pp, int p0, int p1, int n_nodes, int max_grid, int blocks, cudaStream_t stream) {
     const size_t smem = sizeof(double) * ((size_t)n_nodes * kFwdFastThreads + (size_t)max_grid * (fwd_beta_pitch(KT) + 1) + (size_t)(kFwdFastThreads / 32) * (kFwdSums + KT));
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) { cudaFuncSetAttribute(forward_fast_kernel<KT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); configured = smem; }
+    if (ensure_dynamic_smem((const void*)forward_fast_kernel<KT>, smem) != cudaSuccess) return;
     forward_fast_kernel<KT><<<blocks, kFwdFastThreads, smem, stream>>>(pp, p0, p1, max_grid);
+}
+
+// Dynamic shared memory the forward pass needs for this shape (checked by lsmc_set_problem before anything runs).
+size_t forward_smem_bytes(int K, int n_nodes, int max_grid, bool fast) {
+    const int KT = (fast || K <= 16) ? K : 64, threads = fast ? kFwdFastThreads : kFwdThreads;
+    return sizeof(double) * ((size_t)n_nodes * threads + (size_t)max_grid * (fwd_beta_pitch(KT) + 1) + (size_t)(threads / 32) * (kFwdSums + K));
 }
 
 int forward_fast_blocks_per_sm() { return LSMC_FWDF_MINB; }
@@ -976,8 +997,7 @@ int forward_fast_threads() { return kFwdFastThreads; }
 template <int KT, bool EXACT>
 static void launch_forward_t(const ForwardParams* pp, int p0, int p1, int K, int n_nodes, int max_grid, int blocks, cudaStream_t stream) {
     const size_t smem = sizeof(double) * ((size_t)n_nodes * kFwdThreads + (size_t)max_grid * (fwd_beta_pitch(KT) + 1) + (size_t)(kFwdThreads / 32) * (kFwdSums + K));
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) { cudaFuncSetAttribute(forward_kernel<KT, EXACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); configured = smem; }
+    if (ensure_dynamic_smem((const void*)forward_kernel<KT, EXACT>, smem) != cudaSuccess) return;
     forward_kernel<KT, EXACT><<<blocks, kFwdThreads, smem, stream>>>(pp, p0, p1, max_grid);
 }
 

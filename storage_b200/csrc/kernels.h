@@ -35,6 +35,10 @@ struct FinalParams {
     double* o_inventory; double* o_pv;
 };
 
+// Opt a kernel in to `bytes` of dynamic shared memory on the CURRENT device.  The attribute is per (kernel, device):
+// the sizes already granted are cached under a mutex, so contexts on several GPUs (or several host threads) each get it.
+cudaError_t ensure_dynamic_smem(const void* kernel, size_t bytes);
+
 bool choose_sweep_shape(int max_grid, int K, int F, int MT, int* TP, int* nbuf);
 int sweep_max_items();
 int precond_rows(int K, int64_t N);
@@ -48,6 +52,7 @@ cudaError_t launch_sweep4(SweepParams& q, int TP, int n_prod, int blocks, cudaSt
 void launch_reduce_partials(const double* partial, int n_parts, int n_elem, double* out, cudaStream_t stream);
 void launch_solve(const SolveParams& sp, cudaStream_t stream);
 void launch_forward(const ForwardParams* device_params, int p0, int p1, int K, int n_nodes, int max_grid, int blocks, bool fast, cudaStream_t stream);
+size_t forward_smem_bytes(int K, int n_nodes, int max_grid, bool fast);
 int forward_fast_blocks_per_sm();
 int forward_fast_threads();
 void launch_reduce_rows(const double* in, int n_rows, int n_blocks, int n_cols, double* out, cudaStream_t stream);

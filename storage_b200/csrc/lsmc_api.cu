@@ -78,6 +78,7 @@ struct lsmc_ctx {
     cudaStream_t stream = nullptr;
     std::string err;
     bool has_problem = false, sims_ready[2] = {false, false}, backward_done = false, forward_done = false;
+    int fac_set = -1;   // which simulation set currently owns the shared factor panel `fac` (-1: none)
     Plan plan;
     int64_t N = 0, Npad = 0, Nglobal = 0;
     int TP = 56, nbuf = 2, MT = 1, ldb = 4, sweep_blocks = 0, fwd_blocks = 0, ncols_max = 0;
@@ -217,6 +218,8 @@ void set_problem(lsmc_ctx* c, const lsmc_problem* problem) {
     if (const char* e = getenv("LSMC_SWEEP")) { if (atoi(e) == 3) c->TP4 = c->sweep4_blocks = 0; }   // development: force the general sweep kernel
     c->fwd_fast = forward_fast_ok(pl, pb);
     if (const char* e = getenv("LSMC_FORWARD")) { if (atoi(e) == 0) c->fwd_fast = false; }   // development: force the general forward kernel
+    require(forward_smem_bytes(pl.K, pl.basis.n_nodes, pl.max_grid, c->fwd_fast) <= (size_t)227 * 1024 - 4096, LSMC_EUNSUPPORTED,
+            "basis functions / inventory grid too large for the forward kernel's shared memory");
     const int fwd_threads = c->fwd_fast ? forward_fast_threads() : 256;
     c->fwd_blocks = (int)std::min<int64_t>((int64_t)c->num_sms * (c->fwd_fast ? forward_fast_blocks_per_sm() : (pl.K <= 16 ? 3 : 1)), (c->N + fwd_threads - 1) / fwd_threads);   // all CTAs resident: each walks every period
     c->ncols_max = 8 * ((pl.max_grid + 7) / 8 + c->MT);
@@ -278,6 +281,7 @@ void set_problem(lsmc_ctx* c, const lsmc_problem* problem) {
     c->beta_override_set.assign(pl.P - 1, 0);
     c->beta_override.clear();
     c->sims_ready[0] = c->sims_ready[1] = c->backward_done = c->forward_done = false;
+    c->fac_set = -1;
     std::memset(&c->tm, 0, sizeof(c->tm));
     CUDA_CHECK(cudaStreamSynchronize(s));
     c->has_problem = true;
@@ -327,6 +331,7 @@ void simulate(lsmc_ctx* c, int set, const lsmc_rng* rng) {
     if (set == 1) c->valuation_antithetic = (rng->mode == LSMC_RNG_PHILOX && rng->antithetic) ? 1 : 0;
     CUDA_CHECK(cudaEventRecord(c->event(set == 0 ? 1 : 5), s));
     c->sims_ready[set] = true;
+    c->fac_set = set;
     if (set == 0) { c->backward_done = false; }
     c->forward_done = false;
 }
@@ -334,6 +339,7 @@ void simulate(lsmc_ctx* c, int set, const lsmc_rng* rng) {
 // Backward induction (LSV.cs:104-341): terminal values, then one fused sweep + reduce + solve per period.
 void backward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
     require(c->has_problem && c->sims_ready[0], LSMC_EINVAL, "simulate the regression set before lsmc_backward");
+    require(c->fac_set == 0, LSMC_EINVAL, "the regression factors were overwritten by the valuation set: simulate the regression set again before lsmc_backward");
     Plan& pl = c->plan;
     const lsmc_problem& pb = pl.problem.pb;
     const int P = pl.P, s0 = pl.s0, F = pl.F, D = pl.max_dec;
@@ -457,7 +463,7 @@ void backward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
 
 // Forward simulation (LSV.cs:344-579).
 void forward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
-    require(c->backward_done && c->sims_ready[1], LSMC_EINVAL, "run lsmc_backward and simulate the valuation set before lsmc_forward");
+    require(c->backward_done && c->sims_ready[1] && c->fac_set == 1, LSMC_EINVAL, "run lsmc_backward and simulate the valuation set before lsmc_forward");
     Plan& pl = c->plan;
     const lsmc_problem& pb = pl.problem.pb;
     const int P = pl.P, s0 = pl.s0, F = pl.F, K = pl.K, nsum = kFwdSums + K;
@@ -858,7 +864,7 @@ int lsmc_get_sim_panel(lsmc_ctx* ctx, int set, int factor, double* out) {
         require(factor >= -1 && factor < pl.F, LSMC_EINVAL, "bad factor index");
         CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
         if (factor < 0) { copy_panel(ctx, out, ctx->spot[set].p, pl.S); return; }
-        require(set == 1 || !ctx->sims_ready[1], LSMC_EINVAL, "regression factors were overwritten by the valuation set");
+        require(ctx->fac_set == set, LSMC_EINVAL, "the factors of this set were overwritten by the other simulation set");
         for (int j = 0; j < pl.S; j++)
             copy_panel(ctx, out + (size_t)j * ctx->N, ctx->fac.p + ((size_t)j * pl.F + factor) * ctx->Npad, 1);
     });

@@ -494,12 +494,7 @@ bool choose_sweep_shape(int max_grid, int K, int F, int MT, int* TP, int* nbuf) 
 template <int TP, int MT, int NTW>
 static cudaError_t launch_sweep_t(const SweepParams& q, int blocks, size_t smem, int nbuf, cudaStream_t stream) {
     auto kern = sweep_kernel<TP, MT, NTW>;
-    static size_t configured = 0;
-    if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        configured = smem;
-    }
+    if (cudaError_t e = ensure_dynamic_smem((const void*)kern, smem)) return e;
     kern<<<blocks, kSweepWarps * 32, smem, stream>>>(q, nbuf);
     return cudaGetLastError();
 }

@@ -782,12 +782,7 @@ template <int TP, int MTD, int KS, int KSTEPS>
 static cudaError_t launch4_t(const SweepParams& q, int n_prod, int blocks, cudaStream_t stream) {
     auto kern = sweep4_kernel<TP, MTD, KS, KSTEPS>;
     const size_t smem = layout4(TP, q.Gn, q.K, q.F, n_prod).total;
-    static size_t configured = 0;
-    if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        configured = smem;
-    }
+    if (cudaError_t e = ensure_dynamic_smem((const void*)kern, smem)) return e;
     CUtensorMap mv, msp, mfp, msm, mfm;
     if (!make_map(&mv, q.Vnext, q.Npad, q.Gn, TP + kVPad, q.Gn) || !make_map(&msp, q.spot_p, q.Npad, 1, TP, 1) ||
         !make_map(&mfp, q.fac_p, q.Npad, q.F, TP, q.F) || !make_map(&msm, q.spot_m, q.Npad, 1, TP, 1) ||

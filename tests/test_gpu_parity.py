@@ -7,14 +7,18 @@ Bars (BASELINE.json north_star):
     decisions of numerically identical volume;
   * device RNG: Philox stream identical to the oracle's, NPV within 3 standard errors.
 """
+import json
+import os
+
 import numpy as np
 import pytest
 
-from storage_b200 import _abi, _native
+from storage_b200 import CmdtyStorage, RatchetInterp, _abi, _native
 from storage_b200._abi import Rng
-from storage_b200.configs import build_config
+from storage_b200.configs import build_config, full_polynomial_basis
 from oracle import oracle
-from fixtures import reference_problem, simple_daily_storage, ratchet_daily_storage, three_calls_problem
+from fixtures import (reference_problem, simple_daily_storage, ratchet_daily_storage, three_calls_problem, STORAGE_START,
+                      STORAGE_END)
 
 pytestmark = pytest.mark.gpu
 REL = 1e-9   # north_star tolerance with injected normals
@@ -66,7 +70,34 @@ def comparable_trigger_rows(got, ref, side):
     return ~excluded
 
 
+def step_ratchet_storage():
+    """The reference's ratchet fixture (LSMCTest:91-125) under RatchetInterp.STEP (StepInjectWithdrawConstraint.cs:46-79:
+    the top two pillars must carry the same rates; a terminal value is advised, cmdty_storage.py:149-152)."""
+    ratchets = [
+        (STORAGE_START, [(0.0, -702.7, 650.0), (15_000, -785.0, 552.5), (30_000, -790.6, 512.8), (40_000, -825.6, 498.6),
+                         (52_500, -825.6, 498.6)]),
+        ("2020-02-01", [(0.0, -645.35, 650.0), (13_000, -656.0, 552.5), (28_000, -689.6, 512.8), (42_000, -701.06, 498.6),
+                        (52_500, -701.06, 498.6)]),
+    ]
+    return CmdtyStorage("D", STORAGE_START, STORAGE_END, 1.25, 0.93, ratchets=ratchets, ratchet_interp=RatchetInterp.STEP,
+                        terminal_storage_npv=lambda price, inventory: 0.0)
+
+
+def inventory_cost_storage():
+    """Non-zero per-unit inventory cost (CmdtyStorage.cs:544-567, LSV.cs:241-242): the kInvc variants of the sweeps."""
+    return CmdtyStorage("D", STORAGE_START, STORAGE_END, 1.25, 0.93, min_inventory=0.0, max_inventory=52_500.0,
+                        max_injection_rate=625.0, max_withdrawal_rate=850.0, inventory_cost=0.004)
+
+
+# five factors, K = 16, full grid: the pipelined sweep's shared memory only fits with 40-path tiles (sweep4.cu sweep4_tile)
+FIVE_FACTOR_K16 = ("1 + x0 + x1 + x2 + x3 + x4 + x0**2 + x1**2 + x2**2 + x3**2 + x4**2 + x0*x1 + x1*x2 + x2*x3 + x3*x4 + s")
+
 CASES = {
+    "c4_five_factor_k56": lambda: build_config("c4", num_sims=512),                              # K > 32: sweep_kernel MT=8, solve_kernel<64>, forward_kernel<64>
+    "c3_cubic_basis_k20": lambda: build_config("c3", num_sims=640, basis=full_polynomial_basis(3, 3)),   # 16 < K <= 32: MT=4
+    "c4_five_factor_k16_tp40": lambda: build_config("c4", num_sims=600, end="2021-07-01", basis=FIVE_FACTOR_K16),
+    "reference_fixture_step_ratchets": lambda: reference_problem(storage=step_ratchet_storage(), num_sims=768, numerical_tolerance=1e-9),
+    "inventory_cost": lambda: reference_problem(storage=inventory_cost_storage(), num_sims=512),
     "c1_readme_simple_3f": lambda: build_config("c1", num_sims=1000),
     "c2_one_factor": lambda: build_config("c2", num_sims=1536),
     "c3_ratchets_losses_3f": lambda: build_config("c3", num_sims=1024),
@@ -128,30 +159,99 @@ def test_staged_bit_exact_with_injected_normals_and_coefficients(case):
         assert rel_err(r.deltas, o.results.deltas) < 1e-12
 
 
+# Trigger prices (LSV.cs:619-638) are differences of MEAN fitted continuation values divided by df * (volume change).  A mean
+# fitted value is sum_k xbar_k beta_lk; where the basis is nearly collinear (the first half-hourly steps of C5: cond(X) ~ 1e14,
+# sum_k |xbar_k beta_lk| = 4e10 against a value of 2e2) that sum cancels catastrophically, so the reference's own formula is
+# only defined to eps * sum_k |xbar_k beta_lk| — any other summation order (MathNet's, the oracle's, the device's) moves the
+# price by that much.  Every trigger price is therefore held to 1e-9 of the price scale OR to 16 roundings of that
+# cancellation sum (divided by df * volume increment), whichever is larger; the metrics (profiles/r02_parity_metrics.json)
+# record per case the largest error, the largest error over the well-conditioned periods, and how many periods exceed 1e-9.
+METRICS = {}
+EPS = 2.220446049250313e-16
+
+
+@pytest.fixture(scope="module", autouse=True)
+def dump_metrics():
+    yield
+    out_dir = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    if METRICS and os.path.isdir(out_dir):
+        with open(os.path.join(out_dir, "parity_metrics.json"), "w") as f:
+            json.dump(METRICS, f, indent=1, sort_keys=True)
+
+
+def trigger_price_bounds(pb, o, price_scale):
+    """Per decision period: the absolute tolerance of a trigger price (see above) and the conditioning figures behind it.
+    Period p also inherits the noise of period p+1: its continuation values are regressions (or, in the current period,
+    plain means) of V_{p+1}, whose backward decisions were taken on the fitted values of regression p+1 — where those are
+    noise, near-ties resolve differently and move V_{p+1} by a realised, not a near-tied, difference."""
+    P, S = pb.n_periods, pb.n_sim_periods
+    noise = np.zeros(P)
+    amp_max = 0.0
+    for p in range(P - 1):
+        j = p - (P - S)
+        g = o.grid_count[p + 1]
+        if j < 0:   # current period: the continuation is a stored mean, no regression
+            continue
+        X = oracle.design_matrix(pb, o.results.spot_valuation[j], o.factors_valuation[j])
+        amp = float(np.max(np.abs(o.regression_coeffs[p, :g, :]) @ np.abs(X.mean(axis=0))))
+        vols = np.concatenate([o.results.trigger_inject[p, :, 0], o.results.trigger_withdraw[p, :, 0]])
+        vols = np.sort(vols[~np.isnan(vols)])
+        steps = np.diff(vols)
+        steps = steps[steps > 0]
+        inc = float(np.min(steps)) if len(steps) else float(pb.grid_spacing)
+        noise[p] = 16 * EPS * amp / (pb.settle_df[p] * inc)
+        amp_max = max(amp_max, amp)
+    tol = np.maximum(REL * price_scale, np.maximum(noise[:-1], noise[1:]))
+    return tol, amp_max, int(np.sum(tol > REL * price_scale))
+
+
 @pytest.mark.parametrize("case", sorted(CASES))
 def test_end_to_end_within_1e9_with_injected_normals(case, ctx):
     pb = CASES[case]()
     S, F, N = pb.n_sim_periods, pb.n_factors, int(pb.n_sims)
     zr, zv = anti_normals(3, S, F, N), anti_normals(4, S, F, N)
-    ref = oracle.calculate(pb, Rng.from_normals(zr), Rng.from_normals(zv), panels=("inject_withdraw",)).results
+    o = oracle.calculate(pb, Rng.from_normals(zr), Rng.from_normals(zv), keep_factors=True, panels=("inject_withdraw", "spot_valuation"))
+    ref = o.results
     got = ctx.calculate(pb, Rng.from_normals(zr), Rng.from_normals(zv), panels=("inject_withdraw",), decision_index=True)
-    assert rel_err(got.npv, ref.npv) < REL
-    assert rel_err(got.backward_npv, ref.backward_npv) < REL
-    assert rel_err(got.deltas, ref.deltas) < REL
-    assert rel_err(got.profile, ref.profile) < REL
-    assert material_flips(got, ref) == 0
     price_scale = float(np.max(pb.forward))
+    price_tol, amp_max, noisy = trigger_price_bounds(pb, o, price_scale)
+    m = {"npv_rel": rel_err(got.npv, ref.npv), "backward_npv_rel": rel_err(got.backward_npv, ref.backward_npv),
+         "delta_rel": rel_err(got.deltas, ref.deltas), "profile_rel": rel_err(got.profile, ref.profile),
+         "decision_flips": material_flips(got, ref),
+         "index_differences": int(np.sum(got.decision_index != ref.decision_index)),
+         "pv_by_sim_rel": rel_err(got.pv_by_sim, ref.pv_by_sim, max(abs(ref.npv), 1.0)),
+         "trigger_volume_rel": 0.0, "trigger_price_rel": 0.0, "trigger_price_rel_well_conditioned": 0.0,
+         "trigger_periods_noise_limited": noisy, "max_sum_abs_xbar_beta": amp_max,
+         "paths": N, "periods": pb.n_periods - 1, "basis": pb.n_basis}
+    METRICS[case] = m
+    price_ok = True
     for side, (gp, rp) in enumerate(((got.trigger_inject, ref.trigger_inject), (got.trigger_withdraw, ref.trigger_withdraw))):
         rows = comparable_trigger_rows(got, ref, side)
         cols = [2 * side, 2 * side + 1]
-        assert rel_err(got.trigger_summary[rows][:, cols[0]], ref.trigger_summary[rows][:, cols[0]]) < REL               # volumes
-        assert rel_err(got.trigger_summary[rows][:, cols[1]], ref.trigger_summary[rows][:, cols[1]], price_scale) < 1e-5  # prices: ratios of small differences; cond(X) ~ 1e13 at the first half-hourly steps
-        assert rel_err(gp[rows][..., 0], rp[rows][..., 0]) < REL
-        assert rel_err(gp[rows][..., 1], rp[rows][..., 1], price_scale) < 1e-5   # cond(X) ~ 1e13 at the first half-hourly steps
-    assert rel_err(got.pv_by_sim, ref.pv_by_sim, max(abs(ref.npv), 1.0)) < 1e-7
+        m["trigger_volume_rel"] = max(m["trigger_volume_rel"], rel_err(got.trigger_summary[rows][:, cols[0]], ref.trigger_summary[rows][:, cols[0]]),
+                                      rel_err(gp[rows][..., 0], rp[rows][..., 0]))
+        m["trigger_rows_excluded"] = m.get("trigger_rows_excluded", 0) + int((~rows).sum())
+        for prices_got, prices_ref in ((got.trigger_summary[:, cols[1]][:, None], ref.trigger_summary[:, cols[1]][:, None]), (gp[..., 1], rp[..., 1])):
+            err = np.abs(prices_got - prices_ref)
+            err = np.where(np.isnan(prices_ref) | ~rows[:, None], 0.0, err)
+            assert not np.any(np.isnan(err))
+            per_period = err.max(axis=1)
+            m["trigger_price_rel"] = max(m["trigger_price_rel"], float(per_period.max()) / price_scale)
+            tight = price_tol <= REL * price_scale
+            if tight.any():
+                m["trigger_price_rel_well_conditioned"] = max(m["trigger_price_rel_well_conditioned"], float(per_period[tight].max()) / price_scale)
+            price_ok = price_ok and bool(np.all(per_period <= price_tol))
+            m["trigger_periods_above_1e9"] = max(m.get("trigger_periods_above_1e9", 0), int(np.sum(per_period > REL * price_scale)))
+    assert m["npv_rel"] < REL and m["backward_npv_rel"] < REL
+    assert m["delta_rel"] < REL and m["profile_rel"] < REL
+    assert m["decision_flips"] == 0
+    assert m["trigger_volume_rel"] < REL
+    assert price_ok, "a trigger price is outside 1e-9 of the price scale and outside the cancellation noise of its period"
+    assert m["trigger_price_rel_well_conditioned"] < REL
+    assert m["pv_by_sim_rel"] < REL
 
 
-@pytest.mark.parametrize("case", ["c2_one_factor", "c3_ratchets_losses_3f", "reference_fixture_1f"])
+@pytest.mark.parametrize("case", ["c2_one_factor", "c3_ratchets_losses_3f", "c3_ragged_paths", "reference_fixture_1f", "c3_cubic_basis_k20"])
 def test_device_rng_matches_oracle_stream_and_npv_within_3_standard_errors(case, ctx):
     pb = CASES[case]()
     ref = oracle.calculate(pb, Rng.philox(11), Rng.philox(22), panels=("spot_regress", "spot_valuation")).results
@@ -258,6 +358,26 @@ def test_error_statuses(ctx):
     with pytest.raises(_native.LsmcError) as e:
         ctx.simulate(0, Rng(_abi.RNG_NORMALS))                            # normals mode without normals
     assert e.value.status == _abi.LSMC_EINVAL
+
+
+def test_backward_refuses_factors_of_the_valuation_set(ctx):
+    """The factor panel is shared by both simulation sets: after the valuation set has been generated a second
+    lsmc_backward would regress regression-set spot on valuation-set factors — it must be refused, not computed."""
+    pb = reference_problem(num_sims=256)
+    ctx.set_problem(pb)
+    ctx.simulate(0, Rng.philox(1))
+    ctx.backward()
+    ctx.simulate(1, Rng.philox(2))
+    with pytest.raises(_native.LsmcError) as e:
+        ctx.backward()
+    assert e.value.status == _abi.LSMC_EINVAL
+    ctx.forward()
+    first = ctx.get_results()
+    ctx.simulate(0, Rng.philox(1))                                        # regenerating the regression set makes it legal again
+    ctx.backward()
+    ctx.simulate(1, Rng.philox(2))
+    ctx.forward()
+    assert ctx.get_results().npv == first.npv
 
 
 def test_smoke_entry_point():
