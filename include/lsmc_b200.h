@@ -20,6 +20,7 @@
 #ifndef LSMC_B200_H
 #define LSMC_B200_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -211,6 +212,29 @@ int lsmc_get_grid(const lsmc_ctx* ctx, int period, double* out /*[max_grid]*/, i
 int lsmc_get_inventory_space(const lsmc_ctx* ctx, double* min_out /*[P]*/, double* max_out /*[P]*/);
 int lsmc_get_regression_coeffs(lsmc_ctx* ctx, int period, double* out /*[grid(period+1)][K]*/);
 int lsmc_get_sim_panel(lsmc_ctx* ctx, int set, int factor /*-1 = spot*/, double* out /*[S][N]*/);
+
+/*
+ * Allocation-free NPV statistics.  This entry point has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  It is the NPV / standard-error reduction that closes lsmc_forward (mean of pv_by_sim,
+ * LSV.cs:584, and the standard error over antithetic pair means), with the block partials in a file-scope __device__
+ * array of the library (32 KB per GPU that loads the library, held until exit) instead of cudaMalloc'ed scratch.
+ *
+ *   d_pv_by_sim       [n_sims] DEVICE pointer (e.g. the caller's own copy of lsmc_results.pv_by_sim)
+ *   antithetic_pairs  non-zero: paths 2m and 2m+1 are antithetic partners, the standard error is taken over pair means
+ *                     (only when n_sims is even, as lsmc_forward does)
+ *   d_out4            [4] DEVICE pointer: npv, npv_std_error, sum of pv, sum of squared deviations
+ *   cuda_stream       cudaStream_t of the CURRENT device (NULL = default stream); the call only enqueues three kernels
+ *   err, err_len      optional caller buffer for the error text
+ *
+ * Calls no cudaMalloc / cudaFree / allocating library routine.  n_sims above LSMC_NOALLOC_MAX_SIMS is rejected with
+ * LSMC_EUNSUPPORTED.  All calls on one GPU share the static array (it keeps the last call's contents; nothing in it has to
+ * start at zero): calls that overlap on the GPU race — serialise them on one stream.  The first call on a device looks the
+ * array's device address up (cudaGetSymbolAddress); make that call outside stream capture.
+ */
+#define LSMC_NOALLOC_MAX_SIMS (1 << 24)   /* 16,777,216 paths */
+int lsmc_npv_stats_noalloc(const double* d_pv_by_sim, int64_t n_sims, int antithetic_pairs, double* d_out4,
+                           void* cuda_stream, char* err, size_t err_len);
 
 /* Test hooks (tests/ only). */
 int lsmc_debug_set_regression_coeffs(lsmc_ctx* ctx, int period, const double* coeffs /*[grid(period+1)][K]*/);

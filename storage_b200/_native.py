@@ -17,7 +17,7 @@ EXPORTS = (
     "lsmc_calculate", "lsmc_set_problem", "lsmc_get_layout", "lsmc_request_outputs", "lsmc_simulate", "lsmc_backward",
     "lsmc_forward", "lsmc_get_results", "lsmc_get_timings", "lsmc_get_grid", "lsmc_get_inventory_space",
     "lsmc_get_regression_coeffs", "lsmc_get_sim_panel", "lsmc_debug_set_regression_coeffs", "lsmc_debug_keep_values",
-    "lsmc_debug_get_values",
+    "lsmc_debug_get_values", "lsmc_npv_stats_noalloc",
 )
 
 
@@ -185,6 +185,18 @@ class Context:
         out = np.zeros((g, self.layout().n_sims))
         self._check(lib().lsmc_debug_get_values(self._h, C.c_int(period), out.ctypes.data_as(_dp)))
         return out
+
+
+def npv_stats_noalloc(d_pv_by_sim, n_sims, antithetic_pairs, d_out4, cuda_stream=0):
+    """lsmc_npv_stats_noalloc (include/lsmc_b200.h): device pointers as integers; enqueues on `cuda_stream`, allocates nothing."""
+    err = C.create_string_buffer(256)
+    fn = lib().lsmc_npv_stats_noalloc
+    fn.argtypes = [C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_char_p, C.c_size_t]
+    fn.restype = C.c_int
+    rc = fn(C.c_void_p(d_pv_by_sim), C.c_int64(n_sims), C.c_int(int(bool(antithetic_pairs))), C.c_void_p(d_out4),
+            C.c_void_p(cuda_stream), err, C.c_size_t(len(err)))
+    if rc != 0:
+        raise LsmcError(rc, err.value.decode())
 
 
 def comm_setup(ctx, rank, world, dist):
