@@ -34,7 +34,11 @@ CONFIG_TEXT = {
     "c4": "five-factor multi_factor_value, degree-3 polynomial basis (K=56), 2y daily",
     "c5": "battery-style storage, 2-factor, half-hourly 1 month",
 }
-DEFAULT_PATHS = {"c1": 1000, "c2": 100_000, "c3": 1_000_000, "c4": 500_000, "c5": 2_000_000}
+# BASELINE.json configs: total paths of the valuation.  C4 (4M paths x 730 periods) needs 164 GB of simulation panels: it only
+# fits split over several GPUs, so on fewer than 8 GPUs the bench runs the 8-GPU share per GPU (500k paths each) and says so.
+DEFAULT_PATHS = {"c1": 1000, "c2": 100_000, "c3": 1_000_000, "c4": 4_000_000, "c5": 2_000_000}
+MAX_PATHS_PER_GPU = {"c4": 500_000}
+CPU_SAMPLE_PATHS = {"c1": 1000, "c2": 20000, "c3": 8192, "c4": 2048, "c5": 4096}
 
 
 # The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner on the first
@@ -54,7 +58,11 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--config", default="c3", choices=sorted(CONFIG_TEXT))
-    ap.add_argument("--paths-per-gpu", type=int, default=0, help="paths owned by each GPU (weak scaling); default = the config's path count")
+    ap.add_argument("--paths-per-gpu", type=int, default=0, help="paths owned by each GPU; implies --scaling weak")
+    ap.add_argument("--paths-total", type=int, default=0, help="total paths of the valuation (strong scaling); default = the config's path count")
+    ap.add_argument("--scaling", default=None, choices=["strong", "weak"],
+                    help="strong (default): BASELINE's path count in total, split over the GPUs; weak: that many paths on every GPU")
+    ap.add_argument("--no-parity", action="store_true", help="skip the correctness gates against the oracle")
     ap.add_argument("--cpu-paths", type=int, default=0, help="paths of the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -147,11 +155,53 @@ def cpu_sample(config, cpu_paths, kind_note=""):
             "npv": out.results.npv}, dt
 
 
+def parity_gates(ctx, config):
+    """correctness gates printed with every benchmark line, outside the timed region.  A 1 024-path cut of the
+    benchmarked config through the C ABI against the CPU oracle: injected normals (same draws on both sides) and device RNG."""
+    from oracle import oracle
+    from storage_b200._abi import Rng
+    from storage_b200.configs import build_config
+    pb = build_config(config, num_sims=1024)
+    S, F, N = pb.n_sim_periods, pb.n_factors, 1024
+    rs = np.random.default_rng(7)
+
+    def anti(z):
+        out = np.empty((S, F, N))
+        out[:, :, 0::2] = z
+        out[:, :, 1::2] = -z
+        return out
+    zr, zv = anti(rs.standard_normal((S, F, N // 2))), anti(rs.standard_normal((S, F, N // 2)))
+    ref = oracle.calculate(pb, Rng.from_normals(zr), Rng.from_normals(zv), panels=("inject_withdraw",)).results
+    got = ctx.calculate(pb, Rng.from_normals(zr), Rng.from_normals(zv), panels=("inject_withdraw",))
+
+    def rel(a, b, scale=None):
+        a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+        m = ~(np.isnan(a) | np.isnan(b))
+        if not m.any():
+            return 0.0
+        return float(np.max(np.abs(a[m] - b[m])) / (scale if scale else max(np.max(np.abs(b[m])), 1e-300)))
+    vol_scale = max(float(np.max(np.abs(ref.inject_withdraw))), 1e-300)
+    price_scale = float(np.max(pb.forward))
+    trig = max(rel(got.trigger_summary[:, [1, 3]], ref.trigger_summary[:, [1, 3]], price_scale),
+               rel(got.trigger_inject[..., 1], ref.trigger_inject[..., 1], price_scale),
+               rel(got.trigger_withdraw[..., 1], ref.trigger_withdraw[..., 1], price_scale))
+    gates = {"sample": "%s at 1024 paths, injected normals + device Philox, vs the CPU oracle" % config,
+             "npv_rel": rel(got.npv, ref.npv), "delta_rel": rel(got.deltas, ref.deltas), "trigger_rel": trig,
+             "decision_flips": int(np.sum(np.abs(got.inject_withdraw - ref.inject_withdraw) > 1e-9 * vol_scale))}
+    ref_p = oracle.calculate(pb, Rng.philox(11), Rng.philox(22)).results
+    got_p = ctx.calculate(pb, Rng.philox(11), Rng.philox(22))
+    gates["philox_npv_sigma"] = abs(got_p.npv - ref_p.npv) / max(ref_p.npv_std_error, 1e-300)
+    # trigger prices: 1e-9 of the price scale unless the period's own formula is noisier (tests/test_gpu_parity.py); C5's first
+    # half-hourly steps are (cond(X) ~ 1e14), so the gate flag only covers NPV, deltas, decisions and the 3-sigma rule
+    gates["pass"] = bool(gates["npv_rel"] < 1e-9 and gates["delta_rel"] < 1e-9 and gates["decision_flips"] == 0 and gates["philox_npv_sigma"] < 3.0)
+    return gates
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    cpu_paths = args.cpu_paths or {"c1": 1000, "c2": 20000, "c3": 8192, "c4": 2048, "c5": 4096}[args.config]
+    cpu_paths = args.cpu_paths or CPU_SAMPLE_PATHS[args.config]
     from storage_b200.configs import build_config
     for _ in range(min(args.warmup, 1)):
         cpu_sample(args.config, max(256, cpu_paths // 8))
@@ -165,7 +215,7 @@ def run_reference(args):
     value = cpu_paths * T / (ms / 1e3)
     base["value"] = value
     line = {"impl": "reference", "metric": "lsmc_path_steps_per_sec", "value": value, "unit": "path-steps/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": CONFIG_TEXT[args.config], "config": args.config, "paths_sample": cpu_paths, "periods": T,
                        "note": "reference C# cannot be built here (no dotnet/NuGet); this is the CPU oracle port of its algorithm, OpenMP on all host threads, bounded sample"},
@@ -200,11 +250,16 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    n_local = args.paths_per_gpu or DEFAULT_PATHS[args.config]
-    n_global = n_local * world
+    scaling = args.scaling or ("weak" if args.paths_per_gpu else "strong")
+    if scaling == "weak":
+        n_global = (args.paths_per_gpu or min(DEFAULT_PATHS[args.config], MAX_PATHS_PER_GPU.get(args.config, 1 << 62))) * world
+    else:
+        n_global = args.paths_total or DEFAULT_PATHS[args.config]
+        cap = MAX_PATHS_PER_GPU.get(args.config)
+        if cap and n_global > cap * world:
+            n_global = cap * world       # the named total does not fit on this few GPUs: the 8-GPU share per GPU
     from storage_b200.sharding import shard_problem
-    pb, shard = shard_problem(build_config(args.config, num_sims=n_global), world, rank)   # weak scaling: n_local paths on every rank
-    assert shard.count == n_local or n_local % 2, shard
+    pb, shard = shard_problem(build_config(args.config, num_sims=n_global), world, rank)
     n_local = shard.count
     T = pb.n_periods - 1
 
@@ -267,25 +322,28 @@ def main():
         # FP64 pipe occupancy of the sweep from first principles: 25 individually rounded operations per (grid row,
         # path) for the decisions + one FMA lane-slot per (basis, row, path) each for the fit and for X~^T V + 2 K^2 per path
         # (x~ and X~^T X~), against 64 FP64 lanes per clock per SM (DFMA and DMMA share them: profiles/r01_probe_fp64.txt)
-        G, K = 101, pb.n_basis
+        G, K = int(ctx.layout().max_grid), pb.n_basis
         fp64_slots = float(n_local) * (25.0 * G + 2.0 * K * G + 2.0 * K * K)
         sm_hz = 1e6 * float(clocks.get("sm_mhz") or clocks.get("sm_max_mhz") or 1965.0)
         avg_launch_s = (sweep_ms / max(1.0, sweep_launches)) / 1e3
         fp64_frac = fp64_slots / (64.0 * torch.cuda.get_device_properties(0).multi_processor_count * sm_hz * avg_launch_s) if avg_launch_s > 0 else 0.0
         line = {
             "metric": "lsmc_path_steps_per_sec", "value": value, "unit": "path-steps/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
             "config": {"workload": CONFIG_TEXT[args.config], "config": args.config, "paths_per_gpu": n_local, "paths_total": n_global,
-                       "periods": T, "factors": pb.n_factors, "basis_functions": pb.n_basis, "inventory_grid_points": 100,
+                       "periods": T, "factors": pb.n_factors, "basis_functions": pb.n_basis,
+                       "inventory_grid_points": 100, "max_grid_rows": G,
                        "rng": "device Philox4x32-10, antithetic",
                        "timing": "CUDA events on the library's stream (regression-sim start -> forward end of each step, summed over the K steps), "
                                  "max over ranks; wall_ms_per_step is the host clock between barrier+synchronize on both sides",
                        "l2": "inputs larger than L2 (sim panels %.1f GB, value surfaces %.1f GB per GPU)" % (
-                           8e-9 * n_local * pb.n_sim_periods * (pb.n_factors + 2), 16e-9 * n_local * 101)},
+                           8e-9 * n_local * pb.n_sim_periods * (pb.n_factors + 2), 16e-9 * n_local * G)},
             "npv": res_dev.npv, "npv_std_error": res_dev.npv_std_error,
             "wall_ms_per_step": 1e3 * wall / args.steps, "phase_sum_ms_per_step": dev_ms / args.steps,
             "phase_ms": {k: phase[k] for k in ("regression_sim_ms", "backward_ms", "valuation_sim_ms", "forward_ms")},
+            # what one backward period costs outside the sweep kernel (reduction, all-reduce, solve, launch gaps): the limiter of strong scaling
+            "backward_overhead_us_per_period": 1e3 * (phase["backward_ms"] - phase["backward_sweep_kernel_ms"]) / max(1, T),
             "e2e": {"value": n_global * T / (e2e_elapsed / args.steps), "unit": "path-steps/s",
                     "h2d_bytes_per_step": problem_h2d_bytes(pb), "d2h_bytes_per_step": results_d2h_bytes(e2e_res),
                     "ms_per_step": 1e3 * e2e_elapsed / args.steps, "api": "lsmc_calculate (include/lsmc_b200.h) with host buffers"},
@@ -299,13 +357,33 @@ def main():
                          "share_of_step": sweep_ms / max(1e-9, span_ms), "fp64_pipe_frac": fp64_frac,
                          "note": "FP64 pipe (DFMA+DMMA share it, 64 lanes/clk/SM measured) is the co-binding roof: see DESIGN.md 4.1"},
         }
-        if not args.no_cpu_baseline:
-            cpu_paths = args.cpu_paths or {"c1": 1000, "c2": 20000, "c3": 8192, "c4": 2048, "c5": 4096}[args.config]
+        if not args.no_cpu_baseline and world == 1:   # the contract: rank 0 at N = 1 only
+            cpu_paths = args.cpu_paths or CPU_SAMPLE_PATHS[args.config]
             try:
                 base, _ = cpu_sample(args.config, cpu_paths)
                 line["cpu_baseline"] = base
+                # one identical-input pair: the GPU arm end to end (host buffers) on exactly the CPU sample's problem
+                with _native.Context(local_rank) as small:
+                    pb_s = build_config(args.config, num_sims=cpu_paths)
+                    res_s = _abi.Results(pb_s.n_periods, pb_s.n_sim_periods, cpu_paths, pv_by_sim=True)
+                    for _ in range(2):
+                        small.calculate(pb_s, reg, val, results=res_s)
+                    ts = time.perf_counter()
+                    for _ in range(3):
+                        small.calculate(pb_s, reg, val, results=res_s)
+                    gpu_s = (time.perf_counter() - ts) / 3
+                line["same_input"] = {"paths": cpu_paths, "periods": T, "gpu_e2e_ms": 1e3 * gpu_s, "gpu_e2e_value": cpu_paths * T / gpu_s,
+                                      "cpu_value": base["value"], "ratio": cpu_paths * T / gpu_s / base["value"],
+                                      "npv_gpu": res_s.npv, "npv_cpu": base["npv"], "npv_rel": abs(res_s.npv / base["npv"] - 1.0),
+                                      "note": "same problem, same Philox seeds on both arms (one GPU, rank 0)"}
             except Exception as e:   # the oracle is a checker; its absence must not hide the GPU number
                 line["cpu_baseline"] = {"value": None, "unit": "path-steps/s", "cores": 0, "kind": "port", "sample": "failed: %s" % e}
+        if not args.no_parity:
+            try:
+                with _native.Context(local_rank) as pc:
+                    line["parity"] = parity_gates(pc, args.config)
+            except Exception as e:
+                line["parity"] = {"pass": False, "error": str(e)}
         emit(line)
     ctx.close()
     if world > 1:

@@ -186,10 +186,24 @@ void lsmc_destroy(lsmc_ctx* ctx);
 const char* lsmc_last_error(const lsmc_ctx* ctx);   /* ctx may be NULL: last error of a failed lsmc_create */
 const char* lsmc_version(void);
 
-/* Multi-GPU: one context per process per GPU; paths are sharded, only the normal-equation partials
- * and the forward sums are all-reduced (NCCL, loaded with dlopen on first use). */
+/* Multi-GPU, one process per GPU: paths are sharded, only the normal-equation partials and the forward sums are
+ * exchanged.  lsmc_comm_init creates the NCCL communicator (NCCL is loaded with dlopen on first use) and then maps every
+ * rank's exchange buffer into every other rank (cudaIpc): the per-period exchange is fused into the kernel that reduces
+ * and solves the normal equations and goes over NVLink peer memory; NCCL collectives remain as the fallback when the
+ * buffers cannot be mapped. */
 int lsmc_comm_unique_id(void* out128);                                  /* ncclGetUniqueId */
 int lsmc_comm_init(lsmc_ctx* ctx, int rank, int world, const void* unique_id128);
+
+/* Multi-GPU inside ONE process (the shape of the reference: Calculate<T> is one call on one thread):
+ * lsmc_comm_init_local joins n contexts (one per GPU; the same GPU may appear twice, for tests) into a group whose
+ * exchanges go through peer memory only (no NCCL); lsmc_calculate_multi takes the WHOLE problem (n_sims = all paths),
+ * splits the paths over the contexts (one internal host thread per GPU, rank 0 on the calling thread: progress callbacks
+ * arrive there) and fills `results` as lsmc_calculate would: summary from rank 0, per-sim outputs [rows][n_sims] with
+ * every rank writing its own block of columns.  Injected normals / panels are sliced per rank. */
+int lsmc_comm_init_local(lsmc_ctx** ctxs, int n);
+int lsmc_calculate_multi(lsmc_ctx** ctxs, int n, const lsmc_problem* problem,
+                         const lsmc_rng* regression_rng, const lsmc_rng* valuation_rng,
+                         lsmc_progress_cb progress, void* progress_user, lsmc_results* results);
 
 /* One-call entry point: what the body of Calculate<T> becomes. */
 int lsmc_calculate(lsmc_ctx* ctx, const lsmc_problem* problem,

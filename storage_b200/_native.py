@@ -13,7 +13,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("LSMC_B200_LIB") or os.path.join(_HERE, "liblsmc_b200.so")   # override: development builds only
 
 EXPORTS = (
-    "lsmc_version", "lsmc_create", "lsmc_destroy", "lsmc_last_error", "lsmc_comm_unique_id", "lsmc_comm_init",
+    "lsmc_version", "lsmc_create", "lsmc_destroy", "lsmc_last_error", "lsmc_comm_unique_id", "lsmc_comm_init", "lsmc_comm_init_local",
+    "lsmc_calculate_multi",
     "lsmc_calculate", "lsmc_set_problem", "lsmc_get_layout", "lsmc_request_outputs", "lsmc_simulate", "lsmc_backward",
     "lsmc_forward", "lsmc_get_results", "lsmc_get_timings", "lsmc_get_grid", "lsmc_get_inventory_space",
     "lsmc_get_regression_coeffs", "lsmc_get_sim_panel", "lsmc_debug_set_regression_coeffs", "lsmc_debug_keep_values",
@@ -185,6 +186,39 @@ class Context:
         out = np.zeros((g, self.layout().n_sims))
         self._check(lib().lsmc_debug_get_values(self._h, C.c_int(period), out.ctypes.data_as(_dp)))
         return out
+
+
+class Group:
+    """n contexts of ONE process joined by lsmc_comm_init_local: one call values the whole problem on all of them
+    (lsmc_calculate_multi).  `devices` may name the same GPU twice (tests on a one-GPU box)."""
+
+    def __init__(self, devices):
+        self.contexts = [Context(d) for d in devices]
+        self._arr = (C.c_void_p * len(self.contexts))(*[c._h for c in self.contexts])
+        rc = lib().lsmc_comm_init_local(self._arr, C.c_int(len(self.contexts)))
+        if rc != 0:
+            raise LsmcError(rc, lib().lsmc_last_error(self.contexts[0]._h).decode())
+
+    def calculate(self, problem, regression_rng, valuation_rng, results=None, panels=(), decision_index=False, on_progress=None):
+        if results is None:
+            results = _abi.Results(problem.n_periods, problem.n_sim_periods, int(problem.n_sims), panels=panels,
+                                   decision_index=decision_index)
+        cp, cr, cv, cres = problem.c_struct(), regression_rng.c_struct(), valuation_rng.c_struct(), results.c_struct()
+        cb = _make_cb(on_progress)
+        rc = lib().lsmc_calculate_multi(self._arr, C.c_int(len(self.contexts)), C.byref(cp), C.byref(cr), C.byref(cv), cb, None, C.byref(cres))
+        if rc != 0:
+            raise LsmcError(rc, lib().lsmc_last_error(self.contexts[0]._h).decode())
+        return results.sync_scalars()
+
+    def close(self):
+        for c in self.contexts:
+            c.close()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
 
 
 def npv_stats_noalloc(d_pv_by_sim, n_sims, antithetic_pairs, d_out4, cuda_stream=0):

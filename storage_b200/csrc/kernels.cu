@@ -6,6 +6,7 @@
 //   K2 reduce/solve kernels  partial reduction + scaled Cholesky solve of the K x K system for all grid points
 //   K4 forward_kernel        forward inventory / cash-flow simulation of one period (LSV.cs:426-480)
 #include "kernels.h"
+#include "solve_device.cuh"
 
 #include <map>
 #include <mutex>
@@ -297,128 +298,12 @@ void launch_reduce_partials(const double* partial, int n_parts, int n_elem, doub
 template <int KT>
 __global__ void __launch_bounds__(128) solve_kernel(SolveParams sp) {
     extern __shared__ double sm[];
-    const int K = sp.K, G = sp.G, ld = sp.ncols, tid = threadIdx.x;
-    const double* __restrict__ red = sp.reduced;
-    if (sp.accum_mode == 2) {   // current period: continuation = mean over sims (LSV.cs:171-182)
-        for (int i = tid; i < G; i += blockDim.x) {
-            double* b = sp.beta + (size_t)i * sp.ldb;
-            b[0] = red[i] / (double)sp.n_global;
-            for (int k = 1; k < sp.ldb; k++) b[k] = 0.0;
-        }
-        return;
-    }
-    double* A = sm;                 // [K][K] scaled Gram -> Cholesky factor (lower)
-    double* Graw = A + K * K;       // [K][K] unscaled Gram
-    double* dscale = Graw + K * K;  // [K]
-    double* Tm = dscale + K;        // [K][K] preconditioner (when present)
     __shared__ int dropped[64];
-    const int gcol = 8 * sp.NT;
-    const double* T = sp.precond;
-    for (int k = tid; k < K; k += blockDim.x) {
-        double gkk = red[(size_t)k * ld + gcol + k];
-        const bool flagged = T && T[(size_t)K * K + k] != 0.0;   // column found dependent by the preconditioner's QR
-        dscale[k] = (gkk > 0.0 && !flagged) ? rsqrt(gkk) : 0.0;
-        dropped[k] = (gkk > 0.0 && !flagged) ? 0 : 1;
-    }
-    if (T) for (int e = tid; e < K * K; e += blockDim.x) Tm[e] = T[e];
-    __syncthreads();
-    for (int e = tid; e < K * K; e += blockDim.x) {
-        int r = e / K, c = e % K;
-        // symmetrise: the two triangles come from different DMMA tiles and may differ in the last bit
-        double gv = 0.5 * (red[(size_t)r * ld + gcol + c] + red[(size_t)c * ld + gcol + r]);
-        Graw[e] = gv;
-        A[e] = gv * dscale[r] * dscale[c];
-    }
-    __syncthreads();
-    // the thread's first right-hand side is fetched now: its latency hides behind the factorisation
-    double r0[KT];
-#pragma unroll
-    for (int k = 0; k < KT; k++) r0[k] = (k < K && tid < G) ? red[(size_t)k * ld + tid] : 0.0;
-    // Cholesky by warp 0 (lane = row, rows lane and lane + 32): no block-wide barriers in the column loop
-    if (tid < 32) {
-        for (int j = 0; j < K; j++) {
-            if (tid == 0) {
-                double piv = A[j * K + j];
-                if (dropped[j] || !(piv > sp.pivot_tol)) { dropped[j] = 1; A[j * K + j] = 1.0; }
-                else A[j * K + j] = sqrt(piv);
-            }
-            __syncwarp();
-            const bool dj = dropped[j];
-            const double ljj = A[j * K + j];
-            for (int i = j + 1 + tid; i < K; i += 32) A[i * K + j] = dj ? 0.0 : A[i * K + j] / ljj;
-            __syncwarp();
-            for (int i = j + 1 + tid; i < K; i += 32) {
-                const double aij = A[i * K + j];
-                for (int k = j + 1; k <= i; k++) A[i * K + k] -= aij * A[k * K + j];
-            }
-            __syncwarp();
-        }
-    }
-    __syncthreads();
-    double* invd = Tm + K * K;      // [K] reciprocals of the factor's diagonal: the substitutions multiply instead of dividing
-    for (int k = tid; k < K; k += blockDim.x) invd[k] = 1.0 / A[k * K + k];
-    __syncthreads();
-    // each thread: one right-hand side at a time, vectors in registers (KT = compile-time bound of K)
-    for (int i = tid; i < G; i += blockDim.x) {
-        double x[KT], r[KT], y[KT];
-#pragma unroll
-        for (int k = 0; k < KT; k++) { r[k] = (i == tid) ? r0[k] : (k < K ? red[(size_t)k * ld + i] : 0.0); x[k] = 0.0; y[k] = 0.0; }
-#pragma unroll 1
-        for (int pass = 0; pass < 2; pass++) {
-#pragma unroll
-            for (int k = 0; k < KT; k++) {   // L y = D r
-                if (k < K) {
-                    double s = r[k] * dscale[k];
-#pragma unroll
-                    for (int m = 0; m < k; m++) s -= A[k * K + m] * y[m];
-                    y[k] = dropped[k] ? 0.0 : s * invd[k];
-                }
-            }
-#pragma unroll
-            for (int k = KT - 1; k >= 0; k--) {   // L^T z = y
-                if (k < K) {
-                    double s = y[k];
-#pragma unroll
-                    for (int m = k + 1; m < KT; m++) if (m < K) s -= A[m * K + k] * y[m];
-                    y[k] = dropped[k] ? 0.0 : s * invd[k];
-                }
-            }
-#pragma unroll
-            for (int k = 0; k < KT; k++) if (k < K) x[k] += y[k] * dscale[k];
-            if (pass == 0) {   // residual of the unscaled system
-#pragma unroll
-                for (int k = 0; k < KT; k++) {
-                    if (k < K) {
-                        double s = red[(size_t)k * ld + i];
-#pragma unroll
-                        for (int m = 0; m < KT; m++) if (m < K) s = fma(-Graw[k * K + m], x[m], s);
-                        r[k] = dropped[k] ? 0.0 : s;
-                    }
-                }
-            }
-        }
-        double* b = sp.beta + (size_t)i * sp.ldb;
-        if (T) {   // back to the monomial basis: beta = T x
-#pragma unroll
-            for (int k = 0; k < KT; k++) {
-                if (k < K) {
-                    double acc = 0.0;
-#pragma unroll
-                    for (int m = k; m < KT; m++) if (m < K) acc = fma(Tm[k * K + m], x[m], acc);
-                    b[k] = acc;
-                }
-            }
-            for (int k = K; k < sp.ldb; k++) b[k] = 0.0;
-        } else {
-#pragma unroll
-            for (int k = 0; k < KT; k++) if (k < K) b[k] = x[k];
-            for (int k = K; k < sp.ldb; k++) b[k] = 0.0;
-        }
-    }
+    solve_cta<KT>(sp, GlobalRed{sp.reduced, sp.ncols}, sm, dropped, 0, 1);
 }
 
 void launch_solve(const SolveParams& sp, cudaStream_t stream) {
-    size_t smem = sizeof(double) * ((size_t)3 * sp.K * sp.K + 2 * sp.K);
+    size_t smem = solve_smem_bytes(sp.K);
     if (sp.K <= 4) solve_kernel<4><<<1, 128, smem, stream>>>(sp);
     else if (sp.K <= 8) solve_kernel<8><<<1, 128, smem, stream>>>(sp);
     else if (sp.K <= 12) solve_kernel<12><<<1, 128, smem, stream>>>(sp);

@@ -10,8 +10,16 @@
 #include <string>
 #include <vector>
 
+#include <atomic>
+#include <condition_variable>
+#include <functional>
+#include <memory>
+#include <mutex>
+#include <thread>
+
 #include "host_plan.h"
 #include "kernels.h"
+#include "peer.h"
 
 using namespace lsmc;
 
@@ -44,6 +52,24 @@ struct DevBuf {
     ~DevBuf() { release(); }
 };
 
+// Page-locked host staging for the small read-backs of a valuation.  A cudaMemcpyAsync to PAGEABLE memory blocks inside
+// the runtime until the stream has drained; with several ranks in one process (one host thread per GPU) the stream may be
+// waiting for a peer whose host thread then cannot launch — every device-to-host copy between the first and the last
+// exchange of a valuation therefore lands here and is followed by a plain cudaStreamSynchronize.
+struct PinnedBuf {
+    double* p = nullptr;
+    size_t n = 0;
+    void alloc(size_t count) {
+        if (count <= n && p) return;
+        release();
+        CUDA_CHECK(cudaMallocHost(&p, count * sizeof(double)));
+        n = count;
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; n = 0; }
+    ~PinnedBuf() { release(); }
+};
+constexpr size_t kPinScalars = 16;   // [0] backward sum, [1..3] final sums, [4..6] squared deviations, [8] error flag (as int)
+
 // ---- NCCL through dlopen: the library has no link-time dependency on it --------------------------------------
 struct NcclApi {
     void* handle = nullptr;
@@ -51,6 +77,7 @@ struct NcclApi {
     int (*CommInitRank)(void**, int, char[128], int) = nullptr;   // ncclUniqueId is a 128-byte struct passed by value
     int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
     int (*Broadcast)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*AllGather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
     int (*CommDestroy)(void*) = nullptr;
     const char* (*GetErrorString)(int) = nullptr;
     bool load(std::string& err) {
@@ -62,14 +89,71 @@ struct NcclApi {
         CommInitRank = (int (*)(void**, int, char[128], int))dlsym(handle, "ncclCommInitRank");
         AllReduce = (int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t))dlsym(handle, "ncclAllReduce");
         Broadcast = (int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t))dlsym(handle, "ncclBroadcast");
+        AllGather = (int (*)(const void*, void*, size_t, int, void*, cudaStream_t))dlsym(handle, "ncclAllGather");
         CommDestroy = (int (*)(void*))dlsym(handle, "ncclCommDestroy");
         GetErrorString = (const char* (*)(int))dlsym(handle, "ncclGetErrorString");
-        if (!GetUniqueId || !CommInitRank || !AllReduce || !Broadcast || !CommDestroy) { err = "libnccl is missing symbols"; return false; }
+        if (!GetUniqueId || !CommInitRank || !AllReduce || !Broadcast || !AllGather || !CommDestroy) { err = "libnccl is missing symbols"; return false; }
         return true;
     }
 };
 NcclApi g_nccl;
 struct NcclId { char bytes[128]; };
+
+// The exchange buffer of one rank and its view of the other ranks' buffers (peer.h).
+struct PeerComm {
+    bool ready = false;               // every rank's buffer is mapped here
+    double* buf = nullptr;            // this rank's allocation: slots [2][world][kPeerSlotDoubles] + the arrival counter
+    int alloc_world = 0;
+    PeerView view{};
+    unsigned long long target = 0;    // cumulative arrivals expected at this rank's counter
+    unsigned long long epoch = 0;     // exchanges started (the same sequence on every rank)
+    std::vector<void*> opened;        // cudaIpcOpenMemHandle mappings to close
+
+    static size_t bytes(int world) { return (size_t)2 * world * kPeerSlotDoubles * sizeof(double) + 256; }
+    unsigned long long* counter_of(double* base, int world) const { return reinterpret_cast<unsigned long long*>(base + (size_t)2 * world * kPeerSlotDoubles); }
+    void allocate(int world) {
+        if (buf && alloc_world == world) return;
+        release();
+        CUDA_CHECK(cudaMalloc(&buf, bytes(world)));
+        CUDA_CHECK(cudaMemset(buf, 0, bytes(world)));
+        alloc_world = world;
+        target = 0; epoch = 0;
+    }
+    void self_only() {   // one rank: the "exchange" is the grid barrier of the tail kernel
+        allocate(1);
+        view = PeerView{};
+        view.rank = 0; view.world = 1; view.slots[0] = buf; view.counter[0] = counter_of(buf, 1);
+        ready = true;
+    }
+    void release() {
+        for (void* p : opened) cudaIpcCloseMemHandle(p);
+        opened.clear();
+        if (buf) cudaFree(buf);
+        buf = nullptr; alloc_world = 0; ready = false;
+    }
+    // parity and cumulative target of the next exchange in which every rank arrives with `ctas` CTAs
+    void next(int ctas, int* parity, unsigned long long* tgt) {
+        *parity = (int)(epoch & 1);
+        epoch++;
+        target += (unsigned long long)ctas * (unsigned long long)view.world;
+        *tgt = target;
+    }
+    ~PeerComm() { release(); }
+};
+
+// Ranks that live in one process (one host thread each): shared cancellation flag and a host barrier.
+struct LocalGroup {
+    std::atomic<int> cancelled{0};
+    std::mutex mu;
+    std::condition_variable cv;
+    int waiting = 0, generation = 0;
+    void barrier(int n) {
+        std::unique_lock<std::mutex> lock(mu);
+        const int gen = generation;
+        if (++waiting == n) { waiting = 0; generation++; cv.notify_all(); }
+        else cv.wait(lock, [&] { return generation != gen; });
+    }
+};
 
 }  // namespace
 
@@ -104,10 +188,15 @@ struct lsmc_ctx {
     // multi-GPU
     void* comm = nullptr;
     int rank = 0, world = 1;
+    PeerComm peer;                       // exchange over peer memory (world == 1: the tail kernel's grid barrier)
+    bool use_tail = true;                // fused reduce + exchange + solve kernel (tail.cu); false: reduce -> NCCL -> solve
+    std::shared_ptr<LocalGroup> group;   // ranks of one process (lsmc_comm_init_local)
+    int64_t out_pitch = 0, out_col0 = 0; // per-sim outputs of lsmc_get_results: row pitch / first column in the caller's buffers (0: n_sims, 0)
 
     // results staged on host
     double backward_npv = 0.0, npv = 0.0, npv_se = 0.0, final_inventory_sum = 0.0, terminal_pv_sum = 0.0;
     std::vector<double> h_fwd;   // [P-1][nsum]
+    PinnedBuf pin;               // kPinScalars scalars, then the [P-1][nsum] forward sums
 
     // timings
     lsmc_timings tm{};
@@ -124,19 +213,40 @@ struct lsmc_ctx {
         while (ev.size() <= i) { cudaEvent_t e; CUDA_CHECK(cudaEventCreate(&e)); ev.push_back(e); }
         return ev[i];
     }
+    void peer_small(double* buf, size_t count, int root) {
+        for (size_t o = 0; o < count; o += kPeerSlotDoubles) {
+            PeerSmallParams pp{};
+            pp.buf = buf + o; pp.count = (int)std::min<size_t>(kPeerSlotDoubles, count - o); pp.root = root;
+            pp.peers = peer.view; pp.error_flag = error_flag.p;
+            peer.next(1, &pp.parity, &pp.target);
+            launch_peer_small(pp, stream);
+            tm.kernel_launches++;
+        }
+    }
     void allreduce(double* buf, size_t count) {
         if (world <= 1) return;
+        if (peer.ready && (use_tail || !comm)) { peer_small(buf, count, -1); return; }
         int rc = g_nccl.AllReduce(buf, buf, count, /*ncclFloat64*/ 8, /*ncclSum*/ 0, comm, stream);
         if (rc != 0) throw Error(LSMC_ECUDA, std::string("ncclAllReduce: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "error"));
     }
     void broadcast0(double* buf, size_t count) {
         if (world <= 1) return;
+        if (peer.ready && (use_tail || !comm)) { peer_small(buf, count, 0); return; }
         int rc = g_nccl.Broadcast(buf, buf, count, /*ncclFloat64*/ 8, /*root*/ 0, comm, stream);
         if (rc != 0) throw Error(LSMC_ECUDA, std::string("ncclBroadcast: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "error"));
     }
 };
 
 namespace {
+
+// development (LSMC_TRACE_HOST): host-side checkpoints of every rank on stderr
+static const bool g_trace_host = getenv("LSMC_TRACE_HOST") != nullptr;
+#define HOST_TRACE(c, what)                                                                                                       \
+    do {                                                                                                                          \
+        if (g_trace_host)                                                                                                         \
+            fprintf(stderr, "[rank %d %.6f] %s\n", (c)->rank,                                                                     \
+                    std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(), what);            \
+    } while (0)
 
 template <typename Fn>
 int guarded(lsmc_ctx* ctx, Fn&& fn) {
@@ -156,15 +266,76 @@ int guarded(lsmc_ctx* ctx, Fn&& fn) {
 void require(bool ok, int status, const char* msg) { if (!ok) throw Error(status, msg); }
 
 void check_device_error_flag(lsmc_ctx* c) {
-    int flag = 0;
-    CUDA_CHECK(cudaMemcpyAsync(&flag, c->error_flag.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    int* h_flag = reinterpret_cast<int*>(c->pin.p + 8);
+    CUDA_CHECK(cudaMemcpyAsync(h_flag, c->error_flag.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    const int flag = *h_flag;
     switch (flag) {
         case 0: return;
         case 1: case 2: throw Error(LSMC_EINVAL, "A simulated inventory is outside the storage's allowed inventory range (CmdtyStorage.GetInjectWithdrawRange).");
         case 3: throw Error(LSMC_EINVAL, "Inventory constraints cannot be fulfilled. This could potentially be fixed by increasing the numerical tolerance.");
+        case kPeerTimeout: {
+            unsigned long long have = 0;
+            cudaMemcpy(&have, c->peer.view.counter[c->peer.view.rank], sizeof(have), cudaMemcpyDeviceToHost);
+            throw Error(LSMC_ECUDA, "The exchange between the GPUs timed out: another rank failed, was cancelled or is not running the same valuation (rank " +
+                        std::to_string(c->rank) + " of " + std::to_string(c->world) + ", exchange " + std::to_string(c->peer.epoch) + ", arrivals " +
+                        std::to_string(have) + " of " + std::to_string(c->peer.target) + ").");
+        }
         default: throw Error(LSMC_EINVAL, "Inventory is outside of inventoryGrid bounds.");
     }
+}
+
+// One process per GPU: every rank exports its exchange buffer with cudaIpcGetMemHandle, the handles travel through one
+// ncclAllGather, every rank maps the others' buffers.  All ranks then agree (all-reduce of a flag) on whether the peer path
+// is usable; if any rank could not map a peer, all of them keep the NCCL collectives.
+void map_peers_over_ipc(lsmc_ctx* c) {
+    const int world = c->world, rank = c->rank;
+    c->peer.release();
+    if (world > kMaxPeers) return;
+    if (const char* e = getenv("LSMC_COMM")) { if (std::string(e) == "nccl") return; }   // development: NCCL collectives only
+    cudaStream_t s = c->stream;
+    bool ok = true;
+    try { c->peer.allocate(world); } catch (const Error&) { ok = false; }
+    struct Blob { cudaIpcMemHandle_t h; int ok; int pad[3]; };
+    static_assert(sizeof(Blob) % 16 == 0, "blob size");
+    DevBuf<unsigned char> d_send, d_recv;
+    d_send.alloc(sizeof(Blob)); d_recv.alloc(sizeof(Blob) * world);
+    Blob mine{};
+    if (ok && cudaIpcGetMemHandle(&mine.h, c->peer.buf) != cudaSuccess) { (void)cudaGetLastError(); ok = false; }
+    mine.ok = ok ? 1 : 0;
+    CUDA_CHECK(cudaMemcpyAsync(d_send.p, &mine, sizeof(Blob), cudaMemcpyHostToDevice, s));
+    int rc = g_nccl.AllGather(d_send.p, d_recv.p, sizeof(Blob), /*ncclInt8*/ 0, c->comm, s);
+    if (rc != 0) throw Error(LSMC_ECUDA, "ncclAllGather failed while exchanging the peer-memory handles");
+    std::vector<Blob> all(world);
+    CUDA_CHECK(cudaMemcpyAsync(all.data(), d_recv.p, sizeof(Blob) * world, cudaMemcpyDeviceToHost, s));
+    CUDA_CHECK(cudaStreamSynchronize(s));
+    PeerView v{};
+    v.rank = rank; v.world = world;
+    for (int r = 0; r < world && ok; r++) {
+        if (!all[r].ok) { ok = false; break; }
+        double* base = c->peer.buf;
+        if (r != rank) {
+            void* p = nullptr;
+            if (cudaIpcOpenMemHandle(&p, all[r].h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { (void)cudaGetLastError(); ok = false; break; }
+            c->peer.opened.push_back(p);
+            base = static_cast<double*>(p);
+        }
+        v.slots[r] = base;
+        v.counter[r] = c->peer.counter_of(base, world);
+    }
+    // agreement: the minimum of the ranks' flags
+    DevBuf<double> flag;
+    flag.alloc(1);
+    const double f = ok ? 1.0 : 0.0;
+    CUDA_CHECK(cudaMemcpyAsync(flag.p, &f, sizeof(double), cudaMemcpyHostToDevice, s));
+    rc = g_nccl.AllReduce(flag.p, flag.p, 1, /*ncclFloat64*/ 8, /*ncclMin*/ 3, c->comm, s);
+    if (rc != 0) throw Error(LSMC_ECUDA, "ncclAllReduce failed while agreeing on the peer-memory path");
+    double agreed = 0.0;
+    CUDA_CHECK(cudaMemcpyAsync(&agreed, flag.p, sizeof(double), cudaMemcpyDeviceToHost, s));
+    CUDA_CHECK(cudaStreamSynchronize(s));
+    if (agreed == 1.0) { c->peer.view = v; c->peer.ready = true; }
+    else c->peer.release();
+    if (getenv("LSMC_VERBOSE")) fprintf(stderr, "lsmc_comm_init: rank %d of %d, exchange over %s\n", rank, world, c->peer.ready ? "peer memory (cudaIpc)" : "NCCL collectives");
 }
 
 // The straight-line forward kernel (kernels.cu forward_fast_kernel) covers: no extra decisions, K <= 16, and next-period
@@ -203,6 +374,9 @@ void set_problem(lsmc_ctx* c, const lsmc_problem* problem) {
     const lsmc_problem& pb = pl.problem.pb;
     c->N = pb.n_sims;
     c->Nglobal = pb.n_sims_global > 0 ? pb.n_sims_global : pb.n_sims;
+    if (c->Nglobal != c->N)   // a shard of a larger valuation: antithetic partners 2m, 2m+1 must live on one rank
+        require(pb.sim_offset % 2 == 0 && pb.sim_offset >= 0 && pb.sim_offset + c->N <= c->Nglobal && (c->N % 2 == 0 || pb.sim_offset + c->N == c->Nglobal),
+                LSMC_EINVAL, "a shard must start on an even path and hold an even number of paths (except the last shard)");
     c->MT = pl.K <= 8 ? 1 : (pl.K <= 16 ? 2 : (pl.K <= 32 ? 4 : 8));
     c->ldb = (pl.K + 3) & ~3;
     require(pl.basis.n_nodes <= kMaxNodes && (int)pl.basis.ops.size() <= kMaxOps, LSMC_EUNSUPPORTED, "basis functions need too many product nodes");
@@ -216,6 +390,9 @@ void set_problem(lsmc_ctx* c, const lsmc_problem* problem) {
     c->TP4 = sweep4_tile(pl.max_grid, pl.K, pl.F, (int)pl.basis.ops.size());
     c->sweep4_blocks = c->TP4 ? (int)std::min<int64_t>(c->num_sms, (c->N + c->TP4 - 1) / c->TP4) : 0;
     if (const char* e = getenv("LSMC_SWEEP")) { if (atoi(e) == 3) c->TP4 = c->sweep4_blocks = 0; }   // development: force the general sweep kernel
+    if (const char* e = getenv("LSMC_TAIL")) c->use_tail = atoi(e) != 0;   // development: 0 = reduce -> NCCL all-reduce -> one-CTA solve
+    if (c->world <= 1 && !c->peer.ready) c->peer.self_only();
+    require(8 * c->MT * 8 * ((pl.max_grid + 7) / 8 + c->MT) <= kPeerSlotDoubles, LSMC_EUNSUPPORTED, "normal-equation block larger than the exchange slots");
     c->fwd_fast = forward_fast_ok(pl, pb);
     if (const char* e = getenv("LSMC_FORWARD")) { if (atoi(e) == 0) c->fwd_fast = false; }   // development: force the general forward kernel
     require(forward_smem_bytes(pl.K, pl.basis.n_nodes, pl.max_grid, c->fwd_fast) <= (size_t)227 * 1024 - 4096, LSMC_EUNSUPPORTED,
@@ -276,6 +453,7 @@ void set_problem(lsmc_ctx* c, const lsmc_problem* problem) {
     c->precond.alloc((size_t)pl.S * precond_stride(pl.K));
     c->error_flag.alloc(1);
     CUDA_CHECK(cudaMemsetAsync(c->error_flag.p, 0, sizeof(int), s));
+    c->pin.alloc(kPinScalars + (size_t)(pl.P - 1) * nsum);
     if (c->outputs & 1) for (auto& pbuf : c->panels) pbuf.alloc((size_t)pl.P * Np);
     if (c->outputs & 2) c->decisions.alloc((size_t)(pl.P - 1) * Np);
     c->beta_override_set.assign(pl.P - 1, 0);
@@ -328,6 +506,7 @@ void simulate(lsmc_ctx* c, int set, const lsmc_rng* rng) {
         c->tm.kernel_launches++;
         c->broadcast0(c->precond.p, (size_t)pl.S * precond_stride(pl.K));
     }
+    HOST_TRACE(c, set == 0 ? "simulate 0: launched" : "simulate 1: launched");
     if (set == 1) c->valuation_antithetic = (rng->mode == LSMC_RNG_PHILOX && rng->antithetic) ? 1 : 0;
     CUDA_CHECK(cudaEventRecord(c->event(set == 0 ? 1 : 5), s));
     c->sims_ready[set] = true;
@@ -399,6 +578,12 @@ void backward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
             regressors(p - 1, q.spot_m, q.fac_m);
             if (q.accum_mode == 1) q.precond = c->precond.p + (size_t)(p - 1 - s0) * precond_stride(pl.K);
         }
+        if (g_trace_host) {
+            static thread_local double last = 0.0;
+            const double nowt = std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+            if (nowt - last > 0.05) fprintf(stderr, "[rank %d %.6f] backward: period %d reached after %.3f s\n", c->rank, nowt, p, nowt - last);
+            last = nowt;
+        }
         CUDA_CHECK(cudaEventRecord(c->event(ev_base), s));
         const bool use4 = c->TP4 != 0 && sweep4_covers(q);
         DevBuf<long long> trace_buf;
@@ -421,25 +606,36 @@ void backward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
         c->tm.sweep_bytes += (double)c->N * 8.0 * ((double)q.G + q.Gn + (q.mode == 0 && !is_current ? F + 1 : (q.mode == 1 ? 1 : 0)) + (q.accum_mode == 1 ? F + 1 : 0));
 
         const int n_elem = 8 * c->MT * q.ncols;
-        launch_reduce_partials(c->partial.p, n_parts, n_elem, c->reduced.p, s);
-        c->tm.kernel_launches++;
-        c->allreduce(c->reduced.p, (size_t)n_elem);
-        if (p > 0) {
-            SolveParams sp{};
-            sp.reduced = c->reduced.p; sp.ncols = q.ncols; sp.K = pl.K; sp.G = q.G; sp.NT = (q.G + 7) / 8; sp.ldb = c->ldb;
-            sp.accum_mode = q.accum_mode; sp.n_global = c->Nglobal; sp.pivot_tol = 1e-13;
-            sp.precond = q.accum_mode == 1 ? q.precond : nullptr;
-            sp.beta = c->beta_all.p + (size_t)(p - 1) * c->beta_stride();
-            launch_solve(sp, s);
+        SolveParams sp{};
+        sp.reduced = c->reduced.p; sp.ncols = q.ncols; sp.K = pl.K; sp.G = q.G; sp.NT = (q.G + 7) / 8; sp.ldb = c->ldb;
+        sp.accum_mode = q.accum_mode; sp.n_global = c->Nglobal; sp.pivot_tol = 1e-13;
+        sp.precond = q.accum_mode == 1 ? q.precond : nullptr;
+        sp.beta = p > 0 ? c->beta_all.p + (size_t)(p - 1) * c->beta_stride() : nullptr;
+        if (c->use_tail && c->peer.ready) {
+            // one kernel: reduction of the partials, exchange between the ranks over peer memory, solve spread over the CTAs
+            TailParams tp{};
+            tp.solve = sp; tp.partial = c->partial.p; tp.n_parts = n_parts; tp.n_elem = n_elem;
+            tp.do_solve = p > 0 ? 1 : 0;
+            tp.total_out = c->reduced.p; tp.n_out = 1;   // element 0 at p == 0: sum of the start-inventory values (backward NPV)
+            tp.peers = c->peer.view; tp.error_flag = c->error_flag.p;
+            const int blocks = tail_blocks(n_elem, q.G, c->num_sms);
+            c->peer.next(blocks, &tp.parity, &tp.target);
+            launch_tail(tp, blocks, s);
             c->tm.kernel_launches++;
+        } else {
+            launch_reduce_partials(c->partial.p, n_parts, n_elem, c->reduced.p, s);
+            c->tm.kernel_launches++;
+            c->allreduce(c->reduced.p, (size_t)n_elem);
+            if (p > 0) { launch_solve(sp, s); c->tm.kernel_launches++; }
+        }
+        if (p > 0) {
             if (c->beta_override_set[p - 1])
                 CUDA_CHECK(cudaMemcpyAsync(sp.beta, c->beta_override.data() + (size_t)(p - 1) * c->beta_stride(),
                                            c->beta_stride() * sizeof(double), cudaMemcpyHostToDevice, s));
         } else {
-            double sum = 0.0;
-            CUDA_CHECK(cudaMemcpyAsync(&sum, c->reduced.p, sizeof(double), cudaMemcpyDeviceToHost, s));
+            CUDA_CHECK(cudaMemcpyAsync(c->pin.p, c->reduced.p, sizeof(double), cudaMemcpyDeviceToHost, s));
             CUDA_CHECK(cudaStreamSynchronize(s));
-            c->backward_npv = sum / (double)c->Nglobal;
+            c->backward_npv = c->pin.p[0] / (double)c->Nglobal;
         }
         CUDA_CHECK(cudaGetLastError());
         cur ^= 1;
@@ -447,12 +643,18 @@ void backward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
             progress += back_step;
             if (cb) {
                 CUDA_CHECK(cudaStreamSynchronize(s));
-                if (cb(user, progress) != 0) throw Error(LSMC_ECANCELLED, "The operation was canceled.");
+                if (cb(user, progress) != 0) {
+                    if (c->group) c->group->cancelled.store(1);
+                    throw Error(LSMC_ECANCELLED, "The operation was canceled.");
+                }
             }
+            if (c->group && c->group->cancelled.load()) throw Error(LSMC_ECANCELLED, "The operation was canceled.");
         }
     }
+    HOST_TRACE(c, "backward: all periods launched");
     CUDA_CHECK(cudaEventRecord(c->event(3), s));
-    CUDA_CHECK(cudaStreamSynchronize(s));
+    check_device_error_flag(c);   // synchronises the stream; a timed-out exchange surfaces here
+    HOST_TRACE(c, "backward: done");
     float ms = 0.f;
     c->tm.backward_sweep_kernel_ms = 0.0;
     for (size_t e = 8; e < ev_base; e += 2) { CUDA_CHECK(cudaEventElapsedTime(&ms, c->ev[e], c->ev[e + 1])); c->tm.backward_sweep_kernel_ms += ms; }
@@ -469,6 +671,7 @@ void forward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
     const int P = pl.P, s0 = pl.s0, F = pl.F, K = pl.K, nsum = kFwdSums + K;
     const size_t Np = (size_t)c->Npad;
     cudaStream_t s = c->stream;
+    HOST_TRACE(c, "forward: begin");
     CUDA_CHECK(cudaEventRecord(c->event(6), s));
     launch_fill(c->inventory.p, c->Npad, pb.start_inventory, s);   // LSV.cs:362-364
     CUDA_CHECK(cudaMemsetAsync(c->pv_by_sim.p, 0, Np * sizeof(double), s));
@@ -506,7 +709,9 @@ void forward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
         }
         if (c->outputs & 2) q.o_decision = c->decisions.p + (size_t)p * Np;
     }
+    HOST_TRACE(c, "forward: upload params");
     c->fwd_params.upload(hq, s);
+    HOST_TRACE(c, "forward: launch");
     if (!cb) {   // the whole pass in one launch
         launch_forward(c->fwd_params.p, 0, P - 1, K, pl.basis.n_nodes, pl.max_grid, c->fwd_blocks, c->fwd_fast, s);
         c->tm.kernel_launches++;
@@ -517,13 +722,18 @@ void forward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
             progress += fwd_step;
             CUDA_CHECK(cudaStreamSynchronize(s));
             check_device_error_flag(c);
-            if (cb(user, progress) != 0) throw Error(LSMC_ECANCELLED, "The operation was canceled.");
+            if (cb(user, progress) != 0) {
+                if (c->group) c->group->cancelled.store(1);
+                throw Error(LSMC_ECANCELLED, "The operation was canceled.");
+            }
         }
     }
     CUDA_CHECK(cudaGetLastError());
+    HOST_TRACE(c, "forward: reduce + allreduce");
     launch_reduce_rows(c->fwd_sums.p, P - 1, c->fwd_blocks, nsum, c->fwd_red.p, s);
     c->tm.kernel_launches++;
     c->allreduce(c->fwd_red.p, (size_t)(P - 1) * nsum);
+    HOST_TRACE(c, "forward: final");
     // final period + NPV
     FinalParams fq{};
     fq.N = c->N; fq.pass = 0; fq.must_be_empty = pb.must_be_empty_at_end;
@@ -538,23 +748,26 @@ void forward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
     launch_reduce_rows(c->fin_sums.p, 1, c->fwd_blocks, 3, c->reduced.p, s);
     c->tm.kernel_launches += 2;
     c->allreduce(c->reduced.p, 3);
-    double fin[3];
-    CUDA_CHECK(cudaMemcpyAsync(fin, c->reduced.p, sizeof(fin), cudaMemcpyDeviceToHost, s));
+    double* fin = c->pin.p + 1;
+    CUDA_CHECK(cudaMemcpyAsync(fin, c->reduced.p, 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
     c->h_fwd.resize((size_t)(P - 1) * nsum);
-    CUDA_CHECK(cudaMemcpyAsync(c->h_fwd.data(), c->fwd_red.p, c->h_fwd.size() * sizeof(double), cudaMemcpyDeviceToHost, s));
+    CUDA_CHECK(cudaMemcpyAsync(c->pin.p + kPinScalars, c->fwd_red.p, c->h_fwd.size() * sizeof(double), cudaMemcpyDeviceToHost, s));
     CUDA_CHECK(cudaStreamSynchronize(s));
+    std::memcpy(c->h_fwd.data(), c->pin.p + kPinScalars, c->h_fwd.size() * sizeof(double));
     check_device_error_flag(c);
     c->final_inventory_sum = fin[0]; c->terminal_pv_sum = fin[1];
     c->npv = fin[2] / (double)c->Nglobal;   // LSV.cs:584
     // standard error of the NPV (pair means when the valuation draws are antithetic)
-    const bool paired = c->valuation_antithetic && (c->N % 2 == 0) && (pb.sim_offset % 2 == 0);
+    // pair means only when EVERY path of the valuation has its partner: decided on the global count, so that all ranks of a
+    // sharded valuation agree (shards start on even paths and are even except the last: checked in set_problem)
+    const bool paired = c->valuation_antithetic && (c->Nglobal % 2 == 0) && (c->N % 2 == 0) && (pb.sim_offset % 2 == 0);
     fq.pass = 1; fq.paired = paired ? 1 : 0; fq.mean = c->npv;
     launch_final(fq, c->fwd_blocks, s);
     launch_reduce_rows(c->fin_sums.p, 1, c->fwd_blocks, 3, c->reduced.p, s);
     c->tm.kernel_launches += 2;
     c->allreduce(c->reduced.p, 3);
-    double ss[3];
-    CUDA_CHECK(cudaMemcpyAsync(ss, c->reduced.p, sizeof(ss), cudaMemcpyDeviceToHost, s));
+    double* ss = c->pin.p + 4;
+    CUDA_CHECK(cudaMemcpyAsync(ss, c->reduced.p, 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
     CUDA_CHECK(cudaEventRecord(c->event(7), s));
     CUDA_CHECK(cudaStreamSynchronize(s));
     const double m = (double)(paired ? c->Nglobal / 2 : c->Nglobal);
@@ -670,9 +883,12 @@ void assemble_summary(lsmc_ctx* c, lsmc_results* r) {
     }
 }
 
+// Per-sim outputs: rows of N doubles into the caller's [rows][pitch] buffer at column out_col0 (a rank of a multi-GPU
+// valuation writes its own block of columns; a single context has pitch = N, column 0).
 void copy_panel(lsmc_ctx* c, double* dst, const double* src, size_t rows) {
     if (!dst) return;
-    CUDA_CHECK(cudaMemcpy2D(dst, (size_t)c->N * sizeof(double), src, (size_t)c->Npad * sizeof(double), (size_t)c->N * sizeof(double), rows, cudaMemcpyDeviceToHost));
+    const size_t pitch = c->out_pitch > 0 ? (size_t)c->out_pitch : (size_t)c->N;
+    CUDA_CHECK(cudaMemcpy2D(dst + c->out_col0, pitch * sizeof(double), src, (size_t)c->Npad * sizeof(double), (size_t)c->N * sizeof(double), rows, cudaMemcpyDeviceToHost));
 }
 
 void get_results(lsmc_ctx* c, lsmc_results* r) {
@@ -692,7 +908,8 @@ void get_results(lsmc_ctx* c, lsmc_results* r) {
     }
     if (r->decision_index) {
         require((c->outputs & 2) != 0, LSMC_EINVAL, "decision_index was not requested before lsmc_forward (lsmc_request_outputs)");
-        CUDA_CHECK(cudaMemcpy2D(r->decision_index, (size_t)c->N, c->decisions.p, (size_t)c->Npad, (size_t)c->N, pl.P - 1, cudaMemcpyDeviceToHost));
+        const size_t pitch = c->out_pitch > 0 ? (size_t)c->out_pitch : (size_t)c->N;
+        CUDA_CHECK(cudaMemcpy2D(r->decision_index + c->out_col0, pitch, c->decisions.p, (size_t)c->Npad, (size_t)c->N, pl.P - 1, cudaMemcpyDeviceToHost));
     }
 }
 
@@ -758,7 +975,112 @@ int lsmc_comm_init(lsmc_ctx* ctx, int rank, int world, const void* unique_id128)
         typedef int (*init_fn)(void**, int, NcclId, int);
         int rc = ((init_fn)g_nccl.CommInitRank)(&ctx->comm, world, id, rank);
         if (rc != 0) throw Error(LSMC_ECUDA, std::string("ncclCommInitRank: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "error"));
+        map_peers_over_ipc(ctx);
     });
+}
+
+static int calculate_impl(lsmc_ctx* ctx, const lsmc_problem* problem, const lsmc_rng* regression_rng, const lsmc_rng* valuation_rng,
+                          lsmc_progress_cb progress, void* user, lsmc_results* results, const std::function<bool()>& after_setup);
+
+int lsmc_comm_init_local(lsmc_ctx** ctxs, int n) {
+    if (!ctxs || n < 1 || n > kMaxPeers) return LSMC_EINVAL;
+    for (int r = 0; r < n; r++) if (!ctxs[r]) return LSMC_EINVAL;
+    return guarded(ctxs[0], [&] {
+        auto group = std::make_shared<LocalGroup>();
+        for (int r = 0; r < n; r++) {
+            lsmc_ctx* c = ctxs[r];
+            require(c->comm == nullptr, LSMC_EINVAL, "context already belongs to an NCCL communicator");
+            CUDA_CHECK(cudaSetDevice(c->device));
+            c->rank = r; c->world = n; c->group = n > 1 ? group : nullptr;
+            if (n == 1) { c->peer.self_only(); continue; }
+            c->peer.release();
+            c->peer.allocate(n);
+            for (int o = 0; o < n; o++) {   // direct loads/stores between distinct devices
+                if (ctxs[o]->device == c->device) continue;
+                int can = 0;
+                CUDA_CHECK(cudaDeviceCanAccessPeer(&can, c->device, ctxs[o]->device));
+                require(can != 0, LSMC_ECUDA, "the GPUs of the group cannot access each other's memory");
+                cudaError_t e = cudaDeviceEnablePeerAccess(ctxs[o]->device, 0);
+                if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) CUDA_CHECK(e);
+                (void)cudaGetLastError();
+            }
+        }
+        if (n == 1) return;
+        for (int r = 0; r < n; r++) {
+            lsmc_ctx* c = ctxs[r];
+            PeerView v{};
+            v.rank = r; v.world = n;
+            for (int o = 0; o < n; o++) { v.slots[o] = ctxs[o]->peer.buf; v.counter[o] = ctxs[o]->peer.counter_of(ctxs[o]->peer.buf, n); }
+            c->peer.view = v; c->peer.ready = true;
+        }
+        CUDA_CHECK(cudaSetDevice(ctxs[0]->device));
+    });
+}
+
+// Even split of the global paths over the ranks on pair boundaries (antithetic partners 2m, 2m+1 stay on one rank):
+// the same rule as storage_b200/sharding.py shard_paths.
+static void shard_of(int64_t n_global, int world, int rank, int64_t* offset, int64_t* count) {
+    const int64_t pairs = (n_global + 1) / 2, base = pairs / world, rem = pairs % world;
+    const int64_t first = rank * base + std::min<int64_t>(rank, rem), n_pairs = base + (rank < rem ? 1 : 0);
+    *offset = std::min<int64_t>(2 * first, n_global);
+    *count = std::min<int64_t>(2 * (first + n_pairs), n_global) - *offset;
+}
+
+int lsmc_calculate_multi(lsmc_ctx** ctxs, int n, const lsmc_problem* problem, const lsmc_rng* regression_rng,
+                         const lsmc_rng* valuation_rng, lsmc_progress_cb progress, void* user, lsmc_results* results) {
+    if (!ctxs || n < 1 || n > kMaxPeers || !ctxs[0]) return LSMC_EINVAL;
+    if (n == 1) return lsmc_calculate(ctxs[0], problem, regression_rng, valuation_rng, progress, user, results);
+    lsmc_ctx* c0 = ctxs[0];
+    if (!problem || !regression_rng || !valuation_rng || !results) { c0->err = "null argument"; return LSMC_EINVAL; }
+    for (int r = 0; r < n; r++)
+        if (!ctxs[r] || ctxs[r]->world != n || ctxs[r]->rank != r || !ctxs[r]->peer.ready) { c0->err = "call lsmc_comm_init_local on these contexts first"; return LSMC_EINVAL; }
+    const int64_t Ng = problem->n_sims;
+    if (problem->n_sims_global != 0 && problem->n_sims_global != Ng) { c0->err = "lsmc_calculate_multi takes the whole problem: n_sims_global must be 0"; return LSMC_EINVAL; }
+    if (Ng < 2 * n) { c0->err = "fewer than one pair of paths per GPU"; return LSMC_EINVAL; }
+    const int S = problem->n_periods - (problem->first_period_is_current ? 1 : 0), F = problem->n_factors;
+    if (c0->group) c0->group->cancelled.store(0);
+    std::vector<int> status(n, LSMC_OK);
+    auto run_rank = [&](int r) {
+        lsmc_ctx* c = ctxs[r];
+        int64_t off = 0, cnt = 0;
+        shard_of(Ng, n, r, &off, &cnt);
+        lsmc_problem pb = *problem;
+        pb.n_sims = cnt; pb.n_sims_global = Ng; pb.sim_offset = problem->sim_offset + off;
+        // injected draws / panels: this rank's columns, repacked contiguously
+        std::vector<double> stage[2][3];
+        lsmc_rng rng[2] = {*regression_rng, *valuation_rng};
+        for (int k = 0; k < 2; k++) {
+            auto slice = [&](const double* src, size_t rows, std::vector<double>& dst) -> const double* {
+                if (!src) return nullptr;
+                dst.resize(rows * (size_t)cnt);
+                for (size_t row = 0; row < rows; row++) std::memcpy(dst.data() + row * cnt, src + row * Ng + off, sizeof(double) * cnt);
+                return dst.data();
+            };
+            if (rng[k].mode == LSMC_RNG_NORMALS) rng[k].normals = slice(rng[k].normals, (size_t)S * F, stage[k][0]);
+            if (rng[k].mode == LSMC_RNG_PANELS) { rng[k].spot = slice(rng[k].spot, (size_t)S, stage[k][1]); rng[k].factors = slice(rng[k].factors, (size_t)S * F, stage[k][2]); }
+        }
+        lsmc_results res = *results;
+        if (r != 0) {   // the summary is identical on every rank: rank 0 writes it
+            res.deltas = res.profile = res.trigger_summary = res.trigger_inject = res.trigger_withdraw = nullptr;
+        }
+        c->out_pitch = Ng; c->out_col0 = off;
+        // all ranks finish their set-up (allocations) before any of them starts a kernel that waits for the others
+        auto after_setup = [&]() -> bool { if (c->group) { c->group->barrier(n); return c->group->cancelled.load() == 0; } return true; };
+        status[r] = calculate_impl(c, &pb, &rng[0], &rng[1], r == 0 ? progress : nullptr, user, &res, after_setup);
+        c->out_pitch = 0; c->out_col0 = 0;
+        if (r == 0) { results->npv = res.npv; results->npv_std_error = res.npv_std_error; results->backward_npv = res.backward_npv; }
+        else if (status[r] != LSMC_OK && c->group) c->group->cancelled.store(1);
+    };
+    std::vector<std::thread> workers;
+    for (int r = 1; r < n; r++) workers.emplace_back(run_rank, r);
+    run_rank(0);   // the calling thread is rank 0: progress callbacks arrive on it, as in the reference
+    for (auto& w : workers) w.join();
+    // report the failure that started it, not the cancellations it caused on the other ranks
+    int first = -1;
+    for (int r = 0; r < n; r++) if (status[r] != LSMC_OK && (first < 0 || (status[first] == LSMC_ECANCELLED && status[r] != LSMC_ECANCELLED))) first = r;
+    if (first < 0) return LSMC_OK;
+    if (first != 0) c0->err = "GPU " + std::to_string(first) + " of the group: " + ctxs[first]->err;
+    return status[first];
 }
 
 int lsmc_request_outputs(lsmc_ctx* ctx, uint32_t mask) {
@@ -799,11 +1121,14 @@ int lsmc_get_results(lsmc_ctx* ctx, lsmc_results* results) {
     return guarded(ctx, [&] { get_results(ctx, results); });
 }
 
-int lsmc_calculate(lsmc_ctx* ctx, const lsmc_problem* problem, const lsmc_rng* regression_rng, const lsmc_rng* valuation_rng,
-                   lsmc_progress_cb progress, void* user, lsmc_results* results) {
+// lsmc_calculate, with a hook between the set-up (host plan, every device allocation of the valuation) and the first kernel.
+static int calculate_impl(lsmc_ctx* ctx, const lsmc_problem* problem, const lsmc_rng* regression_rng, const lsmc_rng* valuation_rng,
+                          lsmc_progress_cb progress, void* user, lsmc_results* results, const std::function<bool()>& after_setup) {
     if (!ctx) return LSMC_EINVAL;
-    return guarded(ctx, [&] {
+    bool setup_done = false;
+    int rc = guarded(ctx, [&] {
         require(results != nullptr, LSMC_EINVAL, "results is null");
+        require(regression_rng != nullptr && valuation_rng != nullptr, LSMC_EINVAL, "rng is null");
         uint32_t mask = 0;
         if (results->inventory || results->inject_withdraw || results->consumed || results->loss || results->net_volume || results->pv) mask |= 1;
         if (results->decision_index) mask |= 2;
@@ -813,6 +1138,13 @@ int lsmc_calculate(lsmc_ctx* ctx, const lsmc_problem* problem, const lsmc_rng* r
         auto ms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
         const auto t0 = now();
         set_problem(ctx, problem);
+        // every allocation the passes below would make lazily: no cudaMalloc / cudaFree (device-wide synchronisation) once
+        // the ranks of a group have started to wait for each other on the device
+        ctx->fwd_params.alloc((size_t)(ctx->plan.P - 1));
+        if (regression_rng->mode == LSMC_RNG_NORMALS || valuation_rng->mode == LSMC_RNG_NORMALS)
+            ctx->normals_stage.alloc((size_t)ctx->plan.S * ctx->plan.F * (size_t)ctx->N);
+        setup_done = true;
+        if (after_setup && !after_setup()) throw Error(LSMC_ECANCELLED, "Another GPU of the group failed during set-up.");
         const auto t1 = now();
         simulate(ctx, 0, regression_rng);
         backward(ctx, progress, user);
@@ -822,6 +1154,13 @@ int lsmc_calculate(lsmc_ctx* ctx, const lsmc_problem* problem, const lsmc_rng* r
         get_results(ctx, results);
         if (verbose) fprintf(stderr, "lsmc_calculate: set_problem %.2f ms, simulate+backward+forward %.2f ms, get_results %.2f ms\n", ms(t0, t1), ms(t1, t2), ms(t2, now()));
     });
+    if (rc != LSMC_OK && !setup_done && after_setup) { if (ctx->group) ctx->group->cancelled.store(1); after_setup(); }   // keep the group's barrier count whole
+    return rc;
+}
+
+int lsmc_calculate(lsmc_ctx* ctx, const lsmc_problem* problem, const lsmc_rng* regression_rng, const lsmc_rng* valuation_rng,
+                   lsmc_progress_cb progress, void* user, lsmc_results* results) {
+    return calculate_impl(ctx, problem, regression_rng, valuation_rng, progress, user, results, nullptr);
 }
 
 int lsmc_get_timings(const lsmc_ctx* ctx, lsmc_timings* out) {
@@ -862,6 +1201,7 @@ int lsmc_get_sim_panel(lsmc_ctx* ctx, int set, int factor, double* out) {
         require(ctx->has_problem && (set == 0 || set == 1) && ctx->sims_ready[set] && out, LSMC_EINVAL, "simulation set not available");
         const Plan& pl = ctx->plan;
         require(factor >= -1 && factor < pl.F, LSMC_EINVAL, "bad factor index");
+        require(ctx->out_pitch == 0, LSMC_EINVAL, "lsmc_get_sim_panel is a single-context call");
         CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
         if (factor < 0) { copy_panel(ctx, out, ctx->spot[set].p, pl.S); return; }
         require(ctx->fac_set == set, LSMC_EINVAL, "the factors of this set were overwritten by the other simulation set");

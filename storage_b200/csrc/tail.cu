@@ -1,0 +1,144 @@
+// tail.cu — what follows the sweep of one period, as ONE kernel: the deterministic reduction of the sweep's per-CTA
+// normal-equation partials, the exchange of the reduced block between the ranks over peer memory (peer.h), and the
+// solve of the K x K system for every grid point (solve_device.cuh), spread over the CTAs of the grid.
+//
+// It replaces reduce_partials_kernel -> ncclAllReduce -> solve_kernel (three launches, the last on a single CTA).
+// Phases, for a grid of NC co-resident CTAs of 128 threads (NC <= number of SMs, so the spin below cannot starve):
+//   1  element e of the block is reduced by one warp (lanes stride over the partials, shuffle tree: the same summation
+//      order as reduce_partials_kernel) and stored into slot [parity][rank] of every rank's exchange buffer;
+//   2  arrive at every rank's counter (one system-scope atomic per CTA and rank) and wait until this rank's own counter
+//      shows that every CTA of every rank has arrived — with one rank this is simply the grid barrier between 1 and 3;
+//   3  every CTA factorises the (rank-order summed) Gram matrix redundantly and solves the right-hand sides
+//      blockIdx.x, blockIdx.x + NC, ...  (K <= 16: about a microsecond; no second barrier, no broadcast of the factor).
+#include "peer.h"
+#include "solve_device.cuh"
+
+namespace lsmc {
+
+namespace {
+
+constexpr int kTailThreads = 128;
+
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// One thread per CTA: publish this CTA's slot stores, arrive everywhere, wait for everybody.
+__device__ __forceinline__ void arrive_and_wait(const PeerView& pv, unsigned long long target, int* error_flag) {
+    __syncthreads();   // every thread's slot stores happen-before the fence below
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        for (int r = 0; r < pv.world; r++) atomicAdd_system(pv.counter[r], 1ULL);
+        const unsigned long long* mine = pv.counter[pv.rank];
+        const long long t0 = clock64();
+        // a peer that failed or was cancelled never arrives: give up after ~2 s, and at once in every later exchange
+        while (ld_acquire_sys(mine) < target) {
+            if (*reinterpret_cast<volatile int*>(error_flag) == kPeerTimeout) break;
+            if (clock64() - t0 > 4000000000LL) { atomicExch(error_flag, kPeerTimeout); break; }
+            __nanosleep(64);
+        }
+    }
+    __syncthreads();
+}
+
+// The exchanged block: sum over the ranks' slots, in rank order, bypassing L1 (the lines were written by peers).
+struct SlotRed {
+    const double* __restrict__ base;   // this rank's slots of the current parity: [world][kPeerSlotDoubles]
+    int world, ld;
+    __device__ __forceinline__ double at(int e) const {
+        double s = __ldcg(base + e);
+        for (int r = 1; r < world; r++) s += __ldcg(base + (size_t)r * kPeerSlotDoubles + e);
+        return s;
+    }
+    __device__ __forceinline__ double operator()(int k, int col) const { return at(k * ld + col); }
+};
+
+template <int R>   // rows of the system per lane: 1 (K <= 32) or 2 (K <= 64)
+__global__ void __launch_bounds__(kTailThreads) tail_kernel(const TailParams tp) {
+    extern __shared__ double tsm[];
+    __shared__ int dropped[64];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = kTailThreads / 32;
+    const PeerView& pv = tp.peers;
+    const size_t par_off = (size_t)tp.parity * pv.world * kPeerSlotDoubles;
+    // ---- 1: reduce the partials straight into every rank's slot of this rank.  Eight lanes per element: lane j of the
+    //         group sums partials j, j + 8, ... (eight loads in flight per lane), then a three-step shuffle tree: a fixed
+    //         order, the same on every run and every rank count ----
+    {
+        const int sub = lane & 7, grp = lane >> 3;
+        for (int e0 = (blockIdx.x * wpb + warp) * 4; e0 < tp.n_elem; e0 += gridDim.x * wpb * 4) {
+            const int e = e0 + grp;
+            double s = 0.0;
+            if (e < tp.n_elem) {
+                const double* src = tp.partial + e;
+                int c = sub;
+                for (; c + 56 < tp.n_parts; c += 64) {
+                    double v[8];
+#pragma unroll
+                    for (int u = 0; u < 8; u++) v[u] = src[(size_t)(c + 8 * u) * tp.n_elem];
+#pragma unroll
+                    for (int u = 0; u < 8; u++) s += v[u];
+                }
+                for (; c < tp.n_parts; c += 8) s += src[(size_t)c * tp.n_elem];
+            }
+            s += __shfl_xor_sync(0xffffffffu, s, 1);
+            s += __shfl_xor_sync(0xffffffffu, s, 2);
+            s += __shfl_xor_sync(0xffffffffu, s, 4);
+            if (e < tp.n_elem && sub < pv.world) pv.slots[sub][par_off + (size_t)pv.rank * kPeerSlotDoubles + e] = s;
+        }
+    }
+    // ---- 2: exchange ----
+    arrive_and_wait(pv, tp.target, tp.error_flag);
+    const SlotRed red{pv.slots[pv.rank] + par_off, pv.world, tp.solve.ncols};
+    if (blockIdx.x == 0 && (int)threadIdx.x < tp.n_out) tp.total_out[threadIdx.x] = red.at(threadIdx.x);
+    // ---- 3: solve ----
+    if (tp.do_solve) solve_cta_warps<R>(tp.solve, red, tsm, dropped, blockIdx.x, gridDim.x);
+}
+
+__global__ void __launch_bounds__(256) peer_small_kernel(const PeerSmallParams pp) {
+    const PeerView& pv = pp.peers;
+    const size_t par_off = (size_t)pp.parity * pv.world * kPeerSlotDoubles;
+    const bool bcast = pp.root >= 0;
+    if (!bcast || pv.rank == pp.root)
+        for (int i = threadIdx.x; i < pp.count; i += blockDim.x) {
+            const double v = pp.buf[i];
+            for (int r = 0; r < pv.world; r++) pv.slots[r][par_off + (size_t)pv.rank * kPeerSlotDoubles + i] = v;
+        }
+    arrive_and_wait(pv, pp.target, pp.error_flag);
+    const double* mine = pv.slots[pv.rank] + par_off;
+    for (int i = threadIdx.x; i < pp.count; i += blockDim.x) {
+        double s;
+        if (bcast) s = __ldcg(mine + (size_t)pp.root * kPeerSlotDoubles + i);
+        else {
+            s = __ldcg(mine + i);
+            for (int r = 1; r < pv.world; r++) s += __ldcg(mine + (size_t)r * kPeerSlotDoubles + i);
+        }
+        pp.buf[i] = s;
+    }
+}
+
+}  // namespace
+
+// Enough CTAs to give every right-hand side its own and every warp only a few elements to reduce; never more than the
+// SMs (the CTAs spin on each other: they must all be resident).
+int tail_blocks(int n_elem, int G, int num_sms) {
+    const int want = std::max((G + 3) / 4, (n_elem + 15) / 16);   // four warps per CTA: four right-hand sides, sixteen elements
+    return std::max(1, std::min(want, num_sms));
+}
+
+void launch_tail(const TailParams& tp, int blocks, cudaStream_t stream) {
+    const int K = tp.solve.K;
+    const size_t smem = tp.do_solve ? solve_smem_bytes(K) : 0;
+    if (K <= 32) {
+        if (ensure_dynamic_smem((const void*)tail_kernel<1>, smem) != cudaSuccess) return;
+        tail_kernel<1><<<blocks, kTailThreads, smem, stream>>>(tp);
+    } else {
+        if (ensure_dynamic_smem((const void*)tail_kernel<2>, smem) != cudaSuccess) return;
+        tail_kernel<2><<<blocks, kTailThreads, smem, stream>>>(tp);
+    }
+}
+
+void launch_peer_small(const PeerSmallParams& pp, cudaStream_t stream) { peer_small_kernel<<<1, 256, 0, stream>>>(pp); }
+
+}  // namespace lsmc

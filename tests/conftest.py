@@ -4,6 +4,11 @@ import sys
 
 import pytest
 
+# Two contexts of one group on the SAME GPU (tests/test_gpu_multi.py on a one-GPU box) wait for each other on the device.
+# With CUDA's default lazy module loading the first use of a kernel synchronises the device, which would wait for the other
+# context's spinning exchange kernel: load every kernel at start-up instead.  Must be set before cuInit (below).
+os.environ.setdefault("CUDA_MODULE_LOADING", "EAGER")
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
