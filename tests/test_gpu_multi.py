@@ -1,6 +1,6 @@
 """Multi-GPU parity through the C ABI: a valuation whose paths are sharded over several ranks must give the
 one-GPU result — NPV / deltas / profile to 1e-12 relative (only the summation order of the exchanged sums differs)
-and bit-equal decision indices.
+and the same decisions (no path decides another volume; indices may differ between decisions of equal volume).
 
   * one process, several contexts (lsmc_comm_init_local + lsmc_calculate_multi): the exchange goes through peer memory
     only; two or three contexts on the SAME GPU exercise every line of it on a one-GPU box;
@@ -120,5 +120,5 @@ def test_two_ranks_equal_one_gpu(config, paths, comm, tmp_path):
     assert v["ranks_agree"]
     assert v["npv_rel"] < 1e-12 and v["backward_npv_rel"] < 1e-12
     assert v["delta_rel"] < 1e-12 and v["profile_rel"] < 1e-12
-    assert v["decision_differences"] == 0
+    assert v["material_flips"] == 0 and v["decision_differences"] < 0.01 * v["decisions"]
     assert v["se_rel"] < 1e-9

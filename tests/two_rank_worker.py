@@ -32,13 +32,16 @@ def main():
     gathered = [None] * world
     dist.all_gather_object(gathered, {"npv": res.npv, "se": res.npv_std_error, "backward_npv": res.backward_npv,
                                       "deltas": res.deltas, "profile": res.profile, "offset": shard.offset,
-                                      "decision_index": res.decision_index, "trigger_summary": res.trigger_summary})
+                                      "decision_index": res.decision_index, "inject_withdraw": res.inject_withdraw,
+                                      "trigger_summary": res.trigger_summary})
     ctx.close()
     verdict = {}
     if rank == 0:
         with _native.Context(device) as one:
-            ref = one.calculate(pb_global, Rng.philox(11), Rng.philox(22), decision_index=True)
+            ref = one.calculate(pb_global, Rng.philox(11), Rng.philox(22), panels=("inject_withdraw",), decision_index=True)
         dec = np.concatenate([g["decision_index"] for g in sorted(gathered, key=lambda g: g["offset"])], axis=1)
+        vol = np.concatenate([g["inject_withdraw"] for g in sorted(gathered, key=lambda g: g["offset"])], axis=1)
+        vol_scale = max(float(np.max(np.abs(ref.inject_withdraw))), 1e-300)
 
         def rel(a, b):
             a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
@@ -52,7 +55,10 @@ def main():
             "backward_npv_rel": rel(res.backward_npv, ref.backward_npv),
             "delta_rel": rel(res.deltas, ref.deltas), "profile_rel": rel(res.profile, ref.profile),
             "trigger_rel": rel(res.trigger_summary, ref.trigger_summary),
+            # index differences where two decisions carry the same volume are ties broken by the last bit of the coefficients
+            # (the exchange sums in rank order, one GPU in CTA order); a material flip changes the volume decided
             "decision_differences": int(np.sum(dec != ref.decision_index)), "decisions": int(dec.size),
+            "material_flips": int(np.sum(np.abs(vol - ref.inject_withdraw) > 1e-9 * vol_scale)),
         }
         with open(out_path, "w") as f:
             json.dump(verdict, f)
