@@ -55,6 +55,24 @@ void launch_forward(const ForwardParams* device_params, int p0, int p1, int K, i
 size_t forward_smem_bytes(int K, int n_nodes, int max_grid, bool fast);
 int forward_fast_blocks_per_sm();
 int forward_fast_threads();
+// Streaming forward kernel (forward2.cu): per-period constants addressed by the period index alone.
+constexpr int kFwd2PillarDoubles = 80;   // per period: pillar inventories x[16] (+inf padded), min rates, max rates, slopes of both
+__host__ __device__ constexpr int forward2_beta_pitch(int K) { return (((K + 1) & ~1) / 2) % 2 ? ((K + 1) & ~1) : ((K + 1) & ~1) + 2; }   // even, odd half: conflict-free 128-bit rows
+struct Forward2Args {
+    const ForwardParams* params;   // [P-1]
+    int p0, p1;                    // periods of this launch
+    int F, n_nodes, max_grid, ldb, grid_pitch, n_parts;
+    const BasisDev* basis;
+    const double* beta_all; size_t beta_stride;   // coefficients of period p at beta_all + p * beta_stride, rows of pitch ldb
+    const double* grid_pad;        // [P][grid_pitch] the grid of period p at row p
+    const double* pillars;         // [P-1][kFwd2PillarDoubles]
+    double* warp_sums;             // [P-1][n_parts][kFwdSums + K] one partial row per warp
+};
+cudaError_t launch_forward2(const Forward2Args& a, int K, int blocks, cudaStream_t stream);
+size_t forward2_smem_bytes(int K, int n_nodes, int max_grid);
+int forward2_blocks_per_sm();
+int forward2_threads();
+int forward2_parts(int blocks);
 void launch_reduce_rows(const double* in, int n_rows, int n_blocks, int n_cols, double* out, cudaStream_t stream);
 void launch_final(const FinalParams& q, int blocks, cudaStream_t stream);
 void launch_fill(double* p, int64_t n, double v, cudaStream_t stream);

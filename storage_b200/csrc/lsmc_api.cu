@@ -167,6 +167,8 @@ struct lsmc_ctx {
     int64_t N = 0, Npad = 0, Nglobal = 0;
     int TP = 56, nbuf = 2, MT = 1, ldb = 4, sweep_blocks = 0, fwd_blocks = 0, ncols_max = 0;
     bool fwd_fast = false;   // straight-line forward kernel (forward_fast_ok)
+    bool fwd2 = false;       // its streaming form (forward2.cu): additionally every ratchet table has at most 16 pillars
+    int fwd_parts = 0;       // partial rows of the forward sums per period (CTAs, or warps with forward2)
     int TP4 = 0, sweep4_blocks = 0;   // pipelined sweep (sweep4.cu): tile size (0 = shape not covered) and persistent CTAs
     uint32_t outputs = 0;       // bit0 per-sim panels, bit1 decision index
     bool keep_values = false;
@@ -178,6 +180,7 @@ struct lsmc_ctx {
     DevBuf<double> s_decay, s_chol, s_vol, s_drift, s_fwd, normals_stage;
     DevBuf<BasisDev> basis;
     DevBuf<ForwardParams> fwd_params;   // [P-1] per-period descriptors of the forward pass
+    DevBuf<double> grid_pad, fwd_pillars;   // forward2: [P][grid_pitch] grids, [P-1][kFwd2PillarDoubles] ratchet pillars + slopes
     DevBuf<double> precond;     // [S][precond_stride(K)] regression preconditioners (rank 0's, broadcast)
     DevBuf<int> error_flag;
     DevBuf<double> panels[6];
@@ -397,8 +400,14 @@ void set_problem(lsmc_ctx* c, const lsmc_problem* problem) {
     if (const char* e = getenv("LSMC_FORWARD")) { if (atoi(e) == 0) c->fwd_fast = false; }   // development: force the general forward kernel
     require(forward_smem_bytes(pl.K, pl.basis.n_nodes, pl.max_grid, c->fwd_fast) <= (size_t)227 * 1024 - 4096, LSMC_EUNSUPPORTED,
             "basis functions / inventory grid too large for the forward kernel's shared memory");
-    const int fwd_threads = c->fwd_fast ? forward_fast_threads() : 256;
-    c->fwd_blocks = (int)std::min<int64_t>((int64_t)c->num_sms * (c->fwd_fast ? forward_fast_blocks_per_sm() : (pl.K <= 16 ? 3 : 1)), (c->N + fwd_threads - 1) / fwd_threads);   // all CTAs resident: each walks every period
+    c->fwd2 = c->fwd_fast;
+    for (int cid = 0; cid < pb.n_constraints; cid++) c->fwd2 = c->fwd2 && pb.constraint_count[cid] <= 16;
+    c->fwd2 = c->fwd2 && forward2_smem_bytes(pl.K, pl.basis.n_nodes, pl.max_grid) <= (size_t)75 * 1024;
+    if (const char* e = getenv("LSMC_FORWARD")) { if (atoi(e) == 1) c->fwd2 = false; }   // development: 1 = the previous straight-line kernel
+    const int fwd_threads = c->fwd2 ? forward2_threads() : (c->fwd_fast ? forward_fast_threads() : 256);
+    const int fwd_per_sm = c->fwd2 ? forward2_blocks_per_sm() : (c->fwd_fast ? forward_fast_blocks_per_sm() : (pl.K <= 16 ? 3 : 1));
+    c->fwd_blocks = (int)std::min<int64_t>((int64_t)c->num_sms * fwd_per_sm, (c->N + fwd_threads - 1) / fwd_threads);   // all CTAs resident: each walks every period
+    c->fwd_parts = c->fwd2 ? forward2_parts(c->fwd_blocks) : c->fwd_blocks;
     c->ncols_max = 8 * ((pl.max_grid + 7) / 8 + c->MT);
 
     cudaStream_t s = c->stream;
@@ -422,7 +431,33 @@ void set_problem(lsmc_ctx* c, const lsmc_problem* problem) {
     c->reduced.alloc((size_t)8 * c->MT * c->ncols_max);
     c->inventory.alloc(Np); c->pv_by_sim.alloc(Np);
     const int nsum = kFwdSums + pl.K;
-    c->fwd_sums.alloc((size_t)(pl.P - 1) * c->fwd_blocks * nsum);
+    c->fwd_sums.alloc((size_t)(pl.P - 1) * c->fwd_parts * nsum);
+    if (c->fwd2) {   // per-period constants of the streaming forward kernel, addressed by the period index alone
+        const int gp = (pl.max_grid + 1) & ~1;
+        std::vector<double> hg((size_t)pl.P * gp, 0.0), hp((size_t)(pl.P - 1) * kFwd2PillarDoubles, 0.0);
+        const double inf = std::numeric_limits<double>::infinity();
+        for (int p = 0; p < pl.P; p++) std::copy(pl.grid_of(p), pl.grid_of(p) + pl.grid_size(p), hg.begin() + (size_t)p * gp);
+        for (int p = 0; p < pl.P - 1; p++) {
+            double* x = &hp[(size_t)p * kFwd2PillarDoubles];
+            double *lo = x + 16, *hi = x + 32, *slo = x + 48, *shi = x + 64;
+            const int cid = pb.constraint_id[p], first = pb.constraint_first[cid], n = pb.constraint_count[cid], kind = pb.constraint_kind[cid];
+            const double* px = pb.pillar_inventory + first; const double* plo = pb.pillar_min_rate + first; const double* phi = pb.pillar_max_rate + first;
+            for (int i = 0; i < 16; i++) {
+                // piecewise linear: interior pillars only take part in the segment count (entries from n - 1 on are +inf);
+                // step: every pillar does (entries from n on are +inf)
+                const int last_real = kind == LSMC_CONSTRAINT_PIECEWISE_LINEAR ? n - 1 : n;
+                x[i] = i < last_real ? px[i] : inf;
+                lo[i] = i < n ? plo[i] : 0.0; hi[i] = i < n ? phi[i] : 0.0;
+                if (kind == LSMC_CONSTRAINT_PIECEWISE_LINEAR && i + 1 < n) {   // slopes as LinearSpline forms them (kernels.cu spline_dev)
+                    const double dx = px[i + 1] - px[i];
+                    slo[i] = (plo[i + 1] - plo[i]) / dx; shi[i] = (phi[i + 1] - phi[i]) / dx;
+                }
+            }
+            if (kind == LSMC_CONSTRAINT_CONSTANT) x[0] = 0.0;
+        }
+        c->grid_pad.upload(hg, s); c->fwd_pillars.upload(hp, s);
+        CUDA_CHECK(cudaStreamSynchronize(s));   // hg, hp go out of scope
+    }
     c->fwd_red.alloc((size_t)(pl.P - 1) * nsum);
     c->fin_sums.alloc((size_t)c->fwd_blocks * 3);
     c->t_ndec.upload(pl.tables.n_dec, s); c->t_invcost.upload(pl.tables.inv_cost_npv, s);
@@ -701,7 +736,7 @@ void forward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
         q.next_grid = c->grid.p + pl.grid_offset[p + 1];
         q.basis = c->basis.p;
         q.inventory = c->inventory.p; q.pv_by_sim = c->pv_by_sim.p;
-        q.sums = c->fwd_sums.p + (size_t)p * c->fwd_blocks * nsum;
+        q.sums = c->fwd_sums.p + (size_t)p * c->fwd_parts * nsum;
         q.error_flag = c->error_flag.p;
         if (panels) {
             q.o_inventory = c->panels[0].p + (size_t)p * Np; q.o_volume = c->panels[1].p + (size_t)p * Np; q.o_consumed = c->panels[2].p + (size_t)p * Np;
@@ -712,13 +747,21 @@ void forward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
     HOST_TRACE(c, "forward: upload params");
     c->fwd_params.upload(hq, s);
     HOST_TRACE(c, "forward: launch");
-    if (!cb) {   // the whole pass in one launch
-        launch_forward(c->fwd_params.p, 0, P - 1, K, pl.basis.n_nodes, pl.max_grid, c->fwd_blocks, c->fwd_fast, s);
+    Forward2Args fa{};
+    fa.params = c->fwd_params.p; fa.F = F; fa.n_nodes = pl.basis.n_nodes; fa.max_grid = pl.max_grid; fa.ldb = c->ldb;
+    fa.grid_pitch = (pl.max_grid + 1) & ~1; fa.n_parts = c->fwd_parts; fa.basis = c->basis.p;
+    fa.beta_all = c->beta_all.p; fa.beta_stride = c->beta_stride(); fa.grid_pad = c->grid_pad.p; fa.pillars = c->fwd_pillars.p;
+    fa.warp_sums = c->fwd_sums.p;
+    auto launch_periods = [&](int p0, int p1) {
+        if (c->fwd2) { fa.p0 = p0; fa.p1 = p1; CUDA_CHECK(launch_forward2(fa, K, c->fwd_blocks, s)); }
+        else launch_forward(c->fwd_params.p, p0, p1, K, pl.basis.n_nodes, pl.max_grid, c->fwd_blocks, c->fwd_fast, s);
         c->tm.kernel_launches++;
+    };
+    if (!cb) {   // the whole pass in one launch
+        launch_periods(0, P - 1);
     } else {     // one launch per period so that progress / cancellation keep the reference's cadence (LSV.cs:488-490)
         for (int p = 0; p < P - 1; p++) {
-            launch_forward(c->fwd_params.p, p, p + 1, K, pl.basis.n_nodes, pl.max_grid, c->fwd_blocks, c->fwd_fast, s);
-            c->tm.kernel_launches++;
+            launch_periods(p, p + 1);
             progress += fwd_step;
             CUDA_CHECK(cudaStreamSynchronize(s));
             check_device_error_flag(c);
@@ -730,7 +773,7 @@ void forward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
     }
     CUDA_CHECK(cudaGetLastError());
     HOST_TRACE(c, "forward: reduce + allreduce");
-    launch_reduce_rows(c->fwd_sums.p, P - 1, c->fwd_blocks, nsum, c->fwd_red.p, s);
+    launch_reduce_rows(c->fwd_sums.p, P - 1, c->fwd_parts, nsum, c->fwd_red.p, s);
     c->tm.kernel_launches++;
     c->allreduce(c->fwd_red.p, (size_t)(P - 1) * nsum);
     HOST_TRACE(c, "forward: final");

@@ -294,22 +294,27 @@ def test_full_size_properties_c3(ctx):
     assert again.npv == res.npv and np.array_equal(again.deltas, res.deltas)      # deterministic reductions
 
 
-@pytest.mark.parametrize("config,paths", [("c3", 150_000), ("c2", 100_000), ("c5", 20_000), ("c1", 50_000)])
-def test_forward_straight_line_kernel_equals_the_bisecting_kernel(config, paths, monkeypatch):
-    """forward_fast_kernel's O(1) grid lookup (class table replaying SH.cs:280-314) against forward_kernel's bisection on
-    every path of a large run: decisions, inventories and PVs must be bit-identical."""
+@pytest.mark.parametrize("config,paths", [("c3", 150_000), ("c2", 100_000), ("c5", 20_000), ("c1", 50_000), ("c3", 1001)])
+def test_forward_streaming_and_straight_line_kernels_equal_the_bisecting_kernel(config, paths, monkeypatch):
+    """forward2_kernel (streamed per-period constants, O(1) grid lookup from the class table that replays SH.cs:280-314) and
+    its predecessor forward_fast_kernel against forward_kernel's bisection on every path of a large run: decisions,
+    inventories and PVs must be bit-identical."""
     pb = build_config(config, num_sims=paths)
     out = {}
-    for mode in ("1", "0"):   # LSMC_FORWARD=0 forces the general kernel (read in lsmc_set_problem)
+    for mode in ("2", "1", "0"):   # LSMC_FORWARD (read in lsmc_set_problem): 2 streaming, 1 straight-line, 0 bisecting kernel
         monkeypatch.setenv("LSMC_FORWARD", mode)
         with _native.Context(0) as c:
             out[mode] = c.calculate(pb, Rng.philox(11), Rng.philox(22), panels=("inventory", "inject_withdraw", "pv"), decision_index=True)
-    fast, slow = out["1"], out["0"]
-    assert np.array_equal(fast.decision_index, slow.decision_index)
-    assert np.array_equal(fast.inventory, slow.inventory)
-    assert np.array_equal(fast.inject_withdraw, slow.inject_withdraw)
-    assert np.array_equal(fast.pv, slow.pv)
-    assert rel_err(fast.npv, slow.npv) < 1e-13   # block partition of the sums differs
+    slow = out["0"]
+    for mode in ("2", "1"):
+        fast = out[mode]
+        assert np.array_equal(fast.decision_index, slow.decision_index), mode
+        assert np.array_equal(fast.inventory, slow.inventory), mode
+        assert np.array_equal(fast.inject_withdraw, slow.inject_withdraw), mode
+        assert np.array_equal(fast.pv, slow.pv), mode
+        assert rel_err(fast.npv, slow.npv) < 1e-13   # partition of the sums differs
+        assert rel_err(fast.deltas, slow.deltas) < 1e-12 and rel_err(fast.profile, slow.profile) < 1e-12
+        assert rel_err(fast.trigger_summary, slow.trigger_summary) < 1e-9
 
 
 def test_discounted_deltas_identity(ctx):   # LSMCTest:846-869
