@@ -220,6 +220,13 @@ int lsmc_forward(lsmc_ctx* ctx, lsmc_progress_cb progress, void* progress_user);
 int lsmc_get_results(lsmc_ctx* ctx, lsmc_results* results);             /* D2H of whatever is non-NULL */
 int lsmc_get_timings(const lsmc_ctx* ctx, lsmc_timings* out);
 
+/* Intrinsic valuation on the forward curve, the deterministic model the reference's Python entry points run beside the
+ * LSMC (multi_factor.py:406 -> IntrinsicStorageValuation.cs:120-322): backward induction over the same inventory grids with
+ * linear interpolation of the value function, then the optimal schedule from the start inventory.  Host only (O(P * G));
+ * needs no context and no GPU.  profile: [P][6] StorageProfile rows (inventory AFTER the period's decision) or NULL.
+ * Only the storage / curve fields of the problem are read (n_sims >= 1, any basis / factor model).  Errors: lsmc_last_error(NULL). */
+int lsmc_intrinsic(const lsmc_problem* problem, double* npv, double* profile /*[P][6] or NULL*/);
+
 /* Introspection used by hosts that want RegressionCoefficients / InventoryGrids (commented out in
  * LsmcStorageValuationResults.cs:51-52) and by the parity tests. */
 int lsmc_get_grid(const lsmc_ctx* ctx, int period, double* out /*[max_grid]*/, int32_t* count);

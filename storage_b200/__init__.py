@@ -10,8 +10,14 @@ __version__ = "0.1.0"
 
 def __getattr__(name):
     # multi_factor needs the native library only when a valuation is actually run; import lazily
-    if name in ("multi_factor_value", "three_factor_seasonal_value", "MultiFactorModel", "MultiFactorSpotSim",
+    if name in ("multi_factor_value", "three_factor_seasonal_value", "MultiFactorSpotSim",
                 "MultiFactorValuationResults", "create_3_factor_season_params"):
         from . import multi_factor
         return getattr(multi_factor, name)
+    if name == "MultiFactorModel":
+        from .multi_factor_model import MultiFactorModel
+        return MultiFactorModel
+    if name in ("intrinsic_value", "IntrinsicValuationResults"):
+        from . import intrinsic
+        return getattr(intrinsic, name)
     raise AttributeError(name)

@@ -14,7 +14,7 @@ LIB_PATH = os.environ.get("LSMC_B200_LIB") or os.path.join(_HERE, "liblsmc_b200.
 
 EXPORTS = (
     "lsmc_version", "lsmc_create", "lsmc_destroy", "lsmc_last_error", "lsmc_comm_unique_id", "lsmc_comm_init", "lsmc_comm_init_local",
-    "lsmc_calculate_multi",
+    "lsmc_calculate_multi", "lsmc_intrinsic",
     "lsmc_calculate", "lsmc_set_problem", "lsmc_get_layout", "lsmc_request_outputs", "lsmc_simulate", "lsmc_backward",
     "lsmc_forward", "lsmc_get_results", "lsmc_get_timings", "lsmc_get_grid", "lsmc_get_inventory_space",
     "lsmc_get_regression_coeffs", "lsmc_get_sim_panel", "lsmc_debug_set_regression_coeffs", "lsmc_debug_keep_values",
@@ -186,6 +186,17 @@ class Context:
         out = np.zeros((g, self.layout().n_sims))
         self._check(lib().lsmc_debug_get_values(self._h, C.c_int(period), out.ctypes.data_as(_dp)))
         return out
+
+
+def intrinsic(problem):
+    """lsmc_intrinsic: (npv, profile[P][6]) of the deterministic valuation on the forward curve (host only)."""
+    cp = problem.c_struct()
+    npv = C.c_double()
+    profile = np.zeros((int(problem.n_periods), 6))
+    rc = lib().lsmc_intrinsic(C.byref(cp), C.byref(npv), profile.ctypes.data_as(_dp))
+    if rc != 0:
+        raise LsmcError(rc, lib().lsmc_last_error(None).decode())
+    return npv.value, profile
 
 
 class Group:

@@ -444,4 +444,92 @@ void build_plan(const lsmc_problem& problem, Plan& plan) {
     compile_basis(pb, plan.basis);
 }
 
+// ------------------------------------------------------------------------------------------------
+// Intrinsic valuation (IntrinsicStorageValuation.cs:120-322)
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+// MathNet LinearSpline.Interpolate(x, y).Interpolate(t) as LinearInterpolatorFactory.cs:44-50 uses it: the segment left of t
+// (clamped to the first / last segment: linear extrapolation), value y_k + (t - x_k) * slope_k; one point: a constant.
+struct LinearInterp {
+    const double* x = nullptr;
+    std::vector<double> y;
+    int n = 0;
+    double operator()(double t) const {
+        if (n == 1) return y[0];
+        int k = (int)(std::upper_bound(x, x + n, t) - x) - 1;
+        k = std::min(std::max(k, 0), n - 2);
+        const double slope = (y[k + 1] - y[k]) / (x[k + 1] - x[k]);
+        return y[k] + (t - x[k]) * slope;
+    }
+};
+
+struct IntrinsicDecision { double npv, volume, consumed, loss, period_pv; };
+
+// OptimalDecisionAndValue + StorageValueForDecision (IntrinsicStorageValuation.cs:262-320).
+template <typename Continuation>
+IntrinsicDecision optimal_decision(const lsmc_problem& pb, int p, double inventory, double next_min, double next_max,
+                                   double price, const Continuation& continuation) {
+    double rmin, rmax;
+    inject_withdraw_range(pb, p, inventory, rmin, rmax);
+    const double loss = pb.inventory_loss[p] * inventory;
+    double ds[3];
+    const int nd = bang_bang_decisions(rmin, rmax, inventory, loss, next_min, next_max, pb.numerical_tolerance, 0, ds);
+    const double df = pb.settle_df[p];
+    IntrinsicDecision best{};
+    for (int j = 0; j < nd; j++) {
+        const double d = ds[j];
+        const double after = inventory + d - loss;
+        const double cont = continuation(after);
+        const double inject_withdraw_npv = -d * price * df;
+        const double inventory_cost_npv = pb.inventory_cost[p] == 0.0 ? 0.0 : (inventory * pb.inventory_cost[p]) * pb.inventory_cost_df[p];
+        const double cost_npv = decision_cost_npv(pb, p, d);
+        const double consumed = d > 0.0 ? pb.consumed_inject[p] * std::fabs(d) : pb.consumed_withdraw[p] * std::fabs(d);
+        const double consumed_npv = -consumed * price * df;
+        const double period_pv = inject_withdraw_npv - cost_npv + consumed_npv - inventory_cost_npv;
+        const double npv = cont + period_pv;
+        if (j == 0 || npv > best.npv) best = IntrinsicDecision{npv, d, consumed, loss, period_pv};   // first strictly greatest (SH.cs:206-222)
+    }
+    return best;
+}
+
+}  // namespace
+
+double intrinsic_value(const Plan& plan, double* profile) {
+    const lsmc_problem& pb = plan.problem.pb;
+    const int P = plan.P;
+    auto terminal = [&](double price, double inv) {
+        if (pb.must_be_empty_at_end) return 0.0;
+        return pb.terminal_coef[0] + pb.terminal_coef[1] * price + pb.terminal_coef[2] * inv + pb.terminal_coef[3] * (price * inv);
+    };
+    const double price_end = pb.forward[P - 1];
+    // value function of period p (p = 1 .. P-2) on its grid; period P-1 is the terminal value itself
+    std::vector<LinearInterp> value(P);
+    auto continuation_of = [&](int p_next) {
+        return [&, p_next](double inv) { return p_next == P - 1 ? terminal(price_end, inv) : value[p_next](inv); };
+    };
+    for (int p = P - 2; p >= 1; p--) {
+        LinearInterp& v = value[p];
+        v.x = plan.grid_of(p); v.n = plan.grid_size(p); v.y.resize(v.n);
+        const auto cont = continuation_of(p + 1);
+        for (int i = 0; i < v.n; i++)
+            v.y[i] = optimal_decision(pb, p, v.x[i], plan.space_min[p + 1], plan.space_max[p + 1], pb.forward[p], cont).npv;
+    }
+    double inventory = pb.start_inventory, npv = 0.0;
+    for (int p = 0; p < P; p++) {
+        double* row = profile ? profile + (size_t)p * 6 : nullptr;
+        if (p == P - 1) {
+            const double end_npv = terminal(pb.forward[p], inventory);
+            if (row) { row[0] = inventory; row[1] = row[2] = row[3] = row[4] = 0.0; row[5] = end_npv; }
+            npv += end_npv;
+        } else {
+            const IntrinsicDecision d = optimal_decision(pb, p, inventory, plan.space_min[p + 1], plan.space_max[p + 1], pb.forward[p], continuation_of(p + 1));
+            inventory += d.volume - d.loss;
+            if (row) { row[0] = inventory; row[1] = d.volume; row[2] = d.consumed; row[3] = d.loss; row[4] = -d.volume - d.consumed; row[5] = d.period_pv; }
+            npv += d.period_pv;
+        }
+    }
+    return npv;
+}
+
 }  // namespace lsmc

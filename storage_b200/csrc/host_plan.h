@@ -81,6 +81,12 @@ inline double range_slack(double tol, double bound) {
 
 void build_plan(const lsmc_problem& problem, Plan& plan);
 
+// Intrinsic valuation on the forward curve (IntrinsicStorageValuation.cs:120-322): deterministic backward induction over the
+// plan's inventory grids with linear interpolation of the value function (LinearInterpolatorFactory.cs:37-51), then the
+// optimal decisions forward from the start inventory.  profile: [P][6] as StorageProfile (inventory AFTER the period's
+// decision, :283-286).  Host only: O(P * G * 3).
+double intrinsic_value(const Plan& plan, double* profile);
+
 // Storage queries at arbitrary inventory, used by the trigger-price post-processing (LSV.cs:494-497).
 void inject_withdraw_range(const lsmc_problem& pb, int period, double inventory, double& rmin, double& rmax);
 int bang_bang_decisions(double rmin, double rmax, double inventory, double loss, double next_min, double next_max,

@@ -1206,6 +1206,15 @@ int lsmc_calculate(lsmc_ctx* ctx, const lsmc_problem* problem, const lsmc_rng* r
     return calculate_impl(ctx, problem, regression_rng, valuation_rng, progress, user, results, nullptr);
 }
 
+int lsmc_intrinsic(const lsmc_problem* problem, double* npv, double* profile) {
+    return guarded(nullptr, [&] {
+        require(problem != nullptr && npv != nullptr, LSMC_EINVAL, "problem or npv is null");
+        Plan plan;
+        build_plan(*problem, plan);
+        *npv = intrinsic_value(plan, profile);
+    });
+}
+
 int lsmc_get_timings(const lsmc_ctx* ctx, lsmc_timings* out) {
     if (!ctx || !out) return LSMC_EINVAL;
     *out = ctx->tm;

@@ -5,8 +5,8 @@ the valuation on a B200 through the C ABI (include/lsmc_b200.h) instead of pytho
 What differs from the reference, by necessity:
   * random numbers: device Philox4x32-10 (antithetic, like the reference's MersenneTwisterGenerator(seed, true),
     LVP.cs:185-189) instead of MT19937 — seeded results agree with the reference to Monte-Carlo error, not bit-wise;
-  * `intrinsic_npv` / `intrinsic_profile` come from the reference's separate CPU intrinsic model
-    (multi_factor.py:406), which is outside the LSMC hot path: they are NaN / None here;
+  * `intrinsic_npv` / `intrinsic_profile` come from the library's host routine lsmc_intrinsic (storage_b200/intrinsic.py),
+    the reference's IntrinsicStorageValuation restated (pinned by the reference's golden value 1703773.0757192627);
   * there is no CPU fallback: without liblsmc_b200.so or a B200 the call raises.
 """
 import logging
@@ -20,6 +20,7 @@ import pandas as pd
 from . import _abi, _native, utils
 from .cmdty_storage import CmdtyStorage
 from .flatten import flatten_problem, TrivialResult
+from .intrinsic import intrinsic_of_problem
 from .multi_factor_params import create_3_factor_season_params
 
 logger: logging.Logger = logging.getLogger('cmdty.storage.multi-factor')
@@ -179,12 +180,17 @@ def _lsmc_calc(cmdty_storage, fwd_curve, interest_rates, inventory, factors, fac
         profile = pd.DataFrame(index=empty_index, columns=_PROFILE_COLUMNS, dtype=np.float64)
         if on_progress_update is not None:
             on_progress_update(1.0)
-        return MultiFactorValuationResults(problem.npv, pd.Series(index=empty_index, dtype=np.float64), profile, float('nan'), None,
+        intrinsic = intrinsic_of_problem(problem)
+        return MultiFactorValuationResults(problem.npv, pd.Series(index=empty_index, dtype=np.float64), profile, intrinsic.npv,
+                                           intrinsic.profile,
                                            empty, empty, empty, empty, empty, empty, empty, empty,
                                            pd.DataFrame(index=empty_index, columns=_TRIGGER_COLUMNS, dtype=np.float64),
                                            pd.Series(index=empty_index, dtype=object))
     periods = problem.periods
     P, S, N = problem.n_periods, problem.n_sim_periods, int(problem.n_sims)
+    logger.info('Calculating intrinsic value.')
+    intrinsic = intrinsic_of_problem(problem)
+    logger.info('Calculation of intrinsic value complete.')
     reg_seed, val_seed = _seeds(seed, fwd_sim_seed)
     panels = "all" if RETURN_SIM_PANELS else ()
     logger.info('Calculating LSMC value.')
@@ -213,7 +219,7 @@ def _lsmc_calc(cmdty_storage, fwd_curve, interest_rates, inventory, factors, fac
     def frame(a, index):
         return pd.DataFrame(a, index=index) if a is not None else pd.DataFrame(index=index)
 
-    return MultiFactorValuationResults(res.npv, deltas, expected_profile, float('nan'), None,
+    return MultiFactorValuationResults(res.npv, deltas, expected_profile, intrinsic.npv, intrinsic.profile,
                                        frame(res.spot_regress, sim_periods), frame(res.spot_valuation, sim_periods),
                                        frame(res.inventory, periods), frame(res.inject_withdraw, periods),
                                        frame(res.consumed, periods), frame(res.loss, periods), frame(res.net_volume, periods),

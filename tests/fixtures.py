@@ -128,3 +128,69 @@ def three_calls_problem(num_sims=2_000):
         expected += df(settle[str(d.asfreq("M"))]) * (f * norm_cdf(d1) - k * norm_cdf(d1 - vrt)) * n
         deltas[int(np.where(periods == d)[0][0])] = norm_cdf(d1) * n
     return pb, expected, deltas
+
+
+def forced_inject_withdraw_problem(num_sims=1_000):
+    """Calculate_StorageWithForcedInjectAndWithdraw_NpvAlmostEqualsTrivialIntrinsicCalc (LSMCTest:686-837), built directly as
+    a flattened Problem.  The reference builds the storage with ...RatesPolynomial, but every one of its five tables has
+    two rows with equal rates, which AddInjectWithdrawRanges collapses to ConstantInjectWithdrawConstraint
+    (CmdtyStorageBuilderExtensions.cs:163-171): no polynomial is ever fitted.  Injection costs settle 10 days after the
+    injection, withdrawal costs 4 days after (per-period cost discount factors of the C-ABI).
+    Returns (problem, expected NPV of the forced schedule valued on the forward curve)."""
+    val = pd.Period("2019-08-29", freq="D")
+    start, end = pd.Period("2019-12-01", freq="D"), pd.Period("2020-04-01", freq="D")
+    max_inventory = 10_000.0
+    inj_rate, inj_days, inj_start = 211.5, 20, pd.Period("2019-12-20", freq="D")
+    wd_rate, wd_days, wd_start = 187.54, 15, pd.Period("2020-02-05", freq="D")
+    inj_cost, inj_consumed, wd_cost, wd_consumed = 1.23, 0.01, 0.98, 0.015
+    mean_reversion, rate = 16.5, 0.09
+    curve_idx = pd.period_range(val, end, freq="D")
+    i = np.arange(len(curve_idx), dtype=np.float64)
+    fwd_curve = pd.Series(53.5 + np.sin(2.0 * math.pi / 365.0 * i) * 24.6, index=curve_idx)     # TestHelper.cs:86-107
+    vol_curve = pd.Series(0.78 + np.sin(2.0 * math.pi / 365.0 * i) * 0.35, index=curve_idx)
+    settle = {"2019-12": pd.Period("2020-01-20", freq="D"), "2020-01": pd.Period("2020-02-18", freq="D"),
+              "2020-02": pd.Period("2020-03-21", freq="D"), "2020-03": pd.Period("2020-04-22", freq="D")}
+    periods = pd.period_range(start, end, freq="D")
+    P = len(periods)
+
+    def df(day):
+        return 1.0 if day <= val else math.exp(-(day.ordinal - val.ordinal) / 365.0 * rate)
+
+    def forced(per):
+        if inj_start <= per < inj_start + inj_days:
+            return inj_rate
+        if wd_start <= per < wd_start + wd_days:
+            return -wd_rate
+        return 0.0
+
+    rates = [0.0, inj_rate, -wd_rate]
+    cid = np.array([rates.index(forced(per)) for per in periods], dtype=np.int32)
+    settle_df, inj_df, wd_df = np.ones(P), np.ones(P), np.ones(P)
+    for p, per in enumerate(periods[:-1]):
+        settle_df[p] = df(settle[str(per.asfreq("M"))])
+        inj_df[p], wd_df[p] = df(per + 10), df(per + 4)
+    zeros = np.zeros(P)
+    K_spot, K_fac = np.zeros(3, dtype=np.int32), np.array([[0], [1], [2]], dtype=np.int32)
+    pb = Problem(
+        n_periods=P, n_factors=1, n_basis=3, n_sims=num_sims, extra_decisions=0, first_period_is_current=0,
+        discount_deltas=0, must_be_empty_at_end=0, numerical_tolerance=1e-10, start_inventory=0.0,
+        grid_spacing=max_inventory / 499.0, terminal_coef=(0.0, 0.0, 0.0, 0.0),
+        sim_time=np.array([(per.ordinal - val.ordinal) / 365.0 for per in periods]), mean_reversion=np.array([mean_reversion]),
+        factor_vol=vol_curve[periods].values.reshape(P, 1), factor_corr=np.array([[1.0]]), forward=fwd_curve[periods].values,
+        spot_power=K_spot, factor_power=K_fac,
+        min_inventory=zeros.copy(), max_inventory=np.full(P, max_inventory), constraint_id=cid,
+        inject_cost=np.full(P, inj_cost), inject_cost_df=inj_df, withdraw_cost=np.full(P, wd_cost), withdraw_cost_df=wd_df,
+        consumed_inject=np.full(P, inj_consumed), consumed_withdraw=np.full(P, wd_consumed), inventory_loss=zeros.copy(),
+        inventory_cost=zeros.copy(), inventory_cost_df=np.ones(P), settle_df=settle_df,
+        constraint_kind=np.full(3, CONSTRAINT_CONSTANT, dtype=np.int32), constraint_first=np.arange(3, dtype=np.int32),
+        constraint_count=np.ones(3, dtype=np.int32), pillar_inventory=np.zeros(3), pillar_min_rate=np.array(rates),
+        pillar_max_rate=np.array(rates), periods=periods,
+    ).finalize()
+    expected = 0.0
+    for k in range(inj_days):
+        day = inj_start + k
+        expected += -fwd_curve[day] * inj_rate * (1 + inj_consumed) * df(settle[str(day.asfreq("M"))]) - inj_cost * inj_rate * df(day + 10)
+    for k in range(wd_days):
+        day = wd_start + k
+        expected += fwd_curve[day] * wd_rate * (1 - wd_consumed) * df(settle[str(day.asfreq("M"))]) - wd_cost * wd_rate * df(day + 4)
+    return pb, expected

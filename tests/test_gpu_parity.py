@@ -17,8 +17,8 @@ from storage_b200 import CmdtyStorage, RatchetInterp, _abi, _native
 from storage_b200._abi import Rng
 from storage_b200.configs import build_config, full_polynomial_basis
 from oracle import oracle
-from fixtures import (reference_problem, simple_daily_storage, ratchet_daily_storage, three_calls_problem, STORAGE_START,
-                      STORAGE_END)
+from fixtures import (reference_problem, simple_daily_storage, ratchet_daily_storage, three_calls_problem,
+                      forced_inject_withdraw_problem, STORAGE_START, STORAGE_END)
 
 pytestmark = pytest.mark.gpu
 REL = 1e-9   # north_star tolerance with injected normals
@@ -109,6 +109,7 @@ CASES = {
     "before_storage_start": lambda: reference_problem(val_date="2019-07-20", inventory=0.0, num_sims=512),
     "extra_decisions": lambda: reference_problem(num_sims=512, extra_decisions=2),
     "three_calls": lambda: three_calls_problem(num_sims=1024)[0],
+    "forced_inject_withdraw": lambda: forced_inject_withdraw_problem(num_sims=1000)[0],   # LSMCTest:686-837: one-point grids
 }
 
 

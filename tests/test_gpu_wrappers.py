@@ -1,0 +1,104 @@
+"""The reference's Python entry points for the LSMC path, reproduced by storage_b200 with the same names and arguments
+(multi_factor_value, three_factor_seasonal_value, MultiFactorSpotSim; src/Cmdty.Storage.Python/cmdty_storage/
+multi_factor.py:49-92,324-455), run on the GPU and held to the reference's own wrapper tests
+(src/Cmdty.Storage.Python/tests/test_multi_factor.py:167-311): result shapes, 123 deltas, 245 progress calls, the golden
+intrinsic NPV, and the seeded LSMC NPVs 1780380.76 / 1766460.14 as Monte-Carlo bands (they are functions of MathNet's
+MT19937 stream, which is not reproduced: DESIGN.md 3).  The same valuation through the CPU oracle must agree to 1e-9."""
+import numpy as np
+import pandas as pd
+import pytest
+
+import storage_b200
+from storage_b200 import CmdtyStorage, multi_factor
+from storage_b200._abi import Rng
+from storage_b200.flatten import flatten_problem
+from oracle import oracle
+from test_intrinsic import wrapper_test_inputs, twentieth_of_next_month
+
+pytestmark = pytest.mark.gpu
+VAL_DATE, NUM_SIMS, SEED = '2019-08-29', 500, 11
+
+
+def check_result_structure(res, progresses):
+    assert len(res.deltas) == 123 and len(res.expected_profile) == 123            # test_multi_factor.py:227-228
+    assert progresses[-1] == 1.0 and len(progresses) == 245                       # :229-230
+    assert all(b > a for a, b in zip(progresses, progresses[1:]))
+    assert res.intrinsic_npv == 1703773.0757192627 and len(res.intrinsic_profile) == 123   # :231-232
+    assert res.extrinsic_npv == res.npv - res.intrinsic_npv and res.extrinsic_npv > 0.0
+    for frame in (res.sim_spot_regress, res.sim_spot_valuation, res.sim_inventory, res.sim_inject_withdraw, res.sim_cmdty_consumed,
+                  res.sim_inventory_loss, res.sim_net_volume, res.sim_pv):
+        assert frame.shape == (123, NUM_SIMS)                                     # :233-239
+    assert list(res.expected_profile.columns) == ['inventory', 'inject_withdraw_volume', 'cmdty_consumed', 'inventory_loss', 'net_volume', 'period_pv']
+    assert list(res.trigger_prices.columns) == ['inject_volume', 'inject_trigger_price', 'withdraw_volume', 'withdraw_trigger_price']
+    assert len(res.trigger_prices) == 122 and len(res.trigger_profiles) == 122
+    assert res.deltas.index[0] == pd.Period('2019-12-01', freq='D') and res.deltas.iloc[-1] == 0.0
+    assert res.sim_pv.sum(axis=0).mean() == pytest.approx(res.npv, rel=1e-12)     # NPV = mean over sims of the summed period PVs
+    assert res.expected_profile['inventory'].iloc[0] == 0.0
+
+
+def test_multi_factor_value_regression():   # test_multi_factor.py:167-239
+    storage, fwd, rates = wrapper_test_inputs()
+    idx = pd.period_range(VAL_DATE, '2020-06-01', freq='D')
+    factors = [(0.0, pd.Series(0.14, index=idx)), (16.2, pd.Series(1.15, index=idx))]
+    progresses = []
+    res = storage_b200.multi_factor_value(storage, VAL_DATE, 0.0, fwd, rates, twentieth_of_next_month, factors, 0.64, NUM_SIMS,
+                                          '1 + x0 + x0**2 + x1 + x1*x1', False, seed=SEED, fwd_sim_seed=SEED,
+                                          on_progress_update=progresses.append)
+    check_result_structure(res, progresses)
+    assert abs(res.npv / 1780380.7581833513 - 1.0) < 0.03        # the reference's seeded value (:226), as a Monte-Carlo band
+    # the same flattened problem and Philox seeds through the CPU oracle
+    pb = flatten_problem(storage, VAL_DATE, 0.0, fwd, rates, twentieth_of_next_month, factors, np.array([[1.0, 0.64], [0.64, 1.0]]),
+                         NUM_SIMS, '1 + x0 + x0**2 + x1 + x1*x1', False)
+    ref = oracle.calculate(pb, Rng.philox(SEED), Rng.philox(SEED)).results
+    assert abs(res.npv / ref.npv - 1.0) < 1e-9
+    assert np.max(np.abs(res.deltas.values - ref.deltas)) < 1e-9 * np.max(np.abs(ref.deltas))
+    assert np.max(np.abs(res.expected_profile.values - ref.profile)) < 1e-9 * np.max(np.abs(ref.profile))
+
+
+def test_three_factor_seasonal_regression():   # test_multi_factor.py:241-311
+    storage, fwd, rates = wrapper_test_inputs()
+    progresses = []
+    res = storage_b200.three_factor_seasonal_value(storage, VAL_DATE, 0.0, fwd, rates, twentieth_of_next_month, 16.2, 1.15, 0.14, 0.18,
+                                                   NUM_SIMS, '1 + x_st + x_sw + x_lt + x_st**2 + x_sw**2 + x_lt**2', False,
+                                                   seed=SEED, fwd_sim_seed=SEED, on_progress_update=progresses.append)
+    check_result_structure(res, progresses)
+    assert abs(res.npv / 1766460.137569665 - 1.0) < 0.03         # :298
+
+
+def test_wrapper_validates_like_the_reference():
+    storage, fwd, rates = wrapper_test_inputs()
+    idx = pd.period_range(VAL_DATE, '2020-06-01', freq='D')
+    vol = pd.Series(0.5, index=idx)
+    with pytest.raises(ValueError, match="factors cannot be empty"):                               # multi_factor.py:113-115
+        storage_b200.multi_factor_value(storage, VAL_DATE, 0.0, fwd, rates, twentieth_of_next_month, [], None, 10, '1 + x0', False)
+    with pytest.raises(ValueError, match="not valid as not in the interval"):                      # :137-141
+        storage_b200.multi_factor_value(storage, VAL_DATE, 0.0, fwd, rates, twentieth_of_next_month, [(1.0, vol), (2.0, vol)], 1.5, 10,
+                                        '1 + x0', False)
+    monthly = pd.Series(50.0, index=pd.period_range('2019-08', '2020-06', freq='M'))
+    with pytest.raises(ValueError, match="different frequencies"):                                 # :372-373
+        storage_b200.multi_factor_value(storage, VAL_DATE, 0.0, monthly, rates, twentieth_of_next_month, [(1.0, vol)], None, 10,
+                                        '1 + x0', False)
+    with pytest.raises(ValueError, match="Inventory cannot be negative"):                          # LSV.cs:61
+        storage_b200.multi_factor_value(storage, VAL_DATE, -1.0, fwd, rates, twentieth_of_next_month, [(1.0, vol)], None, 10, '1 + x0', False)
+    expired = storage_b200.multi_factor_value(storage, '2020-04-05', 0.0, pd.Series(50.0, index=pd.period_range('2020-04-01', '2020-05-01', freq='D')),
+                                              rates, twentieth_of_next_month, [(1.0, vol)], None, 10, '1 + x0', False)
+    assert expired.npv == 0.0 and len(expired.deltas) == 0                                         # LSV.cs:64-68
+
+
+def test_multi_factor_spot_sim_shapes_mean_and_variance():   # multi_factor.py:49-92; test_multi_factor.py:45-91
+    idx = pd.period_range('2020-08-01', '2021-01-01', freq='D')
+    fwd = pd.Series(50.0 + 0.01 * np.arange(len(idx)), index=idx)
+    vol = pd.Series(0.6, index=idx)
+    sim_periods = pd.period_range('2020-09-01', '2020-09-30', freq='D')
+    sim = multi_factor.MultiFactorSpotSim('D', [(12.0, vol)], None, '2020-08-01', fwd, sim_periods, seed=12, antithetic=True)
+    n = 20_000
+    spots = sim.simulate(n)
+    assert spots.shape == (30, n) and list(spots.index) == list(sim_periods)
+    mean = spots.mean(axis=1).values
+    se = spots.std(axis=1).values / np.sqrt(n / 2)
+    assert np.all(np.abs(mean - fwd[sim_periods].values) < 4.5 * se)                 # martingale: E[S(T)] = F(0,T)
+    t = np.array([(p.start_time - pd.Timestamp('2020-08-01')).days / 365.0 for p in sim_periods])
+    var = 0.6 ** 2 * (1.0 - np.exp(-2 * 12.0 * t)) / (2 * 12.0)                      # TestHelper.cs:77-86
+    assert np.allclose(np.log(spots.values).var(axis=1), var, rtol=0.05)
+    again = multi_factor.MultiFactorSpotSim('D', [(12.0, vol)], None, '2020-08-01', fwd, sim_periods, seed=12, antithetic=True).simulate(n)
+    assert np.array_equal(again.values, spots.values)                                # seeded: reproducible

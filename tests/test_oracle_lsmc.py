@@ -11,7 +11,7 @@ from storage_b200._abi import Rng
 from storage_b200.flatten import flatten_problem, TrivialResult
 from oracle import oracle
 from fixtures import (reference_problem, simple_daily_storage, ratchet_daily_storage, three_calls_problem, sin_forward_curve,
-                      flat_rates, settle_rule, ONE_FACTOR_BASIS, STORAGE_END)
+                      flat_rates, settle_rule, forced_inject_withdraw_problem, ONE_FACTOR_BASIS, STORAGE_END)
 
 
 def run(pb, seed=11, fwd_seed=22, **kw):
@@ -148,3 +148,12 @@ def test_very_low_vol_one_factor_matches_intrinsic(storage_fn, tol):   # LSMCTes
     res = run(pb).results
     intrinsic = intrinsic_value(pb, 600)
     assert abs(res.npv / intrinsic - 1.0) < tol + 5e-4   # + the test DP's own grid error (600 pts vs the reference's exact DP)
+
+
+def test_forced_inject_and_withdraw_npv_equals_the_schedule_valued_on_the_forward_curve():   # LSMCTest:686-837
+    pb, expected = forced_inject_withdraw_problem(num_sims=1_000)
+    res = run(pb, seed=11, fwd_seed=22).results
+    assert abs(res.npv / expected - 1.0) < 0.03          # the reference's own tolerance: sampling error of E[spot] vs forward
+    prof = res.profile
+    assert prof[:, 1].max() == pytest.approx(211.5, rel=1e-12) and prof[:, 1].min() == pytest.approx(-187.54, rel=1e-12)   # every path follows the forced schedule
+    assert prof[-1, 0] == pytest.approx(20 * 211.5 - 15 * 187.54, rel=1e-12)  # what is left at the end

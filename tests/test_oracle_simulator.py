@@ -135,3 +135,27 @@ def test_injected_normals_reproduce_ou_recursion():
         np.testing.assert_allclose(fac[j, 0], x, rtol=1e-12, atol=1e-15)
         var = 0.25 * (1 - math.exp(-6.0 * t[j + 1])) / 6.0
         np.testing.assert_allclose(spot[j], pb.forward[s0 + j] * np.exp(0.5 * x - 0.5 * var), rtol=1e-12)
+
+
+def test_multi_factor_model_closed_forms_match_the_simulator():
+    """storage_b200.MultiFactorModel (the reference's analytic covariances, multi_factor.py:166-229) against the oracle's
+    simulated log-spot: one-factor variance sigma^2 (1 - exp(-2 alpha T)) / (2 alpha) (TestHelper.cs:77-86) in closed form,
+    two-factor variance and correlation against a 40 000-path sample."""
+    import math
+    import pandas as pd
+    from storage_b200 import MultiFactorModel
+    idx = pd.period_range("2019-08-29", "2020-04-01", freq="D")
+    one = MultiFactorModel("D", [(12.5, pd.Series(0.95, index=idx))])
+    expiry = pd.Period("2019-12-15", freq="D")
+    T = (expiry.ordinal - idx[0].ordinal) / 365.0
+    assert one.integrated_variance(idx[0], expiry, expiry) == pytest.approx(0.95 ** 2 * (1 - math.exp(-25.0 * T)) / 25.0, rel=1e-12)
+    assert one.integrated_vol(idx[0], expiry, expiry) == pytest.approx(math.sqrt(0.95 ** 2 * (1 - math.exp(-25.0 * T)) / 25.0 / T), rel=1e-12)
+    assert one.integrated_corr(idx[0], expiry, expiry, expiry) == 1.0
+    two = MultiFactorModel("D", [(0.0, pd.Series(0.3, index=idx)), (16.0, pd.Series(1.1, index=idx))], 0.4)
+    pb = reference_problem(num_sims=40_000, factors=[(0.0, pd.Series(0.3, index=idx)), (16.0, pd.Series(1.1, index=idx))],
+                           corrs=np.array([[1.0, 0.4], [0.4, 1.0]]), basis="1 + x0 + x1")
+    spot, _ = oracle.simulate(pb, Rng.philox(5))
+    for j in (3, 60, 200):
+        period = pb.periods[j + (pb.n_periods - pb.n_sim_periods)]
+        sample = np.log(spot[j]).var()
+        assert sample == pytest.approx(two.integrated_variance(idx[0], period, period), rel=0.03)
