@@ -63,6 +63,7 @@ def parse_args():
     ap.add_argument("--scaling", default=None, choices=["strong", "weak"],
                     help="strong (default): BASELINE's path count in total, split over the GPUs; weak: that many paths on every GPU")
     ap.add_argument("--no-parity", action="store_true", help="skip the correctness gates against the oracle")
+    ap.add_argument("--no-panels", action="store_true", help="skip the timing of the per-sim panel export")
     ap.add_argument("--cpu-paths", type=int, default=0, help="paths of the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -307,6 +308,24 @@ def main():
     barrier()
     e2e_elapsed = time.perf_counter() - t1
 
+    # ---- the same call with the eight [P][N] per-sim panels the reference API always returns (LSV.cs:602-616), into
+    #      page-locked buffers (lsmc_host_alloc): export by the copy engine, all panels in flight ----
+    panels_ms = panels_bytes = None
+    if not args.no_panels and 8.0 * 8 * pb.n_periods * n_local < 48e9:
+        try:
+            pres = _abi.Results(pb.n_periods, pb.n_sim_periods, n_local, panels="all", pv_by_sim=True, pinned=True)
+            ctx.calculate(pb, reg, val, results=pres)
+            barrier()
+            tp0 = time.perf_counter()
+            for _ in range(max(1, min(args.steps, 3))):
+                ctx.calculate(pb, reg, val, results=pres)
+            barrier()
+            panels_ms = 1e3 * (time.perf_counter() - tp0) / max(1, min(args.steps, 3))
+            panels_bytes = int(sum(getattr(pres, name).nbytes for name in _abi.PANEL_NAMES))
+            del pres
+        except Exception as e:   # e.g. not enough page-locked memory on the host
+            panels_ms, panels_bytes = None, str(e)
+
     times = torch.tensor([elapsed, e2e_elapsed, wall], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
@@ -347,6 +366,10 @@ def main():
             "e2e": {"value": n_global * T / (e2e_elapsed / args.steps), "unit": "path-steps/s",
                     "h2d_bytes_per_step": problem_h2d_bytes(pb), "d2h_bytes_per_step": results_d2h_bytes(e2e_res),
                     "ms_per_step": 1e3 * e2e_elapsed / args.steps, "api": "lsmc_calculate (include/lsmc_b200.h) with host buffers"},
+            "e2e_panels": None if panels_ms is None else {
+                "ms_per_step": panels_ms, "value": n_local * T / (panels_ms / 1e3), "unit": "path-steps/s (this rank)",
+                "d2h_bytes_per_step": panels_bytes, "export_gbs": (panels_bytes / 1e9) / max(1e-9, (panels_ms - 1e3 * e2e_elapsed / args.steps) / 1e3),
+                "note": "lsmc_calculate with all eight [P][N] panels requested into page-locked host buffers; export_gbs = panel bytes / (this time - e2e time)"},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"kernel": "sweep4_kernel (fused decision sweep + regression fit + DMMA normal equations, one launch per period)",

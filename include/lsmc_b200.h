@@ -41,7 +41,12 @@ typedef enum lsmc_status {
 enum {
     LSMC_CONSTRAINT_CONSTANT = 0,          /* ConstantInjectWithdrawConstraint.cs:45 */
     LSMC_CONSTRAINT_PIECEWISE_LINEAR = 1,  /* PiecewiseLinearInjectWithdrawConstraint.cs:67 */
-    LSMC_CONSTRAINT_STEP = 2               /* StepInjectWithdrawConstraint.cs:72 */
+    LSMC_CONSTRAINT_STEP = 2,              /* StepInjectWithdrawConstraint.cs:72 */
+    LSMC_CONSTRAINT_POLYNOMIAL = 3         /* PolynomialInjectWithdrawConstraint.cs:80: rates are polynomials in the inventory.  The host
+                                              fits them (the C# shim passes MathNet's own Fit.Polynomial coefficients, :66-73):
+                                              pillar_min_rate / pillar_max_rate hold the COEFFICIENTS c_0 .. c_{n-1} (ascending powers,
+                                              evaluated by Horner's rule like Polynomial.Evaluate), pillar_inventory the fitted pillars'
+                                              inventories (ascending; only the first and last are used, as the inventory range) */
 };
 
 /* Normal-draw source for one simulation set. */
@@ -112,6 +117,7 @@ typedef struct lsmc_problem {
 #define LSMC_MAX_FACTORS 8
 #define LSMC_MAX_BASIS 64
 #define LSMC_NUM_TRIGGER_VOLUMES 10   /* LSV.cs:367 */
+#define LSMC_MAX_POLYNOMIAL_PILLARS 16 /* polynomial constraints: at most degree 15 */
 
 typedef struct lsmc_rng {
     int32_t mode;             /* LSMC_RNG_* */
@@ -219,6 +225,14 @@ int lsmc_backward(lsmc_ctx* ctx, lsmc_progress_cb progress, void* progress_user)
 int lsmc_forward(lsmc_ctx* ctx, lsmc_progress_cb progress, void* progress_user);
 int lsmc_get_results(lsmc_ctx* ctx, lsmc_results* results);             /* D2H of whatever is non-NULL */
 int lsmc_get_timings(const lsmc_ctx* ctx, lsmc_timings* out);
+
+/* Page-locked host memory for result buffers.  lsmc_get_results / lsmc_calculate write per-sim panels ([P][N] doubles each:
+ * 23 GB for the eight panels of a 1M-path daily year, LSV.cs:351-356,602-616) with the copy engine straight into a
+ * destination that is page-locked (these helpers, cudaHostAlloc or cudaHostRegister) — all panels in flight, one
+ * synchronisation; a pageable destination is served through two 32 MB page-locked staging chunks, the copy of one chunk
+ * overlapping the host memcpy of the other. */
+int  lsmc_host_alloc(size_t bytes, void** out);
+void lsmc_host_free(void* p);
 
 /* Intrinsic valuation on the forward curve, the deterministic model the reference's Python entry points run beside the
  * LSMC (multi_factor.py:406 -> IntrinsicStorageValuation.cs:120-322): backward induction over the same inventory grids with

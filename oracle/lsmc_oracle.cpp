@@ -38,6 +38,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <functional>
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
@@ -157,6 +158,58 @@ double linear_spline(const double* x, const double* y, int n, double t) {
     return y[k] + (t - x[k]) * c1;
 }
 
+// MathNet Polynomial.Evaluate(z) (coefficients ascending): sum = c[n-1]; for i = n-2..0 { sum *= z; sum += c[i]; }.
+double polynomial_evaluate(const double* c, int n, double z) {
+    double sum = c[n - 1];
+    for (int i = n - 2; i >= 0; --i) { sum *= z; sum += c[i]; }
+    return sum;
+}
+
+// Polynomial.Differentiate().Evaluate(z): coefficients i * c[i].
+double polynomial_derivative(const double* c, int n, double z) {
+    if (n < 2) return 0.0;
+    double sum = (n - 1) * c[n - 1];
+    for (int i = n - 2; i >= 1; --i) { sum *= z; sum += i * c[i]; }
+    return sum;
+}
+
+// Stand-in for MathNet RobustNewtonRaphson.TryFindRoot(f, df, lower, upper, accuracy, maxIterations, subdivision, out root)
+// (PARITY UNPINNED: MathNet is not in the tree).  Specification shared with the product's host plan so that both compute
+// the same inventory space: bracket by sign change (cutting [lower, upper] into `subdivision` equal parts from the low end
+// when the end points do not bracket), then Newton steps from the mid point, replaced by the bisection point whenever a
+// step leaves the bracket; stop when |f| or the step falls below `accuracy`.
+bool robust_newton_raphson(const std::function<double(double)>& f, const std::function<double(double)>& df, double lower, double upper,
+                           double accuracy, int maxIterations, int subdivision, double& root) {
+    double fl = f(lower), fu = f(upper);
+    if (fl == 0.0) { root = lower; return true; }
+    if (fu == 0.0) { root = upper; return true; }
+    if ((fl > 0.0) == (fu > 0.0)) {
+        double width = (upper - lower) / subdivision;
+        double a = lower, fa = fl;
+        bool bracketed = false;
+        for (int k = 1; k <= subdivision; k++) {
+            double b = (k == subdivision) ? upper : lower + k * width;
+            double fb = f(b);
+            if (fb == 0.0) { root = b; return true; }
+            if ((fa > 0.0) != (fb > 0.0)) { lower = a; upper = b; fl = fa; fu = fb; bracketed = true; break; }
+            a = b; fa = fb;
+        }
+        if (!bracketed) return false;
+    }
+    double x = 0.5 * (lower + upper);
+    for (int it = 0; it < maxIterations; it++) {
+        double fx = f(x);
+        if (std::fabs(fx) < accuracy) { root = x; return true; }
+        if ((fx > 0.0) == (fl > 0.0)) { lower = x; fl = fx; } else { upper = x; fu = fx; }
+        double slope = df(x);
+        double next = (slope != 0.0) ? x - fx / slope : 0.5 * (lower + upper);
+        if (!(next > lower && next < upper)) next = 0.5 * (lower + upper);
+        if (std::fabs(next - x) < accuracy) { root = next; return true; }
+        x = next;
+    }
+    return false;
+}
+
 // IInjectWithdrawConstraint.GetInjectWithdrawRange: Constant…cs:45-48, PiecewiseLinear…cs:67-72, Step…cs:72-79.
 void constraint_range(const Constraint& c, double inventory, double& rmin, double& rmax) {
     switch (c.kind) {
@@ -177,6 +230,10 @@ void constraint_range(const Constraint& c, double inventory, double& rmin, doubl
             rmin = c.rmin[idx]; rmax = c.rmax[idx];
             return;
         }
+        case LSMC_CONSTRAINT_POLYNOMIAL:   // Polynomial…cs:80-85: both rates are polynomials in the inventory
+            rmax = polynomial_evaluate(c.rmax, c.n, inventory);
+            rmin = polynomial_evaluate(c.rmin, c.n, inventory);
+            return;
         default:
             throw OracleError(LSMC_EUNSUPPORTED, "unknown constraint kind");
     }
@@ -209,7 +266,18 @@ double interpolate_linear_and_solve(double x1, double y1, double x2, double y2, 
 // IInjectWithdrawConstraint.InventorySpaceUpperBound:
 //   Constant…cs:50-56, PiecewiseLinear…cs:74-117, Step…cs:81-122.
 double space_upper_bound(const Constraint& c, double nextLo, double nextHi, double curMin, double curMax, double loss) {
-    (void)curMin;
+    if (c.kind == LSMC_CONSTRAINT_POLYNOMIAL) {   // Polynomial…cs:87-120
+        double maxFromMax = curMax + polynomial_evaluate(c.rmax, c.n, curMax);
+        double minFromMax = curMax + polynomial_evaluate(c.rmin, c.n, curMax);
+        if (minFromMax <= nextHi && nextLo <= maxFromMax) return curMax;
+        auto polyToSolve = [&](double inv) { return inv * (1 - loss) + polynomial_evaluate(c.rmin, c.n, inv) - nextHi; };
+        auto polyToSolveDeriv = [&](double inv) { return (1 - loss) + polynomial_derivative(c.rmin, c.n, inv); };
+        double thisPeriodMax = 0.0;
+        if (!robust_newton_raphson(polyToSolve, polyToSolveDeriv, curMin, curMax, 1e-10, 100, 20, thisPeriodMax))
+            throw OracleError(LSMC_ECONSTRAINT, "Cannot solve for the current period inventory space upper bound. Try changing Newton Raphson parameters.");
+        if (thisPeriodMax < curMin) throw OracleError(LSMC_ECONSTRAINT, "Inventory constraints cannot be satisfied.");
+        return std::min(thisPeriodMax, curMax);
+    }
     if (c.kind == LSMC_CONSTRAINT_CONSTANT) {
         double solved = (nextHi - c.rmin[0]) / (1 - loss);
         return std::min(solved, curMax);
@@ -252,7 +320,18 @@ double space_upper_bound(const Constraint& c, double nextLo, double nextHi, doub
 
 //   Constant…cs:58-65, PiecewiseLinear…cs:119-160, Step…cs:124-166.
 double space_lower_bound(const Constraint& c, double nextLo, double nextHi, double curMin, double curMax, double loss) {
-    (void)curMax;
+    if (c.kind == LSMC_CONSTRAINT_POLYNOMIAL) {   // Polynomial…cs:122-156
+        double maxFromMin = curMin + polynomial_evaluate(c.rmax, c.n, curMin);
+        double minFromMin = curMin + polynomial_evaluate(c.rmin, c.n, curMin);
+        if (minFromMin <= nextHi && nextLo <= maxFromMin) return curMin;
+        auto polyToSolve = [&](double inv) { return inv * (1 - loss) + polynomial_evaluate(c.rmax, c.n, inv) - nextLo; };
+        auto polyToSolveDeriv = [&](double inv) { return (1 - loss) + polynomial_derivative(c.rmax, c.n, inv); };
+        double thisPeriodMin = 0.0;
+        if (!robust_newton_raphson(polyToSolve, polyToSolveDeriv, curMin, curMax, 1e-10, 100, 20, thisPeriodMin))
+            throw OracleError(LSMC_ECONSTRAINT, "Cannot solve for the current period inventory space lower bound. Try changing Newton Raphson parameters.");
+        if (thisPeriodMin > curMax) throw OracleError(LSMC_ECONSTRAINT, "Inventory constraints cannot be satisfied.");
+        return std::max(thisPeriodMin, curMin);
+    }
     if (c.kind == LSMC_CONSTRAINT_CONSTANT) {
         double solved = (nextLo - c.rmax[0]) / (1 - loss);
         return std::max(solved, curMin);

@@ -6,7 +6,7 @@ import ctypes as C
 import numpy as np
 
 LSMC_OK, LSMC_EINVAL, LSMC_ECONSTRAINT, LSMC_ECANCELLED, LSMC_ECUDA, LSMC_EUNSUPPORTED = range(6)
-CONSTRAINT_CONSTANT, CONSTRAINT_PIECEWISE_LINEAR, CONSTRAINT_STEP = 0, 1, 2
+CONSTRAINT_CONSTANT, CONSTRAINT_PIECEWISE_LINEAR, CONSTRAINT_STEP, CONSTRAINT_POLYNOMIAL = 0, 1, 2, 3
 RNG_PHILOX, RNG_NORMALS, RNG_PANELS = 0, 1, 2
 MAX_FACTORS, MAX_BASIS, NUM_TRIGGER_VOLUMES = 8, 64, 10
 
@@ -192,8 +192,15 @@ class Rng:
 class Results:
     """Caller-allocated result buffers (lsmc_results)."""
 
-    def __init__(self, P, S, N, panels=(), pv_by_sim=True, decision_index=False, triggers=True):
+    def __init__(self, P, S, N, panels=(), pv_by_sim=True, decision_index=False, triggers=True, pinned=False):
+        """pinned: allocate the per-sim panels in page-locked host memory (lsmc_host_alloc) so that the library's copy
+        engine writes them directly."""
         self.P, self.S, self.N = int(P), int(S), int(N)
+        if pinned:
+            from ._native import pinned_zeros
+            panel_zeros = pinned_zeros
+        else:
+            panel_zeros = np.zeros
         self.deltas = np.zeros(P)
         self.profile = np.zeros((P, 6))
         self.trigger_summary = np.full((P - 1, 4), np.nan) if triggers else None
@@ -202,7 +209,7 @@ class Results:
         self.pv_by_sim = np.zeros(N) if pv_by_sim else None
         for name in PANEL_NAMES:
             rows = S if name.startswith("spot_") else P
-            setattr(self, name, np.zeros((rows, N)) if (panels == "all" or name in panels) else None)
+            setattr(self, name, panel_zeros((rows, N)) if (panels == "all" or name in panels) else None)
         self.decision_index = np.zeros((P - 1, N), dtype=np.int8) if decision_index else None
         self.npv = self.npv_std_error = self.backward_npv = float("nan")
         self._c = None

@@ -14,7 +14,7 @@ LIB_PATH = os.environ.get("LSMC_B200_LIB") or os.path.join(_HERE, "liblsmc_b200.
 
 EXPORTS = (
     "lsmc_version", "lsmc_create", "lsmc_destroy", "lsmc_last_error", "lsmc_comm_unique_id", "lsmc_comm_init", "lsmc_comm_init_local",
-    "lsmc_calculate_multi", "lsmc_intrinsic",
+    "lsmc_calculate_multi", "lsmc_intrinsic", "lsmc_host_alloc", "lsmc_host_free",
     "lsmc_calculate", "lsmc_set_problem", "lsmc_get_layout", "lsmc_request_outputs", "lsmc_simulate", "lsmc_backward",
     "lsmc_forward", "lsmc_get_results", "lsmc_get_timings", "lsmc_get_grid", "lsmc_get_inventory_space",
     "lsmc_get_regression_coeffs", "lsmc_get_sim_panel", "lsmc_debug_set_regression_coeffs", "lsmc_debug_keep_values",
@@ -186,6 +186,47 @@ class Context:
         out = np.zeros((g, self.layout().n_sims))
         self._check(lib().lsmc_debug_get_values(self._h, C.c_int(period), out.ctypes.data_as(_dp)))
         return out
+
+
+class _PinnedBlock:
+    """Owner of one lsmc_host_alloc block; numpy arrays created over it keep it alive through `.base`."""
+
+    def __init__(self, nbytes):
+        self.ptr = C.c_void_p()
+        rc = lib().lsmc_host_alloc(C.c_size_t(nbytes), C.byref(self.ptr))
+        if rc != 0:
+            raise LsmcError(rc, lib().lsmc_last_error(None).decode())
+        self.nbytes = nbytes
+
+    def __del__(self):
+        try:
+            if self.ptr:
+                lib().lsmc_host_free(self.ptr)
+                self.ptr = C.c_void_p()
+        except Exception:
+            pass
+
+
+def pinned_zeros(shape, dtype=np.float64):
+    """A zero-filled numpy array in page-locked host memory (lsmc_host_alloc): result panels allocated this way are written
+    by the copy engine directly (include/lsmc_b200.h)."""
+    dtype = np.dtype(dtype)
+    count = int(np.prod(shape))
+    block = _PinnedBlock(max(count * dtype.itemsize, 1))
+    lib().lsmc_host_free.argtypes = [C.c_void_p]
+    buf = (C.c_char * block.nbytes).from_address(block.ptr.value)
+    arr = np.frombuffer(buf, dtype=dtype, count=count).reshape(shape)
+    arr[...] = 0
+    _PINNED_OWNERS[arr.ctypes.data] = block   # keeps the block alive for the process lifetime of the view
+    return arr
+
+
+_PINNED_OWNERS = {}
+
+
+def release_pinned(arr):
+    """Free the page-locked block behind an array made by pinned_zeros (the array must not be used afterwards)."""
+    _PINNED_OWNERS.pop(arr.ctypes.data, None)
 
 
 def intrinsic(problem):

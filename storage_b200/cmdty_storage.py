@@ -13,7 +13,7 @@ import numpy as np
 import pandas as pd
 
 from . import utils
-from ._abi import CONSTRAINT_CONSTANT, CONSTRAINT_PIECEWISE_LINEAR, CONSTRAINT_STEP
+from ._abi import CONSTRAINT_CONSTANT, CONSTRAINT_PIECEWISE_LINEAR, CONSTRAINT_STEP, CONSTRAINT_POLYNOMIAL
 
 logger = logging.getLogger("cmdty.storage")
 
@@ -26,17 +26,38 @@ class InjectWithdrawRange(tp.NamedTuple):
 class RatchetInterp(Enum):
     LINEAR = 1
     STEP = 2
+    # Not in the reference's Python enum (cmdty_storage.py:44-46); the C# builder has it as InterpolationType.Polynomial
+    # (CmdtyStorageBuilderExtensions.cs:78-82 -> PolynomialInjectWithdrawConstraint): rates are the exact-degree polynomial
+    # through the pillars.
+    POLYNOMIAL = 3
+
+
+def fit_polynomial(x: tp.Sequence[float], y: tp.Sequence[float]) -> tp.Tuple[float, ...]:
+    """Fit.Polynomial(x, y, len(x) - 1) (PolynomialInjectWithdrawConstraint.cs:66-72): least squares on the Vandermonde
+    matrix — exact interpolation at this order.  Coefficients in ascending powers, like MathNet's Polynomial."""
+    design = np.vander(np.asarray(x, dtype=np.float64), len(x), increasing=True)
+    coef, *_ = np.linalg.lstsq(design, np.asarray(y, dtype=np.float64), rcond=None)
+    return tuple(float(c) for c in coef)
+
+
+def _horner(coef: tp.Sequence[float], z: float) -> float:   # Polynomial.Evaluate
+    total = coef[-1]
+    for c in reversed(coef[:-1]):
+        total = total * z + c
+    return total
 
 
 class _Constraint(tp.NamedTuple):
     kind: int
     inventory: tp.Tuple[float, ...]
-    min_rate: tp.Tuple[float, ...]
+    min_rate: tp.Tuple[float, ...]     # polynomial kind: coefficients (ascending powers) instead of pillar rates
     max_rate: tp.Tuple[float, ...]
 
     def range(self, inventory: float) -> InjectWithdrawRange:
         if self.kind == CONSTRAINT_CONSTANT:
             return InjectWithdrawRange(self.min_rate[0], self.max_rate[0])
+        if self.kind == CONSTRAINT_POLYNOMIAL:   # PolynomialInjectWithdrawConstraint.cs:80-85
+            return InjectWithdrawRange(_horner(self.min_rate, inventory), _horner(self.max_rate, inventory))
         x = self.inventory
         if self.kind == CONSTRAINT_STEP:    # StepInjectWithdrawConstraint.cs:72-79
             if inventory < x[0] or inventory > x[-1]:
@@ -159,10 +180,17 @@ class CmdtyStorage:
                 c = _Constraint(CONSTRAINT_CONSTANT, (min_inv, max_inv), (rows[0][1],) * 2, (rows[0][2],) * 2)   # :163-171
             else:
                 rows = sorted(rows, key=lambda r: r[0])
-                kind = CONSTRAINT_PIECEWISE_LINEAR if ratchet_interp == RatchetInterp.LINEAR else CONSTRAINT_STEP
-                if kind == CONSTRAINT_STEP:
-                    self._validate_step(rows)
-                c = _Constraint(kind, tuple(r[0] for r in rows), tuple(r[1] for r in rows), tuple(r[2] for r in rows))
+                if ratchet_interp == RatchetInterp.POLYNOMIAL:
+                    if len(rows) > 16:
+                        raise ValueError("Polynomial ratchets support at most 16 inventory pillars.")
+                    xs = [r[0] for r in rows]
+                    c = _Constraint(CONSTRAINT_POLYNOMIAL, tuple(xs), fit_polynomial(xs, [r[1] for r in rows]),
+                                    fit_polynomial(xs, [r[2] for r in rows]))
+                else:
+                    kind = CONSTRAINT_PIECEWISE_LINEAR if ratchet_interp == RatchetInterp.LINEAR else CONSTRAINT_STEP
+                    if kind == CONSTRAINT_STEP:
+                        self._validate_step(rows)
+                    c = _Constraint(kind, tuple(r[0] for r in rows), tuple(r[1] for r in rows), tuple(r[2] for r in rows))
             self._ratchet_periods.append(period)
             self._ratchet_constraints.append(c)
 

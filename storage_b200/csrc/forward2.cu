@@ -196,7 +196,10 @@ __global__ void __launch_bounds__(kF2Threads, kF2MinBlocks) forward2_kernel(cons
                 rmax = add_rn(s_chi[k], mul_rn(dxv, s_shi[k]));
                 rmin = add_rn(s_clo[k], mul_rn(dxv, s_slo[k]));
             } else if (c_kind == LSMC_CONSTRAINT_CONSTANT) { rmin = s_clo[0]; rmax = s_chi[0]; }
-            else {   // step ratchets (StepInjectWithdrawConstraint.cs:72-79): the pillar at or below v; entries from c_n on are +inf
+            else if (c_kind == LSMC_CONSTRAINT_POLYNOMIAL) {   // Polynomial.Evaluate: Horner over the staged coefficients, no contraction
+                rmax = s_chi[c_n - 1]; rmin = s_clo[c_n - 1];
+                for (int i = c_n - 2; i >= 0; i--) { rmax = add_rn(mul_rn(rmax, v), s_chi[i]); rmin = add_rn(mul_rn(rmin, v), s_clo[i]); }
+            } else {   // step ratchets (StepInjectWithdrawConstraint.cs:72-79): the pillar at or below v; entries from c_n on are +inf
                 if (v < s_cx[0] - q.slack_hi || v > s_cx[c_n - 1] + q.slack_hi) atomicExch(q.error_flag, 2);
                 int idx = 0;
                 for (int i = 1; i < c_n; i++) idx += (s_cx[i] <= v) ? 1 : 0;

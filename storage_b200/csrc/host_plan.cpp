@@ -52,7 +52,8 @@ void ProblemCopy::assign(const lsmc_problem& src) {
         if (pb.constraint_id[p] < 0 || pb.constraint_id[p] >= src.n_constraints) throw Error(LSMC_EINVAL, "constraint_id out of range");
     for (size_t c = 0; c < C; c++) {
         int kind = pb.constraint_kind[c], first = pb.constraint_first[c], count = pb.constraint_count[c];
-        if (kind < LSMC_CONSTRAINT_CONSTANT || kind > LSMC_CONSTRAINT_STEP) throw Error(LSMC_EUNSUPPORTED, "unsupported inject/withdraw constraint kind");
+        if (kind < LSMC_CONSTRAINT_CONSTANT || kind > LSMC_CONSTRAINT_POLYNOMIAL) throw Error(LSMC_EUNSUPPORTED, "unsupported inject/withdraw constraint kind");
+        if (kind == LSMC_CONSTRAINT_POLYNOMIAL && count > LSMC_MAX_POLYNOMIAL_PILLARS) throw Error(LSMC_EUNSUPPORTED, "polynomial inject/withdraw constraint with more than 16 pillars");
         if (first < 0 || count < 1 || first + count > src.n_pillars) throw Error(LSMC_EINVAL, "constraint pillar range out of bounds");
         if (kind != LSMC_CONSTRAINT_CONSTANT && count < 2)
             throw Error(LSMC_EINVAL, "Inject/withdraw ranges collection must contain at least two elements.");
@@ -88,8 +89,58 @@ double spline_eval(const double* x, const double* y, int n, double v) {
     return y[k] + (v - x[k]) * slope;
 }
 
+// Polynomial.Evaluate (MathNet): Horner's rule from the highest coefficient, every multiply and add rounded.
+double horner(const double* coef, int n, double z) {
+    double sum = coef[n - 1];
+    for (int i = n - 2; i >= 0; i--) { sum *= z; sum += coef[i]; }
+    return sum;
+}
+
+double horner_derivative(const double* coef, int n, double z) {   // Polynomial.Differentiate().Evaluate
+    if (n < 2) return 0.0;
+    double sum = (n - 1) * coef[n - 1];
+    for (int i = n - 2; i >= 1; i--) { sum *= z; sum += i * coef[i]; }
+    return sum;
+}
+
+// Root of f on [lo, hi] by Newton's method kept inside a sign-change bracket (bisection when a step leaves it); when the
+// end points do not bracket, the interval is cut into `subdivision` parts and the lowest part with a sign change is used.
+// Stands in for MathNet's RobustNewtonRaphson.TryFindRoot (PolynomialInjectWithdrawConstraint.cs:109,144), which is not in
+// the tree: same contract (accuracy 1e-10, 100 iterations, 20 subdivisions by default), not the same iterates.
+template <typename Fn, typename Dfn>
+bool find_root(const Fn& f, const Dfn& df, double lo, double hi, double accuracy, int max_iterations, int subdivision, double& root) {
+    double flo = f(lo), fhi = f(hi);
+    if (flo == 0.0) { root = lo; return true; }
+    if (fhi == 0.0) { root = hi; return true; }
+    if ((flo > 0.0) == (fhi > 0.0)) {
+        const double step = (hi - lo) / subdivision;
+        bool found = false;
+        double a = lo, fa = flo;
+        for (int k = 1; k <= subdivision && !found; k++) {
+            const double b = k == subdivision ? hi : lo + k * step, fb = f(b);
+            if (fb == 0.0) { root = b; return true; }
+            if ((fa > 0.0) != (fb > 0.0)) { lo = a; hi = b; flo = fa; fhi = fb; found = true; }
+            a = b; fa = fb;
+        }
+        if (!found) return false;
+    }
+    double x = 0.5 * (lo + hi);
+    for (int it = 0; it < max_iterations; it++) {
+        const double fx = f(x);
+        if (std::fabs(fx) < accuracy) { root = x; return true; }
+        if ((fx > 0.0) == (flo > 0.0)) { lo = x; flo = fx; } else { hi = x; fhi = fx; }
+        const double d = df(x);
+        double xn = d != 0.0 ? x - fx / d : 0.5 * (lo + hi);
+        if (!(xn > lo && xn < hi)) xn = 0.5 * (lo + hi);
+        if (std::fabs(xn - x) < accuracy) { root = xn; return true; }
+        x = xn;
+    }
+    return false;
+}
+
 void rate_range(const Pillars& c, double v, double& rmin, double& rmax) {
     if (c.kind == LSMC_CONSTRAINT_CONSTANT) { rmin = c.lo[0]; rmax = c.hi[0]; return; }
+    if (c.kind == LSMC_CONSTRAINT_POLYNOMIAL) { rmax = horner(c.hi, c.n, v); rmin = horner(c.lo, c.n, v); return; }
     if (c.kind == LSMC_CONSTRAINT_PIECEWISE_LINEAR) {
         rmax = spline_eval(c.x, c.hi, c.n, v);
         rmin = spline_eval(c.x, c.lo, c.n, v);
@@ -108,6 +159,32 @@ double solve_on_line(double x1, double y1, double x2, double y2, double y) {   /
 }
 
 // Largest inventory of this period from which [nextLo, nextHi] is reachable.
+// PolynomialInjectWithdrawConstraint.InventorySpaceUpperBound / LowerBound (:87-156).  (The reachability test adds the rate to
+// the bound WITHOUT the loss, the root equation has it: as the reference writes them.)
+double polynomial_upper_bound(const Pillars& c, double nextLo, double nextHi, double curMin, double curMax, double loss) {
+    const double reachHi = curMax + horner(c.hi, c.n, curMax), reachLo = curMax + horner(c.lo, c.n, curMax);
+    if (reachLo <= nextHi && nextLo <= reachHi) return curMax;
+    double root = 0.0;
+    auto f = [&](double inv) { return inv * (1 - loss) + horner(c.lo, c.n, inv) - nextHi; };
+    auto df = [&](double inv) { return (1 - loss) + horner_derivative(c.lo, c.n, inv); };
+    if (!find_root(f, df, curMin, curMax, 1e-10, 100, 20, root))
+        throw Error(LSMC_ECONSTRAINT, "Cannot solve for the current period inventory space upper bound. Try changing Newton Raphson parameters.");
+    if (root < curMin) throw Error(LSMC_ECONSTRAINT, "Inventory constraints cannot be satisfied.");
+    return std::min(root, curMax);
+}
+
+double polynomial_lower_bound(const Pillars& c, double nextLo, double nextHi, double curMin, double curMax, double loss) {
+    const double reachHi = curMin + horner(c.hi, c.n, curMin), reachLo = curMin + horner(c.lo, c.n, curMin);
+    if (reachLo <= nextHi && nextLo <= reachHi) return curMin;
+    double root = 0.0;
+    auto f = [&](double inv) { return inv * (1 - loss) + horner(c.hi, c.n, inv) - nextLo; };
+    auto df = [&](double inv) { return (1 - loss) + horner_derivative(c.hi, c.n, inv); };
+    if (!find_root(f, df, curMin, curMax, 1e-10, 100, 20, root))
+        throw Error(LSMC_ECONSTRAINT, "Cannot solve for the current period inventory space lower bound. Try changing Newton Raphson parameters.");
+    if (root > curMax) throw Error(LSMC_ECONSTRAINT, "Inventory constraints cannot be satisfied.");
+    return std::max(root, curMin);
+}
+
 double upper_bound_of_space(const Pillars& c, double nextLo, double nextHi, double curMax, double loss) {
     if (c.kind == LSMC_CONSTRAINT_CONSTANT) return std::min((nextHi - c.lo[0]) / (1 - loss), curMax);
     double rmin, rmax;
@@ -270,6 +347,11 @@ void inventory_space(const lsmc_problem& pb, std::vector<double>& lo, std::vecto
         int period = i + 1;
         Pillars c = pillars_of(pb, period);
         double loss = pb.inventory_loss[period];
+        if (c.kind == LSMC_CONSTRAINT_POLYNOMIAL) {
+            bHi[i] = polynomial_upper_bound(c, bLo[i + 1], bHi[i + 1], pb.min_inventory[period], pb.max_inventory[period], loss);
+            bLo[i] = polynomial_lower_bound(c, bLo[i + 1], bHi[i + 1], pb.min_inventory[period], pb.max_inventory[period], loss);
+            continue;
+        }
         bHi[i] = upper_bound_of_space(c, bLo[i + 1], bHi[i + 1], pb.max_inventory[period], loss);
         bLo[i] = lower_bound_of_space(c, bLo[i + 1], bHi[i + 1], pb.min_inventory[period], loss);
     }

@@ -328,6 +328,13 @@ __device__ __forceinline__ int last_at_or_below(const double* x, int n, double v
     return lo - 1;
 }
 
+// Polynomial.Evaluate (PolynomialInjectWithdrawConstraint.cs:80-85): Horner from the highest coefficient, no contraction.
+__device__ __forceinline__ double horner_dev(const double* coef, int n, double z) {
+    double sum = __ldg(coef + n - 1);
+    for (int i = n - 2; i >= 0; i--) sum = add_rn(mul_rn(sum, z), __ldg(coef + i));
+    return sum;
+}
+
 __device__ __forceinline__ double spline_dev(const double* x, const double* y, int n, double v) {
     int k = min(max(last_at_or_below(x, n, v), 0), n - 2);
     double x0 = __ldg(x + k), y0 = __ldg(y + k);
@@ -518,6 +525,7 @@ __global__ void __launch_bounds__(kFwdThreads, KT <= 16 ? LSMC_FWD_MINB : 1) for
                 rmin = add_rn(s_clo[k], mul_rn(dxv, s_slo[k]));
             }
             else if (q.c_kind == LSMC_CONSTRAINT_PIECEWISE_LINEAR) { rmax = spline_dev(q.c_x, q.c_hi, q.c_n, v); rmin = spline_dev(q.c_x, q.c_lo, q.c_n, v); }
+            else if (q.c_kind == LSMC_CONSTRAINT_POLYNOMIAL) { rmax = horner_dev(q.c_hi, q.c_n, v); rmin = horner_dev(q.c_lo, q.c_n, v); }
             else {
                 if (v < __ldg(q.c_x) - q.slack_hi || v > __ldg(q.c_x + q.c_n - 1) + q.slack_hi) atomicExch(q.error_flag, 2);
                 int idx = min(max(last_at_or_below(q.c_x, q.c_n, v), 0), q.c_n - 1);
@@ -760,6 +768,7 @@ __global__ void __launch_bounds__(kFwdFastThreads, LSMC_FWDF_MINB) forward_fast_
                 rmin = add_rn(s_clo[k], mul_rn(dxv, s_slo[k]));
             } else if (c_kind == LSMC_CONSTRAINT_CONSTANT) { rmin = __ldg(q.c_lo); rmax = __ldg(q.c_hi); }
             else if (c_kind == LSMC_CONSTRAINT_PIECEWISE_LINEAR) { rmax = spline_dev(q.c_x, q.c_hi, c_n, v); rmin = spline_dev(q.c_x, q.c_lo, c_n, v); }
+            else if (c_kind == LSMC_CONSTRAINT_POLYNOMIAL) { rmax = horner_dev(q.c_hi, c_n, v); rmin = horner_dev(q.c_lo, c_n, v); }
             else {
                 if (v < __ldg(q.c_x) - q.slack_hi || v > __ldg(q.c_x + c_n - 1) + q.slack_hi) atomicExch(q.error_flag, 2);
                 int idx = min(max(last_at_or_below(q.c_x, c_n, v), 0), c_n - 1);

@@ -200,6 +200,9 @@ struct lsmc_ctx {
     double backward_npv = 0.0, npv = 0.0, npv_se = 0.0, final_inventory_sum = 0.0, terminal_pv_sum = 0.0;
     std::vector<double> h_fwd;   // [P-1][nsum]
     PinnedBuf pin;               // kPinScalars scalars, then the [P-1][nsum] forward sums
+    PinnedBuf export_stage;      // two page-locked staging chunks of the panel export (pageable destinations)
+    bool export_pending = false; // asynchronous copies into page-locked destinations not yet synchronised
+    cudaEvent_t export_ev[2] = {nullptr, nullptr};
 
     // timings
     lsmc_timings tm{};
@@ -207,6 +210,7 @@ struct lsmc_ctx {
 
     ~lsmc_ctx() {
         for (auto e : ev) cudaEventDestroy(e);
+        for (auto e : export_ev) if (e) cudaEventDestroy(e);
         if (comm && g_nccl.CommDestroy) g_nccl.CommDestroy(comm);
         if (stream) cudaStreamDestroy(stream);
     }
@@ -928,10 +932,58 @@ void assemble_summary(lsmc_ctx* c, lsmc_results* r) {
 
 // Per-sim outputs: rows of N doubles into the caller's [rows][pitch] buffer at column out_col0 (a rank of a multi-GPU
 // valuation writes its own block of columns; a single context has pitch = N, column 0).
+//
+// Export path (the eight [P][N] panels are 23 GB at C3).  A destination in page-locked memory
+// (lsmc_host_alloc, cudaHostAlloc, cudaHostRegister) is written by the copy engine directly: every panel is enqueued on the
+// context's stream and the call synchronises once.  A pageable destination goes through two page-locked staging chunks:
+// the copy engine fills one while the calling thread empties the other into the caller's array.
+constexpr size_t kExportChunkBytes = (size_t)32 << 20;
+
+bool is_page_locked(const void* p) {
+    cudaPointerAttributes attr{};
+    if (cudaPointerGetAttributes(&attr, p) != cudaSuccess) { (void)cudaGetLastError(); return false; }
+    return attr.type == cudaMemoryTypeHost;
+}
+
 void copy_panel(lsmc_ctx* c, double* dst, const double* src, size_t rows) {
-    if (!dst) return;
-    const size_t pitch = c->out_pitch > 0 ? (size_t)c->out_pitch : (size_t)c->N;
-    CUDA_CHECK(cudaMemcpy2D(dst + c->out_col0, pitch * sizeof(double), src, (size_t)c->Npad * sizeof(double), (size_t)c->N * sizeof(double), rows, cudaMemcpyDeviceToHost));
+    if (!dst || rows == 0) return;
+    const size_t pitch = c->out_pitch > 0 ? (size_t)c->out_pitch : (size_t)c->N, n = (size_t)c->N;
+    const size_t src_pitch = (size_t)c->Npad * sizeof(double), width = n * sizeof(double);
+    cudaStream_t s = c->stream;
+    dst += c->out_col0;
+    if (is_page_locked(dst)) {
+        CUDA_CHECK(cudaMemcpy2DAsync(dst, pitch * sizeof(double), src, src_pitch, width, rows, cudaMemcpyDeviceToHost, s));
+        c->export_pending = true;
+        return;
+    }
+    if (rows * width <= ((size_t)1 << 20)) {   // small: not worth the staging
+        CUDA_CHECK(cudaMemcpy2DAsync(dst, pitch * sizeof(double), src, src_pitch, width, rows, cudaMemcpyDeviceToHost, s));
+        CUDA_CHECK(cudaStreamSynchronize(s));
+        return;
+    }
+    c->export_stage.alloc(2 * kExportChunkBytes / sizeof(double));
+    const size_t rows_per_chunk = std::max<size_t>(1, kExportChunkBytes / width);
+    if (rows_per_chunk * width > kExportChunkBytes) {   // one row is larger than a chunk (> 4M paths): plain copy
+        CUDA_CHECK(cudaMemcpy2DAsync(dst, pitch * sizeof(double), src, src_pitch, width, rows, cudaMemcpyDeviceToHost, s));
+        CUDA_CHECK(cudaStreamSynchronize(s));
+        return;
+    }
+    for (auto& e : c->export_ev) if (!e) CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    cudaEvent_t* done = c->export_ev;
+    double* stage[2] = {c->export_stage.p, c->export_stage.p + kExportChunkBytes / sizeof(double)};
+    const size_t n_chunks = (rows + rows_per_chunk - 1) / rows_per_chunk;
+    auto issue = [&](size_t k) {
+        const size_t r0 = k * rows_per_chunk, nr = std::min(rows_per_chunk, rows - r0);
+        CUDA_CHECK(cudaMemcpy2DAsync(stage[k & 1], width, src + r0 * (size_t)c->Npad, src_pitch, width, nr, cudaMemcpyDeviceToHost, s));
+        CUDA_CHECK(cudaEventRecord(done[k & 1], s));
+    };
+    issue(0);
+    for (size_t k = 0; k < n_chunks; k++) {
+        if (k + 1 < n_chunks) issue(k + 1);
+        CUDA_CHECK(cudaEventSynchronize(done[k & 1]));
+        const size_t r0 = k * rows_per_chunk, nr = std::min(rows_per_chunk, rows - r0);
+        for (size_t r = 0; r < nr; r++) std::memcpy(dst + (r0 + r) * pitch, stage[k & 1] + r * n, width);
+    }
 }
 
 void get_results(lsmc_ctx* c, lsmc_results* r) {
@@ -954,6 +1006,7 @@ void get_results(lsmc_ctx* c, lsmc_results* r) {
         const size_t pitch = c->out_pitch > 0 ? (size_t)c->out_pitch : (size_t)c->N;
         CUDA_CHECK(cudaMemcpy2D(r->decision_index + c->out_col0, pitch, c->decisions.p, (size_t)c->Npad, (size_t)c->N, pl.P - 1, cudaMemcpyDeviceToHost));
     }
+    if (c->export_pending) { CUDA_CHECK(cudaStreamSynchronize(c->stream)); c->export_pending = false; }
 }
 
 }  // namespace
@@ -1206,6 +1259,14 @@ int lsmc_calculate(lsmc_ctx* ctx, const lsmc_problem* problem, const lsmc_rng* r
     return calculate_impl(ctx, problem, regression_rng, valuation_rng, progress, user, results, nullptr);
 }
 
+int lsmc_host_alloc(size_t bytes, void** out) {
+    if (!out) return LSMC_EINVAL;
+    *out = nullptr;
+    return guarded(nullptr, [&] { CUDA_CHECK(cudaHostAlloc(out, std::max<size_t>(bytes, 1), cudaHostAllocPortable)); });
+}
+
+void lsmc_host_free(void* p) { if (p) cudaFreeHost(p); }
+
 int lsmc_intrinsic(const lsmc_problem* problem, double* npv, double* profile) {
     return guarded(nullptr, [&] {
         require(problem != nullptr && npv != nullptr, LSMC_EINVAL, "problem or npv is null");
@@ -1255,10 +1316,11 @@ int lsmc_get_sim_panel(lsmc_ctx* ctx, int set, int factor, double* out) {
         require(factor >= -1 && factor < pl.F, LSMC_EINVAL, "bad factor index");
         require(ctx->out_pitch == 0, LSMC_EINVAL, "lsmc_get_sim_panel is a single-context call");
         CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
-        if (factor < 0) { copy_panel(ctx, out, ctx->spot[set].p, pl.S); return; }
+        if (factor < 0) { copy_panel(ctx, out, ctx->spot[set].p, pl.S); CUDA_CHECK(cudaStreamSynchronize(ctx->stream)); ctx->export_pending = false; return; }
         require(ctx->fac_set == set, LSMC_EINVAL, "the factors of this set were overwritten by the other simulation set");
         for (int j = 0; j < pl.S; j++)
             copy_panel(ctx, out + (size_t)j * ctx->N, ctx->fac.p + ((size_t)j * pl.F + factor) * ctx->Npad, 1);
+        CUDA_CHECK(cudaStreamSynchronize(ctx->stream)); ctx->export_pending = false;
     });
 }
 
@@ -1286,6 +1348,7 @@ int lsmc_debug_get_values(lsmc_ctx* ctx, int period, double* out) {
     return guarded(ctx, [&] {
         require(ctx->backward_done && ctx->keep_values && ctx->Vall.p && period >= 0 && period < ctx->plan.P && out, LSMC_EINVAL, "values were not kept");
         copy_panel(ctx, out, ctx->Vall.p + (size_t)period * ctx->plan.max_grid * ctx->Npad, ctx->plan.grid_size(period));
+        CUDA_CHECK(cudaStreamSynchronize(ctx->stream)); ctx->export_pending = false;
     });
 }
 

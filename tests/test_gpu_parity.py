@@ -83,6 +83,16 @@ def step_ratchet_storage():
                         terminal_storage_npv=lambda price, inventory: 0.0)
 
 
+def polynomial_ratchet_storage():
+    """Rates that are polynomials in the inventory (PolynomialInjectWithdrawConstraint.cs:66-85; C# builder only): cubic in the
+    first table, quadratic in the second; the backward inventory-space sweep needs the bound solver near the end (:87-156)."""
+    ratchets = [
+        (STORAGE_START, [(0.0, -30.0, 25.0), (500.0, -36.0, 21.0), (1000.0, -38.0, 19.5), (1400.0, -39.0, 19.0)]),
+        ("2020-02-01", [(0.0, -28.0, 26.0), (700.0, -33.0, 22.0), (1400.0, -35.0, 20.5)]),
+    ]
+    return CmdtyStorage("D", STORAGE_START, STORAGE_END, 1.25, 0.93, ratchets=ratchets, ratchet_interp=RatchetInterp.POLYNOMIAL)
+
+
 def inventory_cost_storage():
     """Non-zero per-unit inventory cost (CmdtyStorage.cs:544-567, LSV.cs:241-242): the kInvc variants of the sweeps."""
     return CmdtyStorage("D", STORAGE_START, STORAGE_END, 1.25, 0.93, min_inventory=0.0, max_inventory=52_500.0,
@@ -98,6 +108,7 @@ CASES = {
     "c4_five_factor_k16_tp40": lambda: build_config("c4", num_sims=600, end="2021-07-01", basis=FIVE_FACTOR_K16),
     "reference_fixture_step_ratchets": lambda: reference_problem(storage=step_ratchet_storage(), num_sims=768, numerical_tolerance=1e-9),
     "inventory_cost": lambda: reference_problem(storage=inventory_cost_storage(), num_sims=512),
+    "polynomial_ratchets": lambda: reference_problem(storage=polynomial_ratchet_storage(), num_sims=640, inventory=300.0, numerical_tolerance=1e-9),
     "c1_readme_simple_3f": lambda: build_config("c1", num_sims=1000),
     "c2_one_factor": lambda: build_config("c2", num_sims=1536),
     "c3_ratchets_losses_3f": lambda: build_config("c3", num_sims=1024),
@@ -316,6 +327,23 @@ def test_forward_streaming_and_straight_line_kernels_equal_the_bisecting_kernel(
         assert rel_err(fast.npv, slow.npv) < 1e-13   # partition of the sums differs
         assert rel_err(fast.deltas, slow.deltas) < 1e-12 and rel_err(fast.profile, slow.profile) < 1e-12
         assert rel_err(fast.trigger_summary, slow.trigger_summary) < 1e-9
+
+
+def test_panel_export_paths_agree(ctx):
+    """The per-sim panels through the three export paths of lsmc_get_results — page-locked destination (copy engine, all
+    panels in flight), pageable destination above the staging threshold (two 32 MB page-locked chunks) and below it —
+    are the same bytes."""
+    pb = build_config("c3", num_sims=30_000)                       # 366 x 30 000 doubles = 88 MB per panel: three staging chunks
+    names = ("inventory", "inject_withdraw", "pv", "spot_valuation", "net_volume")
+    pageable = ctx.calculate(pb, Rng.philox(11), Rng.philox(22), panels=names)
+    pinned = _abi.Results(pb.n_periods, pb.n_sim_periods, 30_000, panels=names, pinned=True)
+    ctx.calculate(pb, Rng.philox(11), Rng.philox(22), results=pinned)
+    for name in names:
+        assert np.array_equal(getattr(pinned, name), getattr(pageable, name)), name
+    assert np.array_equal(pinned.pv_by_sim, pageable.pv_by_sim)
+    assert pinned.pv.sum(axis=0) == pytest.approx(pinned.pv_by_sim, rel=1e-12)
+    small = ctx.calculate(build_config("c3", num_sims=300), Rng.philox(11), Rng.philox(22), panels=names)   # below the staging threshold
+    assert small.pv.sum(axis=0) == pytest.approx(small.pv_by_sim, rel=1e-12)
 
 
 def test_discounted_deltas_identity(ctx):   # LSMCTest:846-869

@@ -292,3 +292,51 @@ def test_det_exp_accuracy():
             assert got == ref or got < 1e-300 or (x > 709.0 and math.isinf(got))
         else:
             assert abs(got / ref - 1.0) < 4e-16
+
+
+# ---- PolynomialInjectWithdrawConstraint (PolynomialInjectWithdrawConstraint.cs:66-156; C# builder only) ------------------------
+def _polynomial_problem(rows, **kw):
+    from storage_b200 import CmdtyStorage, RatchetInterp
+    from fixtures import reference_problem, STORAGE_START, STORAGE_END
+    storage = CmdtyStorage("D", STORAGE_START, STORAGE_END, 1.25, 0.93, ratchets=[(STORAGE_START, rows)],
+                           ratchet_interp=RatchetInterp.POLYNOMIAL)
+    return reference_problem(storage=storage, num_sims=8, numerical_tolerance=1e-9, **kw), storage
+
+
+def test_polynomial_constraint_passes_through_its_pillars_and_is_evaluated_by_horner():
+    rows = [(0.0, -30.0, 25.0), (500.0, -36.0, 21.0), (1000.0, -38.0, 19.5), (1400.0, -39.0, 19.0)]
+    pb, storage = _polynomial_problem(rows, inventory=300.0)
+    from storage_b200._abi import CONSTRAINT_POLYNOMIAL
+    assert list(pb.constraint_kind) == [CONSTRAINT_POLYNOMIAL] and list(pb.constraint_count) == [4]
+    for inv, lo, hi in rows:     # exact-degree fit: the polynomial interpolates the pillars (Fit.Polynomial at order n - 1)
+        rmin, rmax = oracle.inject_withdraw_range(pb, 0, inv)
+        assert rmin == pytest.approx(lo, abs=1e-6) and rmax == pytest.approx(hi, abs=1e-6)
+    coef_lo, coef_hi = pb.pillar_min_rate, pb.pillar_max_rate
+    for inv in (123.4, 777.0, 1399.0):   # Polynomial.Evaluate: Horner, each multiply and add rounded
+        want_lo, want_hi = coef_lo[-1], coef_hi[-1]
+        for k in (2, 1, 0):
+            want_lo = want_lo * inv + coef_lo[k]
+            want_hi = want_hi * inv + coef_hi[k]
+        assert oracle.inject_withdraw_range(pb, 0, inv) == (want_lo, want_hi)
+        host = storage.inject_withdraw_range(pb.periods[0], inv)
+        assert (host.min_inject_withdraw_rate, host.max_inject_withdraw_rate) == (want_lo, want_hi)
+
+
+def test_polynomial_table_with_two_equal_rows_collapses_to_constant():   # CmdtyStorageBuilderExtensions.cs:163-171
+    pb, _ = _polynomial_problem([(0.0, -20.0, 15.0), (1000.0, -20.0, 15.0)], inventory=100.0)
+    from storage_b200._abi import CONSTRAINT_CONSTANT
+    assert list(pb.constraint_kind) == [CONSTRAINT_CONSTANT]
+    assert oracle.inject_withdraw_range(pb, 3, 400.0) == (-20.0, 15.0)
+
+
+def test_polynomial_inventory_space_bounds_solve_the_reachability_equation():   # Polynomial…cs:87-156
+    rows = [(0.0, -30.0, 25.0), (500.0, -36.0, 21.0), (1000.0, -38.0, 19.5), (1400.0, -39.0, 19.0)]
+    pb, _ = _polynomial_problem(rows, inventory=300.0)
+    # next period's space [0, 100]: from 1400 one cannot get down to 100 in a day -> the upper bound x solves x + rmin(x) = 100
+    upper, lower = oracle.constraint_bounds(pb, 5, 0.0, 100.0)
+    rmin, _ = oracle.inject_withdraw_range(pb, 5, upper)
+    assert upper + rmin == pytest.approx(100.0, abs=1e-9) and lower == 0.0
+    # next period's space [1350, 1400]: the lower bound x solves x + rmax(x) = 1350
+    upper, lower = oracle.constraint_bounds(pb, 5, 1350.0, 1400.0)
+    _, rmax = oracle.inject_withdraw_range(pb, 5, lower)
+    assert lower + rmax == pytest.approx(1350.0, abs=1e-9) and upper == 1400.0
