@@ -39,7 +39,7 @@ struct FinalParams {
 // the sizes already granted are cached under a mutex, so contexts on several GPUs (or several host threads) each get it.
 cudaError_t ensure_dynamic_smem(const void* kernel, size_t bytes);
 
-bool choose_sweep_shape(int max_grid, int K, int F, int MT, int* TP, int* nbuf);
+bool choose_sweep_shape(int max_grid, int K, int F, int MT, int n_prod, int* TP, int* nbuf);
 int sweep_max_items();
 int precond_rows(int K, int64_t N);
 void launch_precond(const PrecondParams& q, cudaStream_t stream);

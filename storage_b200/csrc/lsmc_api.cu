@@ -388,7 +388,7 @@ void set_problem(lsmc_ctx* c, const lsmc_problem* problem) {
     c->ldb = (pl.K + 3) & ~3;
     require(pl.basis.n_nodes <= kMaxNodes && (int)pl.basis.ops.size() <= kMaxOps, LSMC_EUNSUPPORTED, "basis functions need too many product nodes");
     require(pl.max_dec <= 16, LSMC_EUNSUPPORTED, "extra_decisions above 6 is not supported on the device path");
-    require(choose_sweep_shape(pl.max_grid, pl.K, pl.F, c->MT, &c->TP, &c->nbuf), LSMC_EUNSUPPORTED,
+    require(choose_sweep_shape(pl.max_grid, pl.K, pl.F, c->MT, (int)pl.basis.ops.size(), &c->TP, &c->nbuf), LSMC_EUNSUPPORTED,
             "inventory grid / basis too large for the sweep kernel's shared memory");
     require((pl.max_grid + 7) / 8 + c->MT <= sweep_max_items(), LSMC_EUNSUPPORTED, "inventory grid has too many points for the sweep kernel (about 200 at most)");
     const int64_t n_tiles = (c->N + c->TP - 1) / c->TP;
@@ -659,8 +659,18 @@ void backward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
             tp.peers = c->peer.view; tp.error_flag = c->error_flag.p;
             const int blocks = tail_blocks(n_elem, q.G, c->num_sms);
             c->peer.next(blocks, &tp.parity, &tp.target);
+            static const bool tail_trace = getenv("LSMC_TAIL_TRACE") != nullptr;   // development: phase stamps of one mid-horizon tail
+            DevBuf<long long> tail_tr;
+            if (tail_trace && p == P / 2) { tail_tr.alloc(8); CUDA_CHECK(cudaMemsetAsync(tail_tr.p, 0, 64, s)); tp.trace = tail_tr.p; }
             launch_tail(tp, blocks, s);
             c->tm.kernel_launches++;
+            if (tp.trace) {
+                long long h[8];
+                CUDA_CHECK(cudaMemcpyAsync(h, tail_tr.p, 64, cudaMemcpyDeviceToHost, s));
+                CUDA_CHECK(cudaStreamSynchronize(s));
+                fprintf(stderr, "tail trace (ns): reduce %lld, barrier %lld, stage %lld, factor %lld, solve+store %lld, total %lld\n", h[1] - h[0], h[2] - h[1],
+                        h[3] - h[2], h[4] - h[3], h[6] - h[4], h[6] - h[0]);
+            }
         } else {
             launch_reduce_partials(c->partial.p, n_parts, n_elem, c->reduced.p, s);
             c->tm.kernel_launches++;

@@ -169,8 +169,10 @@ __device__ __forceinline__ void solve_cta(const SolveParams& sp, const Red& red,
 // instead of K^2 dependent operations of one thread.  CTA-wide call; warp w takes the right-hand sides
 // col0 + w * col_step, col0 + (w + nwarps) * col_step, ...
 template <int R, class Red>   // R = rows per lane: 1 (K <= 32) or 2 (K <= 64)
-__device__ __forceinline__ void solve_cta_warps(const SolveParams& sp, const Red& red, double* sm, int* dropped, const int col0, const int col_step) {
+__device__ __forceinline__ void solve_cta_warps(const SolveParams& sp, const Red& red, double* sm, int* dropped, const int col0, const int col_step,
+                                                long long* tr = nullptr) {
     if (!solve_stage(sp, red, sm, dropped, col0, col_step)) return;
+    if (tr) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(tr[3]));
     const int K = sp.K, G = sp.G, lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
     const double* A = sm;
     const double* Graw = A + K * K;
@@ -183,6 +185,7 @@ __device__ __forceinline__ void solve_cta_warps(const SolveParams& sp, const Red
 #pragma unroll
     for (int q = 0; q < R; q++) { const int k = lane + 32 * q; rhs[q] = (k < K && i_first < G) ? red(k, i_first) : 0.0; }
     solve_factor(sp, sm, dropped);
+    if (tr) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(tr[4]));
     for (int i = i_first; i < G; i += nwarps * col_step) {
         if (i != i_first) {
 #pragma unroll

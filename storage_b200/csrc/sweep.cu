@@ -57,10 +57,10 @@ constexpr int kWorkers = 15;
 // the decision loop conflict-free), LDX = TP + 4 for the design rows read as DMMA B operands, LDB for beta rows.
 struct SweepSmem {
     int LD, LDX, LDB, GnP, Kp4, nbuf, raw_rows;
-    size_t vn, raw, c, xp, xm, xt, beta, t, total;   // offsets in doubles
+    size_t vn, raw, c, xp, xm, xt, beta, t, nodes, total;   // offsets in doubles
 };
 
-__host__ __device__ inline SweepSmem sweep_layout(int TP, int Gn, int K, int F, int MT, int nbuf) {
+__host__ __device__ inline SweepSmem sweep_layout(int TP, int Gn, int K, int F, int MT, int nbuf, int n_prod) {
     SweepSmem L;
     L.LD = TP; L.LDX = TP + 4; L.nbuf = nbuf;
     L.GnP = (Gn + 7) & ~7;
@@ -76,6 +76,7 @@ __host__ __device__ inline SweepSmem sweep_layout(int TP, int Gn, int K, int F, 
     L.xt = o;    o += (size_t)8 * MT * L.LD;                 // preconditioned rows x~ (rows >= K stay zero)
     L.beta = o;  o += (size_t)L.GnP * L.LDB;
     L.t = o;     o += (size_t)K * K;
+    L.nodes = o; o += (size_t)2 * n_prod * L.LD;                 // product nodes of the basis program, both periods
     L.total = o;
     return L;
 }
@@ -239,7 +240,8 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
     const int g = lane >> 2, t = lane & 3;
     const BasisDev* __restrict__ bd = q.basis;
     const int K = q.K, F = q.F;
-    const SweepSmem L = sweep_layout(TP, q.Gn, K, F, MT, nbuf);
+    const int n_prod = bd->n_ops;
+    const SweepSmem L = sweep_layout(TP, q.Gn, K, F, MT, nbuf, n_prod);
     constexpr int LD = TP, LDX = TP + 4;
     const int LDB = L.LDB, GnP = L.GnP, Kp4 = L.Kp4;
     double* const sVn = smem + L.vn;
@@ -250,8 +252,10 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
     double* const sXT = smem + L.xt;
     double* const sBeta = smem + L.beta;
     double* const sT = smem + L.t;
+    double* const sNodes = smem + L.nodes;
     __shared__ uint64_t s_full[2];
-    __shared__ int8_t sPow[64][1 + kMaxFactors];
+    __shared__ int sWaveEnd[kMaxOps + 1], sNWaves;   // product nodes in waves of mutually independent multiplies
+    __shared__ int16_t sOpD[kMaxOps], sOpA[kMaxOps], sOpB[kMaxOps], sNodeOfBasis[64];
 
     const int NT = (q.G + 7) >> 3;                        // decision items (8 grid rows each)
     const int n_items = q.accum_mode ? NT + MT : NT;      // + X~^T X~ items
@@ -262,9 +266,18 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
     const bool accum = q.accum_mode != 0;
 
     // ---- one-time staging ----
-    for (int k = tid; k < 64; k += blockDim.x) {
-        sPow[k][0] = (k < K) ? bd->spot_pow[k] : (int8_t)0;
-        for (int f = 0; f < kMaxFactors; f++) sPow[k][1 + f] = (k < K && f < F) ? bd->fac_pow[k][f] : (int8_t)0;
+    for (int k = tid; k < 64; k += blockDim.x) sNodeOfBasis[k] = (k < K) ? bd->node_of_basis[k] : (int16_t)0;
+    for (int o = tid; o < n_prod; o += blockDim.x) { const BasisOpDev op = bd->ops[o]; sOpD[o] = op.dst; sOpA[o] = op.a; sOpB[o] = op.b; }
+    if (tid == 0) {   // a wave ends before the first node that reads a node of the same wave (host_plan.cpp compile_basis emits operands first)
+        int nw = 0, w0 = 0;
+        for (int o = 0; o < n_prod; o++) {
+            const BasisOpDev op = bd->ops[o];
+            bool dep = false;
+            for (int e = w0; e < o; e++) dep = dep || bd->ops[e].dst == op.a || bd->ops[e].dst == op.b;
+            if (dep) { sWaveEnd[nw++] = o; w0 = o; }
+        }
+        if (n_prod > 0) sWaveEnd[nw++] = n_prod;
+        sNWaves = nw;
     }
     for (size_t i = tid; i < L.total; i += blockDim.x) smem[i] = 0.0;
     __syncthreads();
@@ -355,24 +368,40 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
         if (any_copy) mbar_wait(&s_full[b], (uint32_t)((it / nbuf) & 1));   // this tile's rows have landed
         if (!need_sp) for (int path = tid; path < TP; path += blockDim.x) raw[path] = (n0 + path < q.N) ? q.spot_const : 0.0;
         {
+            // The basis program (host_plan.cpp compile_basis: left-to-right product chains, spot first, factors ascending, shared
+            // prefixes computed once — the order BasisFunctions.cs:92-132 and the oracle multiply in): node 0 zero, 1 ones,
+            // 2 spot, 3 + f factor f, then one multiply per product node, wave by wave.
+            auto node_row = [&](int sel, int id) -> const double* {   // sel 0: period p, 1: period p-1
+                if (id >= 3 + F) return sNodes + ((size_t)sel * n_prod + (id - 3 - F)) * LD;
+                return raw + (sel ? (size_t)(F + 1) * LD : 0) + (size_t)(id - 2) * LD;
+            };
+            auto node_value = [&](int sel, int id, int path) -> double {
+                if (id < 2) return id == 1 ? 1.0 : 0.0;
+                if (id == 2 && sel == 0 && !need_sp) return q.spot_const;   // deterministic price of the current period
+                return node_row(sel, id)[path];
+            };
+            const int n_waves = sNWaves;
+            int o0 = 0;
+            for (int w = 0; w < n_waves; w++) {
+                const int o1 = sWaveEnd[w], nw = o1 - o0;
+                for (int e = tid; e < 2 * nw * TP; e += blockDim.x) {
+                    const int sel = e / (nw * TP), r = e - sel * nw * TP, o = o0 + r / TP, path = r % TP;
+                    if (sel == 0 ? !need_fp : !need_m) continue;
+                    const int ia = sOpA[o], ib = sOpB[o];
+                    const double va = node_value(sel, ia, path), vb = node_value(sel, ib, path);
+                    sNodes[((size_t)sel * n_prod + (sOpD[o] - 3 - F)) * LD + path] = mul_rn(va, vb);
+                }
+                o0 = o1;
+                __syncthreads();
+            }
             const int nP = need_fp ? K : 0, nM = need_m ? K : 0;
             for (int e = tid; e < (nP + nM) * TP; e += blockDim.x) {
                 const int row = e / TP, path = e - row * TP;
                 const bool isM = row >= nP;
                 const int k = isM ? row - nP : row;
-                const double* rr = raw + (isM ? (size_t)(F + 1) * LD : 0) + path;
-                // left-to-right product chain: spot first, factors ascending (BasisFunctions.cs:92-132; same order as the oracle)
-                double a = 1.0;
-                bool started = false;
-                for (int v = 0; v <= F; v++) {
-                    const int pw = sPow[k][v];
-                    if (pw > 0) {
-                        const double x = (v == 0 && !isM && !need_sp) ? q.spot_const : rr[(size_t)v * LD];
-                        for (int c = 0; c < pw; c++) { a = started ? mul_rn(a, x) : x; started = true; }
-                    }
-                }
-                if (!started) a = (n0 + path < q.N) ? 1.0 : 0.0;
-                else if (!(n0 + path < q.N)) a = 0.0;
+                const int id = sNodeOfBasis[k];
+                const bool live = n0 + path < q.N;   // columns beyond the last path contribute nothing
+                const double a = live ? node_value(isM ? 1 : 0, id, path) : 0.0;
                 if (isM) sXM[(size_t)k * LD + path] = a; else sXP[(size_t)k * LDX + path] = a;
             }
         }
@@ -380,32 +409,43 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
 
         // ================= phase F1: preconditioned regressors + fitted continuation values =================
         if (q.accum_mode == 1) {
-            for (int e = tid; e < K * TP; e += blockDim.x) {
-                const int j = e / TP, path = e - j * TP;
-                double a = 0.0;
-                for (int i = 0; i <= j; i++) a = fma(sT[i * K + j], sXM[(size_t)i * LD + path], a);
-                sXT[(size_t)j * LD + path] = a;
+            // x~ = T^T x_{p-1} on the FP64 tensor pipe: D[j][path] = sum_i T[i][j] x[i][path]; one (row block, path block) per warp step
+            constexpr int NNT = TP / 8;
+            for (int item = warp; item < MT * NNT; item += kSweepWarps) {
+                const int m = item / NNT, nt = item - m * NNT, j = 8 * m + g;
+                double c0 = 0.0, c1 = 0.0;
+                for (int ks = 0; ks < Kp4; ks += 4) {
+                    const int i = ks + t;
+                    const double av = (i < K && j < K) ? sT[i * K + j] : 0.0;
+                    const double bv = (i < K) ? sXM[(size_t)i * LD + 8 * nt + g] : 0.0;
+                    dmma8x8x4(c0, c1, av, bv);
+                }
+                *reinterpret_cast<double2*>(sXT + (size_t)j * LD + 8 * nt + 2 * t) = make_double2(c0, c1);
             }
         } else if (q.accum_mode == 2) {
             for (int path = tid; path < TP; path += blockDim.x) sXT[path] = (n0 + path < q.N) ? 1.0 : 0.0;
         }
         if (q.mode == 0) {
             if (q.cont_mode == 0) {
-                constexpr int NNT = TP / 8, H0 = (NNT + 1) / 2;
+                // one block of 8 next-grid rows per warp step, all TP / 8 path blocks at once: the coefficient fragment is loaded
+                // once per k-step and feeds independent accumulator chains
+                constexpr int NNT = TP / 8;
                 const int NTn = GnP >> 3;
-                for (int item = warp; item < 2 * NTn; item += kSweepWarps) {
-                    const int mt = item >> 1, half = item & 1;
+                for (int mt = warp; mt < NTn; mt += kSweepWarps) {
                     const double* brow = sBeta + (size_t)(8 * mt + g) * LDB + t;
                     const double* xcol = sXP + (size_t)t * LDX + g;
-                    double* crow = sC + (size_t)(8 * mt + g) * LD + 2 * t;
-                    for (int nt = half ? H0 : 0; nt < (half ? NNT : H0); nt++) {
-                        double c0 = 0.0, c1 = 0.0;
-                        const double* ap = brow;
-                        const double* bp = xcol + 8 * nt;
-#pragma unroll 1
-                        for (int ks = 0; ks < Kp4; ks += 4, ap += 4, bp += 4 * LDX) dmma8x8x4(c0, c1, *ap, *bp);
-                        *reinterpret_cast<double2*>(crow + 8 * nt) = make_double2(c0, c1);
+                    double cf[NNT][2];
+#pragma unroll
+                    for (int nt = 0; nt < NNT; nt++) cf[nt][0] = cf[nt][1] = 0.0;
+#pragma unroll 2
+                    for (int ks = 0; ks < Kp4; ks += 4) {
+                        const double av = brow[ks];
+#pragma unroll
+                        for (int nt = 0; nt < NNT; nt++) dmma8x8x4(cf[nt][0], cf[nt][1], av, xcol[(size_t)ks * LDX + 8 * nt]);
                     }
+                    double* crow = sC + (size_t)(8 * mt + g) * LD + 2 * t;
+#pragma unroll
+                    for (int nt = 0; nt < NNT; nt++) *reinterpret_cast<double2*>(crow + 8 * nt) = make_double2(cf[nt][0], cf[nt][1]);
                 }
             } else {
                 for (int i = tid; i < q.Gn * TP; i += blockDim.x) {
@@ -477,17 +517,17 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
 // ------------------------------------------------------------------------------------------------
 // Launch configuration
 // ------------------------------------------------------------------------------------------------
-static size_t layout_bytes(int TP, int Gn, int K, int F, int MT, int nbuf) {
-    return sweep_layout(TP, Gn, K, F, MT, nbuf).total * sizeof(double);
+static size_t layout_bytes(int TP, int Gn, int K, int F, int MT, int nbuf, int n_prod) {
+    return sweep_layout(TP, Gn, K, F, MT, nbuf, n_prod).total * sizeof(double);
 }
 
 // Largest tile that fits the 227 KB of an SM, double-buffered when possible.
-bool choose_sweep_shape(int max_grid, int K, int F, int MT, int* TP, int* nbuf) {
+bool choose_sweep_shape(int max_grid, int K, int F, int MT, int n_prod, int* TP, int* nbuf) {
     const size_t limit = 224 * 1024;
     const int tps[2] = {56, 24};
     for (int nb = 2; nb >= 1; nb--)
         for (int tp : tps)
-            if (layout_bytes(tp, max_grid, K, F, MT, nb) <= limit) { *TP = tp; *nbuf = nb; return true; }
+            if (layout_bytes(tp, max_grid, K, F, MT, nb, n_prod) <= limit) { *TP = tp; *nbuf = nb; return true; }
     return false;
 }
 
@@ -524,7 +564,7 @@ cudaError_t launch_sweep(SweepParams& q, const SweepConfig& cfg, cudaStream_t st
     if (n_items > 2 * kWorkers) return cudaErrorInvalidValue;
     const int NTW = n_items <= kWorkers ? 1 : 2;
     q.ncols = 8 * (NT + MT);
-    const size_t smem = layout_bytes(cfg.TP, q.Gn, q.K, q.F, MT, cfg.nbuf);
+    const size_t smem = layout_bytes(cfg.TP, q.Gn, q.K, q.F, MT, cfg.nbuf, cfg.n_nodes - 3 - q.F);
     if (cfg.TP == 56) return launch_sweep_tp<56>(q, MT, NTW, cfg.blocks, smem, cfg.nbuf, stream);
 #ifdef LSMC_FAST_BUILD
     return cudaErrorInvalidValue;

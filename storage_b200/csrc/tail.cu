@@ -37,7 +37,7 @@ __device__ __forceinline__ void arrive_and_wait(const PeerView& pv, unsigned lon
         while (ld_acquire_sys(mine) < target) {
             if (*reinterpret_cast<volatile int*>(error_flag) == kPeerTimeout) break;
             if (clock64() - t0 > 4000000000LL) { atomicExch(error_flag, kPeerTimeout); break; }
-            __nanosleep(64);
+            __nanosleep(20);
         }
     }
     __syncthreads();
@@ -55,10 +55,14 @@ struct SlotRed {
     __device__ __forceinline__ double operator()(int k, int col) const { return at(k * ld + col); }
 };
 
+__device__ __forceinline__ long long gtimer() { long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+
 template <int R>   // rows of the system per lane: 1 (K <= 32) or 2 (K <= 64)
 __global__ void __launch_bounds__(kTailThreads) tail_kernel(const TailParams tp) {
     extern __shared__ double tsm[];
     __shared__ int dropped[64];
+    long long* tr = (tp.trace && blockIdx.x == 0 && threadIdx.x == 0) ? tp.trace : nullptr;
+    if (tr) tr[0] = gtimer();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = kTailThreads / 32;
     const PeerView& pv = tp.peers;
     const size_t par_off = (size_t)tp.parity * pv.world * kPeerSlotDoubles;
@@ -89,11 +93,16 @@ __global__ void __launch_bounds__(kTailThreads) tail_kernel(const TailParams tp)
         }
     }
     // ---- 2: exchange ----
+    if (tr) tr[1] = gtimer();
     arrive_and_wait(pv, tp.target, tp.error_flag);
+    if (tr) tr[2] = gtimer();
     const SlotRed red{pv.slots[pv.rank] + par_off, pv.world, tp.solve.ncols};
     if (blockIdx.x == 0 && (int)threadIdx.x < tp.n_out) tp.total_out[threadIdx.x] = red.at(threadIdx.x);
     // ---- 3: solve ----
-    if (tp.do_solve) solve_cta_warps<R>(tp.solve, red, tsm, dropped, blockIdx.x, gridDim.x);
+    // (A register-resident variant — rows of L, L^T, T per lane, fully unrolled for K <= 16 — was measured and dropped: 34 us
+    //  against 21 us; a kernel that runs its straight-line code once per launch pays for every instruction fetch.)
+    if (tp.do_solve) solve_cta_warps<R>(tp.solve, red, tsm, dropped, blockIdx.x, gridDim.x, tr);
+    if (tr) tr[6] = gtimer();
 }
 
 __global__ void __launch_bounds__(256) peer_small_kernel(const PeerSmallParams pp) {
