@@ -446,6 +446,42 @@ void compile_basis(const lsmc_problem& pb, BasisProgram& prog) {
 
 }  // namespace
 
+void compile_row_program(const BasisProgram& prog, int K, int F, RowProgram& rows) {
+    struct Loc { int8_t region; int16_t row; };
+    const int n_base = 3 + F;
+    std::vector<Loc> loc(prog.n_nodes);
+    std::vector<int> level(prog.n_nodes, 0);
+    loc[0] = {kRowConst, 0};
+    loc[1] = {kRowConst, 1};
+    for (int v = 2; v < n_base; v++) loc[v] = {kRowRaw, (int16_t)(v - 2)};
+    rows.n_scratch = 0;
+    for (int node = n_base; node < prog.n_nodes; node++) {
+        int k_first = -1;
+        for (int k = 0; k < K && k_first < 0; k++) if (prog.node_of_basis[k] == node) k_first = k;
+        if (k_first >= 0) loc[node] = {kRowBasis, (int16_t)k_first};
+        else loc[node] = {kRowScratch, (int16_t)rows.n_scratch++};
+    }
+    struct Pending { RowOp op; int level; };
+    std::vector<Pending> pending;
+    for (const BasisOp& o : prog.ops) {   // operands precede results in prog.ops (compile_basis)
+        level[o.dst] = 1 + std::max(level[o.a], level[o.b]);
+        pending.push_back({RowOp{loc[o.a].region, loc[o.b].region, loc[o.dst].region, 0, loc[o.a].row, loc[o.b].row, loc[o.dst].row, 0}, level[o.dst]});
+    }
+    for (int k = 0; k < K; k++) {
+        const int node = prog.node_of_basis[k];
+        if (loc[node].region == kRowBasis && loc[node].row == k) continue;   // produced in place
+        pending.push_back({RowOp{loc[node].region, kRowConst, kRowBasis, 0, loc[node].row, 1, (int16_t)k, 0}, level[node] + 1});
+    }
+    std::stable_sort(pending.begin(), pending.end(), [](const Pending& x, const Pending& y) { return x.level < y.level; });
+    rows.ops.clear();
+    rows.wave_end.clear();
+    for (size_t i = 0; i < pending.size(); i++) {
+        if (i > 0 && pending[i].level != pending[i - 1].level) rows.wave_end.push_back((int16_t)i);
+        rows.ops.push_back(pending[i].op);
+    }
+    if (!pending.empty()) rows.wave_end.push_back((int16_t)pending.size());
+}
+
 void build_plan(const lsmc_problem& problem, Plan& plan) {
     plan.problem.assign(problem);
     const lsmc_problem& pb = plan.problem.pb;
@@ -524,6 +560,7 @@ void build_plan(const lsmc_problem& problem, Plan& plan) {
 
     sim_coefficients(pb, plan.s0, plan.sim);
     compile_basis(pb, plan.basis);
+    compile_row_program(plan.basis, pb.n_basis, pb.n_factors, plan.basis_rows);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -27,6 +27,19 @@ struct BasisProgram {
     std::vector<int16_t> node_of_basis;   // [K]
 };
 
+// The same program addressed by shared-memory ROWS, for the general sweep (sweep.cu phase F0): every operand and result of
+// a multiply is a row of one of four regions, so that a product node which IS a basis function is written straight into
+// its design-matrix row.  Copies (basis functions that are a raw variable, the constant, or a second name of a node) are
+// multiplies by the ones row: x * 1.0 is exact.  Ops are sorted into waves of mutually independent multiplies.
+enum RowRegion : int8_t { kRowConst = 0 /* row 0 zeros, row 1 ones */, kRowRaw = 1 /* 0 spot, 1 + f factor f */, kRowBasis = 2, kRowScratch = 3 };
+struct RowOp { int8_t ra, rb, rd, pad; int16_t a, b, d, pad2; };
+struct RowProgram {
+    std::vector<RowOp> ops;          // wave after wave
+    std::vector<int16_t> wave_end;   // [n_waves] one past the last op of each wave
+    int n_scratch = 0;               // rows of product nodes that are not basis functions
+};
+void compile_row_program(const BasisProgram& prog, int K, int F, RowProgram& rows);
+
 // Decision table entry for one (period, grid point, decision): LSV.cs:249-300.
 struct DecisionTables {
     // per (period p < P-1, grid index i): offsets via row_offset[p] + i
@@ -66,6 +79,7 @@ struct Plan {
     DecisionTables tables;
     SimCoefficients sim;
     BasisProgram basis;
+    RowProgram basis_rows;
 
     int grid_size(int p) const { return grid_offset[p + 1] - grid_offset[p]; }
     const double* grid_of(int p) const { return grid.data() + grid_offset[p]; }

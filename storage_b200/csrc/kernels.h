@@ -8,11 +8,12 @@
 namespace lsmc {
 
 struct SweepConfig {
-    int TP;        // paths per tile (56 or 24)
+    int TP;        // paths per tile (56, 40 or 24)
     int MT;        // basis m-tiles: 1, 2, 4 or 8 (8*MT >= K)
     int blocks;    // persistent CTAs
-    int n_nodes;   // basis-program nodes
+    int n_scratch; // rows of basis-program nodes that are not basis functions (host_plan.h RowProgram)
     int nbuf;      // shared-memory buffers for the staged V_next tile (2 = prefetch the next tile)
+    int n_rowops;  // multiplies of the row program
 };
 
 struct SolveParams {
@@ -39,7 +40,7 @@ struct FinalParams {
 // the sizes already granted are cached under a mutex, so contexts on several GPUs (or several host threads) each get it.
 cudaError_t ensure_dynamic_smem(const void* kernel, size_t bytes);
 
-bool choose_sweep_shape(int max_grid, int K, int F, int MT, int n_prod, int* TP, int* nbuf);
+bool choose_sweep_shape(int max_grid, int K, int F, int MT, int n_scratch, int n_rowops, int* TP, int* nbuf);
 int sweep_max_items();
 int precond_rows(int K, int64_t N);
 void launch_precond(const PrecondParams& q, cudaStream_t stream);

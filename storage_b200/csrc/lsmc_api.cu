@@ -388,7 +388,7 @@ void set_problem(lsmc_ctx* c, const lsmc_problem* problem) {
     c->ldb = (pl.K + 3) & ~3;
     require(pl.basis.n_nodes <= kMaxNodes && (int)pl.basis.ops.size() <= kMaxOps, LSMC_EUNSUPPORTED, "basis functions need too many product nodes");
     require(pl.max_dec <= 16, LSMC_EUNSUPPORTED, "extra_decisions above 6 is not supported on the device path");
-    require(choose_sweep_shape(pl.max_grid, pl.K, pl.F, c->MT, (int)pl.basis.ops.size(), &c->TP, &c->nbuf), LSMC_EUNSUPPORTED,
+    require(choose_sweep_shape(pl.max_grid, pl.K, pl.F, c->MT, pl.basis_rows.n_scratch, (int)pl.basis_rows.ops.size(), &c->TP, &c->nbuf), LSMC_EUNSUPPORTED,
             "inventory grid / basis too large for the sweep kernel's shared memory");
     require((pl.max_grid + 7) / 8 + c->MT <= sweep_max_items(), LSMC_EUNSUPPORTED, "inventory grid has too many points for the sweep kernel (about 200 at most)");
     const int64_t n_tiles = (c->N + c->TP - 1) / c->TP;
@@ -486,6 +486,12 @@ void set_problem(lsmc_ctx* c, const lsmc_problem* problem) {
                 b.fac_pow[k][f] = (int8_t)pb.factor_power[k * pl.F + f];
             }
         }
+        const RowProgram& rp = pl.basis_rows;
+        require((int)rp.ops.size() <= kMaxRowOps, LSMC_EUNSUPPORTED, "basis functions need too many product nodes");
+        b.n_rowops = (int)rp.ops.size(); b.n_rowwaves = (int)rp.wave_end.size(); b.n_scratch = rp.n_scratch;
+        for (size_t i = 0; i < rp.wave_end.size(); i++) b.rowwave_end[i] = rp.wave_end[i];
+        for (size_t i = 0; i < rp.ops.size(); i++)
+            b.rowops[i] = RowOpDev{rp.ops[i].ra, rp.ops[i].rb, rp.ops[i].rd, 0, rp.ops[i].a, rp.ops[i].b, rp.ops[i].d, 0};
         c->basis.upload(hb, s);
         CUDA_CHECK(cudaStreamSynchronize(s));   // hb goes out of scope
     }
@@ -563,7 +569,7 @@ void backward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
     const int P = pl.P, s0 = pl.s0, F = pl.F, D = pl.max_dec;
     const size_t Np = (size_t)c->Npad;
     cudaStream_t s = c->stream;
-    SweepConfig cfg{c->TP, c->MT, c->sweep_blocks, pl.basis.n_nodes, c->nbuf};
+    SweepConfig cfg{c->TP, c->MT, c->sweep_blocks, pl.basis_rows.n_scratch, c->nbuf, (int)pl.basis_rows.ops.size()};
     CUDA_CHECK(cudaEventRecord(c->event(2), s));
     c->tm.backward_sweep_launches = 0;
     c->tm.sweep_bytes = 0.0;

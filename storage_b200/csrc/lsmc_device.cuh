@@ -81,6 +81,8 @@ __device__ __forceinline__ void dmma8x8x4(double& d0, double& d1, double a, doub
 }
 
 struct BasisOpDev { int16_t dst, a, b, pad; };
+struct RowOpDev { int8_t ra, rb, rd, pad; int16_t a, b, d, pad2; };   // host_plan.h RowOp: (region, row) of the operands and the result
+constexpr int kMaxRowOps = kMaxOps + 64;
 
 // Compiled basis (host_plan.h BasisProgram) + exponents, uploaded once per problem.
 struct BasisDev {
@@ -89,6 +91,10 @@ struct BasisDev {
     int16_t node_of_basis[64];
     int8_t spot_pow[64];                 // exponents (BasisFunctions.cs:92-132), used by the preconditioner kernel
     int8_t fac_pow[64][kMaxFactors];
+    // the same program by shared-memory rows, in waves (host_plan.h RowProgram), for the general sweep
+    int n_rowops, n_rowwaves, n_scratch;
+    int16_t rowwave_end[kMaxRowOps];
+    RowOpDev rowops[kMaxRowOps];
 };
 
 // Per-period regression preconditioner: T = R_sub^-1 (upper triangular, K x K, row-major) from a

@@ -57,10 +57,10 @@ constexpr int kWorkers = 15;
 // the decision loop conflict-free), LDX = TP + 4 for the design rows read as DMMA B operands, LDB for beta rows.
 struct SweepSmem {
     int LD, LDX, LDB, GnP, Kp4, nbuf, raw_rows;
-    size_t vn, raw, c, xp, xm, xt, beta, t, nodes, total;   // offsets in doubles
+    size_t vn, raw, c, xp, xm, xt, beta, t, nodes, cst, ops, total;   // offsets in doubles
 };
 
-__host__ __device__ inline SweepSmem sweep_layout(int TP, int Gn, int K, int F, int MT, int nbuf, int n_prod) {
+__host__ __device__ inline SweepSmem sweep_layout(int TP, int Gn, int K, int F, int MT, int nbuf, int n_scratch, int n_rowops) {
     SweepSmem L;
     L.LD = TP; L.LDX = TP + 4; L.nbuf = nbuf;
     L.GnP = (Gn + 7) & ~7;
@@ -76,7 +76,10 @@ __host__ __device__ inline SweepSmem sweep_layout(int TP, int Gn, int K, int F, 
     L.xt = o;    o += (size_t)8 * MT * L.LD;                 // preconditioned rows x~ (rows >= K stay zero)
     L.beta = o;  o += (size_t)L.GnP * L.LDB;
     L.t = o;     o += (size_t)K * K;
-    L.nodes = o; o += (size_t)2 * n_prod * L.LD;                 // product nodes of the basis program, both periods
+    L.nodes = o; o += (size_t)2 * n_scratch * L.LD;              // product nodes that are not basis functions, both periods
+    L.cst = o;   o += (size_t)2 * L.LD;                          // row 0 zeros, row 1 ones (zero beyond the last path)
+    o = (o + 1) & ~(size_t)1;
+    L.ops = o;   o += (size_t)2 * n_rowops * 2;                  // the row program of both periods as int4 {A, B, D offsets, raw flags}
     L.total = o;
     return L;
 }
@@ -240,8 +243,8 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
     const int g = lane >> 2, t = lane & 3;
     const BasisDev* __restrict__ bd = q.basis;
     const int K = q.K, F = q.F;
-    const int n_prod = bd->n_ops;
-    const SweepSmem L = sweep_layout(TP, q.Gn, K, F, MT, nbuf, n_prod);
+    const int n_rowops = bd->n_rowops, n_scr = bd->n_scratch;
+    const SweepSmem L = sweep_layout(TP, q.Gn, K, F, MT, nbuf, n_scr, n_rowops);
     constexpr int LD = TP, LDX = TP + 4;
     const int LDB = L.LDB, GnP = L.GnP, Kp4 = L.Kp4;
     double* const sVn = smem + L.vn;
@@ -252,10 +255,9 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
     double* const sXT = smem + L.xt;
     double* const sBeta = smem + L.beta;
     double* const sT = smem + L.t;
-    double* const sNodes = smem + L.nodes;
+    int4* const sOp4 = reinterpret_cast<int4*>(smem + L.ops);
     __shared__ uint64_t s_full[2];
-    __shared__ int sWaveEnd[kMaxOps + 1], sNWaves;   // product nodes in waves of mutually independent multiplies
-    __shared__ int16_t sOpD[kMaxOps], sOpA[kMaxOps], sOpB[kMaxOps], sNodeOfBasis[64];
+    __shared__ int16_t sWaveEnd[kMaxRowOps];
 
     const int NT = (q.G + 7) >> 3;                        // decision items (8 grid rows each)
     const int n_items = q.accum_mode ? NT + MT : NT;      // + X~^T X~ items
@@ -266,21 +268,30 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
     const bool accum = q.accum_mode != 0;
 
     // ---- one-time staging ----
-    for (int k = tid; k < 64; k += blockDim.x) sNodeOfBasis[k] = (k < K) ? bd->node_of_basis[k] : (int16_t)0;
-    for (int o = tid; o < n_prod; o += blockDim.x) { const BasisOpDev op = bd->ops[o]; sOpD[o] = op.dst; sOpA[o] = op.a; sOpB[o] = op.b; }
-    if (tid == 0) {   // a wave ends before the first node that reads a node of the same wave (host_plan.cpp compile_basis emits operands first)
-        int nw = 0, w0 = 0;
-        for (int o = 0; o < n_prod; o++) {
-            const BasisOpDev op = bd->ops[o];
-            bool dep = false;
-            for (int e = w0; e < o; e++) dep = dep || bd->ops[e].dst == op.a || bd->ops[e].dst == op.b;
-            if (dep) { sWaveEnd[nw++] = o; w0 = o; }
-        }
-        if (n_prod > 0) sWaveEnd[nw++] = n_prod;
-        sNWaves = nw;
-    }
+    const int n_waves = bd->n_rowwaves;
+    for (int w = tid; w < n_waves; w += blockDim.x) sWaveEnd[w] = bd->rowwave_end[w];
     for (size_t i = tid; i < L.total; i += blockDim.x) smem[i] = 0.0;
     __syncthreads();
+    // The row program (host_plan.cpp compile_row_program) of both periods with shared-memory offsets: per wave the entries of
+    // period p, then those of period p-1.  Operands in the raw rows move with the tile buffer (flags: bit 0 A, bit 1 B).
+    for (int e = tid; e < 2 * n_rowops; e += blockDim.x) {
+        const int sel = e >= n_rowops ? 1 : 0, o = e - sel * n_rowops;
+        int o0 = 0, o1 = 0;
+        for (int w = 0; w < n_waves; w++) { o1 = bd->rowwave_end[w]; if (o < o1) break; o0 = o1; }
+        const RowOpDev op = bd->rowops[o];
+        auto offset = [&](int region, int row) -> int {
+            if (region == 0) return (int)(L.cst + (size_t)row * LD);
+            if (region == 1) return (int)(L.raw + (size_t)(sel * (F + 1) + row) * LD);
+            if (region == 2) return sel ? (int)(L.xm + (size_t)row * LD) : (int)(L.xp + (size_t)row * LDX);
+            return (int)(L.nodes + (size_t)(sel * n_scr + row) * LD);
+        };
+        sOp4[2 * o0 + sel * (o1 - o0) + (o - o0)] =
+            make_int4(offset(op.ra, op.a), offset(op.rb, op.b), offset(op.rd, op.d), (op.ra == 1 ? 1 : 0) | (op.rb == 1 ? 2 : 0));
+    }
+    for (int path = tid; path < TP; path += blockDim.x) {
+        smem[L.cst + LD + path] = 1.0;
+        if (!need_sp) { sRaw[path] = q.spot_const; if (nbuf == 2) sRaw[(size_t)L.raw_rows * LD + path] = q.spot_const; }   // every tile buffer
+    }
     if (need_fp) {
         for (int i = tid; i < q.Gn * Kp4; i += blockDim.x) {
             const int l = i / Kp4, k = i - l * Kp4;
@@ -366,46 +377,34 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
 
         // ================= phase F0: basis monomials of both periods from the raw rows =================
         if (any_copy) mbar_wait(&s_full[b], (uint32_t)((it / nbuf) & 1));   // this tile's rows have landed
-        if (!need_sp) for (int path = tid; path < TP; path += blockDim.x) raw[path] = (n0 + path < q.N) ? q.spot_const : 0.0;
+        if (n0 + TP > q.N) {   // the last tile: columns beyond the last path must contribute nothing
+            for (int path = tid; path < TP; path += blockDim.x) if (n0 + path >= q.N) smem[L.cst + LD + path] = 0.0;
+            for (int e = tid; e < L.raw_rows * TP; e += blockDim.x) {
+                const int r = e / TP, path = e - r * TP;
+                if (n0 + path >= q.N) raw[(size_t)r * LD + path] = 0.0;
+            }
+            __syncthreads();
+        }
         {
             // The basis program (host_plan.cpp compile_basis: left-to-right product chains, spot first, factors ascending, shared
-            // prefixes computed once — the order BasisFunctions.cs:92-132 and the oracle multiply in): node 0 zero, 1 ones,
-            // 2 spot, 3 + f factor f, then one multiply per product node, wave by wave.
-            auto node_row = [&](int sel, int id) -> const double* {   // sel 0: period p, 1: period p-1
-                if (id >= 3 + F) return sNodes + ((size_t)sel * n_prod + (id - 3 - F)) * LD;
-                return raw + (sel ? (size_t)(F + 1) * LD : 0) + (size_t)(id - 2) * LD;
-            };
-            auto node_value = [&](int sel, int id, int path) -> double {
-                if (id < 2) return id == 1 ? 1.0 : 0.0;
-                if (id == 2 && sel == 0 && !need_sp) return q.spot_const;   // deterministic price of the current period
-                return node_row(sel, id)[path];
-            };
-            const int n_waves = sNWaves;
+            // prefixes computed once — the order BasisFunctions.cs:92-132 and the oracle multiply in), one multiply per element,
+            // wave by wave; a node that is a basis function lands in its design-matrix row.
+            const int rb = b * L.raw_rows * LD;
             int o0 = 0;
             for (int w = 0; w < n_waves; w++) {
                 const int o1 = sWaveEnd[w], nw = o1 - o0;
-                for (int e = tid; e < 2 * nw * TP; e += blockDim.x) {
-                    const int sel = e / (nw * TP), r = e - sel * nw * TP, o = o0 + r / TP, path = r % TP;
-                    if (sel == 0 ? !need_fp : !need_m) continue;
-                    const int ia = sOpA[o], ib = sOpB[o];
-                    const double va = node_value(sel, ia, path), vb = node_value(sel, ib, path);
-                    sNodes[((size_t)sel * n_prod + (sOpD[o] - 3 - F)) * LD + path] = mul_rn(va, vb);
+                const int lo = need_fp ? 0 : nw, hi = need_m ? 2 * nw : nw;
+                const int4* ops = sOp4 + 2 * o0 + lo;
+                for (int e = tid; e < (hi - lo) * TP; e += blockDim.x) {
+                    const int idx = e / TP, path = e - idx * TP;
+                    const int4 op = ops[idx];
+                    const double va = smem[op.x + ((op.w & 1) ? rb : 0) + path], vb = smem[op.y + ((op.w & 2) ? rb : 0) + path];
+                    smem[op.z + path] = mul_rn(va, vb);
                 }
                 o0 = o1;
                 __syncthreads();
             }
-            const int nP = need_fp ? K : 0, nM = need_m ? K : 0;
-            for (int e = tid; e < (nP + nM) * TP; e += blockDim.x) {
-                const int row = e / TP, path = e - row * TP;
-                const bool isM = row >= nP;
-                const int k = isM ? row - nP : row;
-                const int id = sNodeOfBasis[k];
-                const bool live = n0 + path < q.N;   // columns beyond the last path contribute nothing
-                const double a = live ? node_value(isM ? 1 : 0, id, path) : 0.0;
-                if (isM) sXM[(size_t)k * LD + path] = a; else sXP[(size_t)k * LDX + path] = a;
-            }
         }
-        __syncthreads();
 
         // ================= phase F1: preconditioned regressors + fitted continuation values =================
         if (q.accum_mode == 1) {
@@ -517,17 +516,17 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
 // ------------------------------------------------------------------------------------------------
 // Launch configuration
 // ------------------------------------------------------------------------------------------------
-static size_t layout_bytes(int TP, int Gn, int K, int F, int MT, int nbuf, int n_prod) {
-    return sweep_layout(TP, Gn, K, F, MT, nbuf, n_prod).total * sizeof(double);
+static size_t layout_bytes(int TP, int Gn, int K, int F, int MT, int nbuf, int n_scratch, int n_rowops) {
+    return sweep_layout(TP, Gn, K, F, MT, nbuf, n_scratch, n_rowops).total * sizeof(double);
 }
 
 // Largest tile that fits the 227 KB of an SM, double-buffered when possible.
-bool choose_sweep_shape(int max_grid, int K, int F, int MT, int n_prod, int* TP, int* nbuf) {
+bool choose_sweep_shape(int max_grid, int K, int F, int MT, int n_scratch, int n_rowops, int* TP, int* nbuf) {
     const size_t limit = 224 * 1024;
     const int tps[2] = {56, 24};
     for (int nb = 2; nb >= 1; nb--)
         for (int tp : tps)
-            if (layout_bytes(tp, max_grid, K, F, MT, nb, n_prod) <= limit) { *TP = tp; *nbuf = nb; return true; }
+            if (layout_bytes(tp, max_grid, K, F, MT, nb, n_scratch, n_rowops) <= limit) { *TP = tp; *nbuf = nb; return true; }
     return false;
 }
 
@@ -564,7 +563,7 @@ cudaError_t launch_sweep(SweepParams& q, const SweepConfig& cfg, cudaStream_t st
     if (n_items > 2 * kWorkers) return cudaErrorInvalidValue;
     const int NTW = n_items <= kWorkers ? 1 : 2;
     q.ncols = 8 * (NT + MT);
-    const size_t smem = layout_bytes(cfg.TP, q.Gn, q.K, q.F, MT, cfg.nbuf, cfg.n_nodes - 3 - q.F);
+    const size_t smem = layout_bytes(cfg.TP, q.Gn, q.K, q.F, MT, cfg.nbuf, cfg.n_scratch, cfg.n_rowops);
     if (cfg.TP == 56) return launch_sweep_tp<56>(q, MT, NTW, cfg.blocks, smem, cfg.nbuf, stream);
 #ifdef LSMC_FAST_BUILD
     return cudaErrorInvalidValue;
