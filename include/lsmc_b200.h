@@ -171,7 +171,8 @@ typedef struct lsmc_timings {
     double valuation_sim_ms;
     double forward_ms;
     double total_ms;
-    double backward_sweep_kernel_ms;   /* sum over periods of the fused decision+normal-equation kernel */
+    double backward_sweep_kernel_ms;   /* sum over periods of the fused decision+normal-equation kernel; 0 unless
+                                          lsmc_set_kernel_timing(ctx, 1) was called before lsmc_backward */
     double backward_solve_kernel_ms;   /* sum over periods of reduce+solve */
     int64_t backward_sweep_launches;
     int64_t kernel_launches;           /* all kernels launched since lsmc_set_problem */
@@ -225,6 +226,11 @@ int lsmc_backward(lsmc_ctx* ctx, lsmc_progress_cb progress, void* progress_user)
 int lsmc_forward(lsmc_ctx* ctx, lsmc_progress_cb progress, void* progress_user);
 int lsmc_get_results(lsmc_ctx* ctx, lsmc_results* results);             /* D2H of whatever is non-NULL */
 int lsmc_get_timings(const lsmc_ctx* ctx, lsmc_timings* out);
+/* Per-launch CUDA events around every sweep kernel of the following lsmc_backward calls (fills backward_sweep_kernel_ms;
+ * the reference's Stopwatches.cs has no finer counterpart).  Off by default: an event between two kernels serialises them,
+ * and the kernels of the backward loop otherwise overlap their set-up with the predecessor's drain (programmatic
+ * dependent launch), about 5 us per period. */
+int lsmc_set_kernel_timing(lsmc_ctx* ctx, int on);
 
 /* Page-locked host memory for result buffers.  lsmc_get_results / lsmc_calculate write per-sim panels ([P][N] doubles each:
  * 23 GB for the eight panels of a 1M-path daily year, LSV.cs:351-356,602-616) with the copy engine straight into a

@@ -3,6 +3,12 @@
 import sys
 import numpy as np
 a = np.fromfile(sys.argv[1], dtype=np.int64).reshape(16, 64, 8)
+entry, waited = int(a[0, 63, 6]), int(a[0, 63, 7])
+a[0, 63, 6] = a[0, 63, 7] = 0
+if entry > 0:
+    body = a[:13, :, :4]
+    print("kernel entry -> dependency wait over: %d clk; -> first decision tile starts: %d clk; -> last decision tile ends: %d clk" % (
+        waited - entry, body[:, 0, 2][body[:, 0, 2] > 0].min() - entry, body[:, :, 3].max() - entry))
 t0 = a[a > 0].min()
 rel = np.where(a > 0, a - t0, -1)
 ntile = int((rel[0, :, 0] >= 0).sum())

@@ -16,7 +16,7 @@ EXPORTS = (
     "lsmc_version", "lsmc_create", "lsmc_destroy", "lsmc_last_error", "lsmc_comm_unique_id", "lsmc_comm_init", "lsmc_comm_init_local",
     "lsmc_calculate_multi", "lsmc_intrinsic", "lsmc_host_alloc", "lsmc_host_free",
     "lsmc_calculate", "lsmc_set_problem", "lsmc_get_layout", "lsmc_request_outputs", "lsmc_simulate", "lsmc_backward",
-    "lsmc_forward", "lsmc_get_results", "lsmc_get_timings", "lsmc_get_grid", "lsmc_get_inventory_space",
+    "lsmc_forward", "lsmc_get_results", "lsmc_get_timings", "lsmc_set_kernel_timing", "lsmc_get_grid", "lsmc_get_inventory_space",
     "lsmc_get_regression_coeffs", "lsmc_get_sim_panel", "lsmc_debug_set_regression_coeffs", "lsmc_debug_keep_values",
     "lsmc_debug_get_values", "lsmc_npv_stats_noalloc",
 )
@@ -141,6 +141,10 @@ class Context:
         cres = results.c_struct()
         self._check(lib().lsmc_get_results(self._h, C.byref(cres)))
         return results.sync_scalars()
+
+    def set_kernel_timing(self, on):
+        """CUDA events around every sweep launch of the next backward passes (timings()['backward_sweep_kernel_ms'])."""
+        self._check(lib().lsmc_set_kernel_timing(self._h, C.c_int(1 if on else 0)))
 
     def timings(self):
         t = _abi.LsmcTimings()

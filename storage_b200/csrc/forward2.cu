@@ -79,10 +79,17 @@ __host__ __device__ inline F2Layout f2_layout(int K, int n_nodes, int max_grid) 
 
 }  // namespace
 
+// KT > 0: K = KT at compile time (K <= 16): the path's basis row and its column sums are registers.
+// KT == 0: any K <= 64 (C4: 56 monomials of five factors).  The basis row stays in the thread's shared-memory node column, the
+//          six fitted values of a path come from one pass over k, and the design matrix's column sums are taken by the warp
+//          together from its 32 node columns (lane = basis function, rotated reads: conflict free) — 112 accumulator registers per
+//          thread was what made the general forward kernel spill (342 ms per valuation at C4).
 template <int KT>
-__global__ void __launch_bounds__(kF2Threads, kF2MinBlocks) forward2_kernel(const Forward2Args a) {
+__global__ void __launch_bounds__(kF2Threads, KT == 0 ? 1 : kF2MinBlocks) forward2_kernel(const Forward2Args a) {
     extern __shared__ __align__(16) double f2sm[];
-    constexpr int K = KT, nsum = kFwdSums + K;
+    constexpr bool BIG = KT == 0;
+    constexpr int KR = BIG ? 1 : KT;           // register arrays of the small-K form
+    const int K = BIG ? a.K : KT, nsum = kFwdSums + K;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const F2Layout L = f2_layout(K, a.n_nodes, a.max_grid);
     const int BP = L.BP;
@@ -152,18 +159,50 @@ __global__ void __launch_bounds__(kF2Threads, kF2MinBlocks) forward2_kernel(cons
         const int c_kind = q.c_kind, c_n = q.c_n;
         const bool any_panel = q.o_inventory || q.o_volume || q.o_consumed || q.o_loss || q.o_net || q.o_pv || q.o_decision;
 
-        double sums[kFwdSums], xsum[KT];
+        double sums[kFwdSums], xsum[KR];
+        double xs0 = 0.0, xs1 = 0.0;   // BIG: column sums of basis functions `lane` and `lane + 32` over the warp's paths
 #pragma unroll
         for (int i = 0; i < kFwdSums; i++) sums[i] = 0.0;
 #pragma unroll
-        for (int k = 0; k < KT; k++) xsum[k] = 0.0;
+        for (int k = 0; k < KR; k++) xsum[k] = 0.0;
 
-        for (int64_t n = (int64_t)blockIdx.x * kF2Threads + tid; n < N; n += stride) {
+        // (BIG: the path loop is warp uniform — the warp sums its node columns together — and lanes beyond N idle inside it)
+        for (int64_t nb = (int64_t)blockIdx.x * kF2Threads + (BIG ? warp * 32 : tid); nb < N; nb += stride) {
+            const int64_t n = BIG ? nb + lane : nb;
+            const bool live = !BIG || n < N;
+            if (BIG && fitted_mode) {
+                if (live) {
+                    nodes[0] = 0.0; nodes[kF2Threads] = 1.0; nodes[2 * kF2Threads] = spot_is_const ? q.spot_const : __ldcs(spot_row + n);
+                    const double* fp = fac_rows + n;
+                    for (int f = 0; f < F; f++, fp += Npad) nodes[(3 + f) * kF2Threads] = __ldcs(fp);
+                    for (int o = 0; o < n_ops; o++) {
+                        const uint4 op = s_ops[o];
+                        nodes[op.x] = mul_rn(nodes[op.y], nodes[op.z]);
+                    }
+                } else {
+                    for (int j = 0; j < a.n_nodes; j++) nodes[j * kF2Threads] = 0.0;   // a lane beyond the last path adds zeros to the column sums
+                }
+                __syncwarp();
+                {
+                    const double* col = f2sm + warp * 32;
+                    const uint32_t o0 = s_basis_off[lane], o1 = s_basis_off[lane + 32];
+#pragma unroll 8
+                    for (int t = 0; t < 32; t++) {
+                        const int r = (t + lane) & 31;
+                        if (lane < K) xs0 += col[o0 + r];
+                        if (lane + 32 < K) xs1 += col[o1 + r];
+                    }
+                }
+                __syncwarp();
+            }
+            if (!live) continue;
             const double s = spot_is_const ? q.spot_const : __ldcs(spot_row + n);
             const double v = inv_state[n];
             const double pv_old = pv_state[n];
-            double xrow[KT];
-            if (fitted_mode) {
+            double xrow[KR];
+            if (BIG) {
+                // (basis row already in the node column)
+            } else if (fitted_mode) {
                 nodes[0] = 0.0; nodes[kF2Threads] = 1.0; nodes[2 * kF2Threads] = s;
                 {
                     const double* fp = fac_rows + n;
@@ -221,6 +260,9 @@ __global__ void __launch_bounds__(kF2Threads, kF2MinBlocks) forward2_kernel(cons
             double vol[3], tot[3], imm[3], cons[3];
             vol[0] = w; vol[1] = one_sided ? jn : 0.0; vol[2] = jn;
             bool all_found = true;
+            double flo[3], fhi[3], gl_d[3], gu_d[3], after_d[3];
+            bool lo_eq_hi[3];
+            [[maybe_unused]] int blo[3], bhi[3];
 #pragma unroll
             for (int d = 0; d < 3; d++) {
                 const double vd = vol[d];
@@ -251,18 +293,45 @@ __global__ void __launch_bounds__(kF2Threads, kF2MinBlocks) forward2_kernel(cons
                 const int lo = found ? (int)(cls & 0xffu) : 0, hi = found ? (int)(cls >> 8) : 0;
                 gl = grid_s[lo]; gu = grid_s[hi];
                 all_found = all_found && found;
-                const double2* bl = reinterpret_cast<const double2*>(beta_s + lo * BP);
-                const double2* bh = reinterpret_cast<const double2*>(beta_s + hi * BP);
                 double f_lo = 0.0, f_hi = 0.0;
+                if (BIG) { blo[d] = lo * BP; bhi[d] = hi * BP; }
+                else {
+                    const double2* bl = reinterpret_cast<const double2*>(beta_s + lo * BP);
+                    const double2* bh = reinterpret_cast<const double2*>(beta_s + hi * BP);
 #pragma unroll
-                for (int k2 = 0; k2 < (KT + 1) / 2; k2++) {
-                    const double2 cl = bl[k2], ch = bh[k2];
-                    f_lo = fma(xrow[2 * k2], cl.x, f_lo); f_hi = fma(xrow[2 * k2], ch.x, f_hi);
-                    if (2 * k2 + 1 < KT) { f_lo = fma(xrow[2 * k2 + 1], cl.y, f_lo); f_hi = fma(xrow[2 * k2 + 1], ch.y, f_hi); }
+                    for (int k2 = 0; k2 < (KR + 1) / 2; k2++) {
+                        const double2 cl = bl[k2], ch = bh[k2];
+                        f_lo = fma(xrow[2 * k2], cl.x, f_lo); f_hi = fma(xrow[2 * k2], ch.x, f_hi);
+                        if (2 * k2 + 1 < KR) { f_lo = fma(xrow[2 * k2 + 1], cl.y, f_lo); f_hi = fma(xrow[2 * k2 + 1], ch.y, f_hi); }
+                    }
                 }
+                flo[d] = f_lo; fhi[d] = f_hi; lo_eq_hi[d] = lo == hi; gl_d[d] = gl; gu_d[d] = gu; after_d[d] = after;
+            }
+            if (BIG) {   // the six fitted values in one pass over k: x_k from the node column, coefficient pairs from the staged rows
+                if (fitted_mode) {
+                    for (int k2 = 0; k2 < (K + 1) / 2; k2++) {
+                        const double x0 = nodes[s_basis_off[2 * k2]];
+                        const double x1 = (2 * k2 + 1 < K) ? nodes[s_basis_off[2 * k2 + 1]] : 0.0;
+#pragma unroll
+                        for (int d = 0; d < 3; d++) {
+                            const double2 cl = *reinterpret_cast<const double2*>(beta_s + blo[d] + 2 * k2);
+                            const double2 ch = *reinterpret_cast<const double2*>(beta_s + bhi[d] + 2 * k2);
+                            flo[d] = fma(x0, cl.x, flo[d]); fhi[d] = fma(x0, ch.x, fhi[d]);
+                            if (2 * k2 + 1 < K) { flo[d] = fma(x1, cl.y, flo[d]); fhi[d] = fma(x1, ch.y, fhi[d]); }
+                        }
+                    }
+                } else {
+#pragma unroll
+                    for (int d = 0; d < 3; d++) { flo[d] = beta_s[blo[d]]; fhi[d] = beta_s[bhi[d]]; }   // x = (1, 0, ...)
+                }
+            }
+#pragma unroll
+            for (int d = 0; d < 3; d++) {
+                const double f_lo = flo[d], f_hi = fhi[d], gl = gl_d[d], gu = gu_d[d], after = after_d[d];
+                const bool same = lo_eq_hi[d];
                 const double wl = sub_rn(gu, after) / sub_rn(gu, gl);
                 const double wu = sub_rn(1.0, wl);
-                const double cont = lo == hi ? f_lo : add_rn(mul_rn(f_lo, wl), mul_rn(f_hi, wu));
+                const double cont = same ? f_lo : add_rn(mul_rn(f_lo, wl), mul_rn(f_hi, wu));
                 tot[d] = add_rn(imm[d], cont);
             }
             if (!all_found) atomicExch(q.error_flag, 4);
@@ -293,16 +362,21 @@ __global__ void __launch_bounds__(kF2Threads, kF2MinBlocks) forward2_kernel(cons
         // per-warp partial sums (fixed shuffle tree), one row per warp: sums[p][warp_global][nsum]
         double* out = a.warp_sums + ((size_t)p * a.n_parts + warp_global) * nsum;
 #pragma unroll
-        for (int i = 0; i < kFwdSums + KT; i++) {
+        for (int i = 0; i < kFwdSums + KR; i++) {
+            if (BIG && i >= kFwdSums) break;
             double val = i < kFwdSums ? sums[i < kFwdSums ? i : 0] : xsum[i >= kFwdSums ? i - kFwdSums : 0];
 #pragma unroll
             for (int off = 16; off > 0; off >>= 1) val += __shfl_xor_sync(0xffffffffu, val, off);
             if (lane == 0) out[i] = val;
         }
+        if (BIG) {   // the column sums are already whole-warp sums: lane = basis function
+            if (lane < K) out[kFwdSums + lane] = xs0;
+            if (lane + 32 < K) out[kFwdSums + lane + 32] = xs1;
+        }
     }
 }
 
-int forward2_blocks_per_sm() { return kF2MinBlocks; }
+int forward2_blocks_per_sm(int K) { return K > 16 ? 1 : kF2MinBlocks; }
 int forward2_threads() { return kF2Threads; }
 int forward2_parts(int blocks) { return blocks * kF2Warps; }
 
@@ -317,6 +391,13 @@ static cudaError_t launch_forward2_t(const Forward2Args& a, int blocks, cudaStre
 }
 
 cudaError_t launch_forward2(const Forward2Args& a, int K, int blocks, cudaStream_t stream) {
+    if (K > 16) {
+        if (K > 64 || a.K != K) return cudaErrorInvalidValue;
+        const size_t smem = forward2_smem_bytes(K, a.n_nodes, a.max_grid);
+        if (cudaError_t e = ensure_dynamic_smem((const void*)forward2_kernel<0>, smem)) return e;
+        forward2_kernel<0><<<blocks, kF2Threads, smem, stream>>>(a);
+        return cudaGetLastError();
+    }
     switch (K) {
 #define F2_K(k) case k: return launch_forward2_t<k>(a, blocks, stream);
 #ifdef LSMC_FAST_BUILD

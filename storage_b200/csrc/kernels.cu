@@ -8,6 +8,7 @@
 #include "kernels.h"
 #include "solve_device.cuh"
 
+#include <cstdlib>
 #include <map>
 #include <mutex>
 #include <utility>
@@ -26,6 +27,11 @@ cudaError_t ensure_dynamic_smem(const void* kernel, size_t bytes) {
     e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
     if (e == cudaSuccess) have = bytes;
     return e;
+}
+
+bool pdl_enabled() {
+    static const bool on = [] { const char* e = getenv("LSMC_PDL"); return !(e && e[0] == '0'); }();
+    return on;
 }
 
 // =================================================================================================

@@ -2,6 +2,7 @@
 #pragma once
 #include <algorithm>
 #include <cstddef>
+#include <utility>
 #include "../../include/lsmc_b200.h"
 #include "lsmc_device.cuh"
 
@@ -9,7 +10,7 @@ namespace lsmc {
 
 struct SweepConfig {
     int TP;        // paths per tile (56, 40 or 24)
-    int MT;        // basis m-tiles: 1, 2, 4 or 8 (8*MT >= K)
+    int MT;        // basis m-tiles: 1, 2, 4, 7 or 8 (8*MT >= K)
     int blocks;    // persistent CTAs
     int n_scratch; // rows of basis-program nodes that are not basis functions (host_plan.h RowProgram)
     int nbuf;      // shared-memory buffers for the staged V_next tile (2 = prefetch the next tile)
@@ -40,6 +41,20 @@ struct FinalParams {
 // the sizes already granted are cached under a mutex, so contexts on several GPUs (or several host threads) each get it.
 cudaError_t ensure_dynamic_smem(const void* kernel, size_t bytes);
 
+// Launch with programmatic stream serialisation (lsmc_device.cuh pdl_wait / pdl_launch_dependents).  LSMC_PDL=0 in the
+// environment falls back to plain stream order (development).
+bool pdl_enabled();
+template <class... KArgs, class... Args>
+inline cudaError_t launch_pdl(bool pdl, void (*kern)(KArgs...), int blocks, int threads, size_t smem, cudaStream_t stream, Args&&... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)blocks); cfg.blockDim = dim3((unsigned)threads); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, KArgs(std::forward<Args>(args))...);
+}
+
 bool choose_sweep_shape(int max_grid, int K, int F, int MT, int n_scratch, int n_rowops, int* TP, int* nbuf);
 int sweep_max_items();
 int precond_rows(int K, int64_t N);
@@ -62,7 +77,7 @@ __host__ __device__ constexpr int forward2_beta_pitch(int K) { return (((K + 1) 
 struct Forward2Args {
     const ForwardParams* params;   // [P-1]
     int p0, p1;                    // periods of this launch
-    int F, n_nodes, max_grid, ldb, grid_pitch, n_parts;
+    int K, F, n_nodes, max_grid, ldb, grid_pitch, n_parts;
     const BasisDev* basis;
     const double* beta_all; size_t beta_stride;   // coefficients of period p at beta_all + p * beta_stride, rows of pitch ldb
     const double* grid_pad;        // [P][grid_pitch] the grid of period p at row p
@@ -71,7 +86,7 @@ struct Forward2Args {
 };
 cudaError_t launch_forward2(const Forward2Args& a, int K, int blocks, cudaStream_t stream);
 size_t forward2_smem_bytes(int K, int n_nodes, int max_grid);
-int forward2_blocks_per_sm();
+int forward2_blocks_per_sm(int K);
 int forward2_threads();
 int forward2_parts(int blocks);
 void launch_reduce_rows(const double* in, int n_rows, int n_blocks, int n_cols, double* out, cudaStream_t stream);

@@ -192,6 +192,10 @@ struct lsmc_ctx {
     void* comm = nullptr;
     int rank = 0, world = 1;
     PeerComm peer;                       // exchange over peer memory (world == 1: the tail kernel's grid barrier)
+    bool use_pdl = true;                 // programmatic dependent launch of the backward loop's kernels.  Off when another rank of the
+                                         // group runs on the same GPU: its CTAs, parked at their dependency wait, could hold the SMs that
+                                         // the other rank's kernels — which this rank's exchange is waiting for — need to become resident.
+    bool time_kernels = false;           // lsmc_set_kernel_timing: CUDA events around every sweep launch (they break the kernels' programmatic overlap)
     bool use_tail = true;                // fused reduce + exchange + solve kernel (tail.cu); false: reduce -> NCCL -> solve
     std::shared_ptr<LocalGroup> group;   // ranks of one process (lsmc_comm_init_local)
     int64_t out_pitch = 0, out_col0 = 0; // per-sim outputs of lsmc_get_results: row pitch / first column in the caller's buffers (0: n_sims, 0)
@@ -310,6 +314,13 @@ void map_peers_over_ipc(lsmc_ctx* c) {
     Blob mine{};
     if (ok && cudaIpcGetMemHandle(&mine.h, c->peer.buf) != cudaSuccess) { (void)cudaGetLastError(); ok = false; }
     mine.ok = ok ? 1 : 0;
+    {   // which GPU this rank runs on: two ranks of one GPU must not use programmatic dependent launch (lsmc_ctx::use_pdl)
+        int dom = 0, bus = 0, dev = 0;
+        cudaDeviceGetAttribute(&dom, cudaDevAttrPciDomainId, c->device);
+        cudaDeviceGetAttribute(&bus, cudaDevAttrPciBusId, c->device);
+        cudaDeviceGetAttribute(&dev, cudaDevAttrPciDeviceId, c->device);
+        mine.pad[0] = (dom << 16) | (bus << 8) | dev;
+    }
     CUDA_CHECK(cudaMemcpyAsync(d_send.p, &mine, sizeof(Blob), cudaMemcpyHostToDevice, s));
     int rc = g_nccl.AllGather(d_send.p, d_recv.p, sizeof(Blob), /*ncclInt8*/ 0, c->comm, s);
     if (rc != 0) throw Error(LSMC_ECUDA, "ncclAllGather failed while exchanging the peer-memory handles");
@@ -318,6 +329,7 @@ void map_peers_over_ipc(lsmc_ctx* c) {
     CUDA_CHECK(cudaStreamSynchronize(s));
     PeerView v{};
     v.rank = rank; v.world = world;
+    for (int r = 0; r < world; r++) if (r != rank && all[r].pad[0] == mine.pad[0]) c->use_pdl = false;
     for (int r = 0; r < world && ok; r++) {
         if (!all[r].ok) { ok = false; break; }
         double* base = c->peer.buf;
@@ -345,13 +357,13 @@ void map_peers_over_ipc(lsmc_ctx* c) {
     if (getenv("LSMC_VERBOSE")) fprintf(stderr, "lsmc_comm_init: rank %d of %d, exchange over %s\n", rank, world, c->peer.ready ? "peer memory (cudaIpc)" : "NCCL collectives");
 }
 
-// The straight-line forward kernel (kernels.cu forward_fast_kernel) covers: no extra decisions, K <= 16, and next-period
+// The straight-line forward kernels (forward2.cu; kernels.cu forward_fast_kernel for K <= 16) cover: no extra decisions and next-period
 // grids on which its O(1) lookup provably equals the bisection of SH.cs:280-314 (kernels.cu fwd_class_result): at most 127
 // points; every interval but the last wider than twice the tolerance (the last one only has to be positive: accumulating
 // the step and clamping to the maximum, FixedSpacingStateSpaceGridCalc.cs:45-62, can leave one of a rounding error); all
 // points but the last within a quarter step of fixed spacing, so that the index guess is off by at most one.
 bool forward_fast_ok(const Plan& pl, const lsmc_problem& pb) {
-    if (pb.extra_decisions != 0 || pl.K > 16 || pl.max_dec > 3) return false;
+    if (pb.extra_decisions != 0 || pl.K > 64 || pl.max_dec > 3) return false;
     const double tol = pb.numerical_tolerance;
     if (!(tol >= 0.0)) return false;
     for (int p = 1; p < pl.P; p++) {
@@ -384,7 +396,7 @@ void set_problem(lsmc_ctx* c, const lsmc_problem* problem) {
     if (c->Nglobal != c->N)   // a shard of a larger valuation: antithetic partners 2m, 2m+1 must live on one rank
         require(pb.sim_offset % 2 == 0 && pb.sim_offset >= 0 && pb.sim_offset + c->N <= c->Nglobal && (c->N % 2 == 0 || pb.sim_offset + c->N == c->Nglobal),
                 LSMC_EINVAL, "a shard must start on an even path and hold an even number of paths (except the last shard)");
-    c->MT = pl.K <= 8 ? 1 : (pl.K <= 16 ? 2 : (pl.K <= 32 ? 4 : 8));
+    c->MT = pl.K <= 8 ? 1 : (pl.K <= 16 ? 2 : (pl.K <= 32 ? 4 : (pl.K > 48 && pl.K <= 56 ? 7 : 8)));   // sweep.cu instantiates 1, 2, 4, 7, 8
     c->ldb = (pl.K + 3) & ~3;
     require(pl.basis.n_nodes <= kMaxNodes && (int)pl.basis.ops.size() <= kMaxOps, LSMC_EUNSUPPORTED, "basis functions need too many product nodes");
     require(pl.max_dec <= 16, LSMC_EUNSUPPORTED, "extra_decisions above 6 is not supported on the device path");
@@ -397,19 +409,21 @@ void set_problem(lsmc_ctx* c, const lsmc_problem* problem) {
     c->TP4 = sweep4_tile(pl.max_grid, pl.K, pl.F, (int)pl.basis.ops.size());
     c->sweep4_blocks = c->TP4 ? (int)std::min<int64_t>(c->num_sms, (c->N + c->TP4 - 1) / c->TP4) : 0;
     if (const char* e = getenv("LSMC_SWEEP")) { if (atoi(e) == 3) c->TP4 = c->sweep4_blocks = 0; }   // development: force the general sweep kernel
+    if (getenv("LSMC_TIME_KERNELS")) c->time_kernels = true;   // development: per-launch events without the API call
     if (const char* e = getenv("LSMC_TAIL")) c->use_tail = atoi(e) != 0;   // development: 0 = reduce -> NCCL all-reduce -> one-CTA solve
     if (c->world <= 1 && !c->peer.ready) c->peer.self_only();
     require(8 * c->MT * 8 * ((pl.max_grid + 7) / 8 + c->MT) <= kPeerSlotDoubles, LSMC_EUNSUPPORTED, "normal-equation block larger than the exchange slots");
-    c->fwd_fast = forward_fast_ok(pl, pb);
-    if (const char* e = getenv("LSMC_FORWARD")) { if (atoi(e) == 0) c->fwd_fast = false; }   // development: force the general forward kernel
+    bool fwd_grid_ok = forward_fast_ok(pl, pb);
+    if (const char* e = getenv("LSMC_FORWARD")) { if (atoi(e) == 0) fwd_grid_ok = false; }   // development: force the general forward kernel
+    c->fwd_fast = fwd_grid_ok && pl.K <= 16;
     require(forward_smem_bytes(pl.K, pl.basis.n_nodes, pl.max_grid, c->fwd_fast) <= (size_t)227 * 1024 - 4096, LSMC_EUNSUPPORTED,
             "basis functions / inventory grid too large for the forward kernel's shared memory");
-    c->fwd2 = c->fwd_fast;
+    c->fwd2 = fwd_grid_ok;   // the streaming kernel also has a K <= 64 form (forward2.cu KT = 0)
     for (int cid = 0; cid < pb.n_constraints; cid++) c->fwd2 = c->fwd2 && pb.constraint_count[cid] <= 16;
-    c->fwd2 = c->fwd2 && forward2_smem_bytes(pl.K, pl.basis.n_nodes, pl.max_grid) <= (size_t)75 * 1024;
+    c->fwd2 = c->fwd2 && forward2_smem_bytes(pl.K, pl.basis.n_nodes, pl.max_grid) <= (pl.K <= 16 ? (size_t)75 * 1024 : (size_t)227 * 1024 - 2048);
     if (const char* e = getenv("LSMC_FORWARD")) { if (atoi(e) == 1) c->fwd2 = false; }   // development: 1 = the previous straight-line kernel
     const int fwd_threads = c->fwd2 ? forward2_threads() : (c->fwd_fast ? forward_fast_threads() : 256);
-    const int fwd_per_sm = c->fwd2 ? forward2_blocks_per_sm() : (c->fwd_fast ? forward_fast_blocks_per_sm() : (pl.K <= 16 ? 3 : 1));
+    const int fwd_per_sm = c->fwd2 ? forward2_blocks_per_sm(pl.K) : (c->fwd_fast ? forward_fast_blocks_per_sm() : (pl.K <= 16 ? 3 : 1));
     c->fwd_blocks = (int)std::min<int64_t>((int64_t)c->num_sms * fwd_per_sm, (c->N + fwd_threads - 1) / fwd_threads);   // all CTAs resident: each walks every period
     c->fwd_parts = c->fwd2 ? forward2_parts(c->fwd_blocks) : c->fwd_blocks;
     c->ncols_max = 8 * ((pl.max_grid + 7) / 8 + c->MT);
@@ -485,6 +499,16 @@ void set_problem(lsmc_ctx* c, const lsmc_problem* problem) {
                 require(pb.factor_power[k * pl.F + f] <= 127, LSMC_EUNSUPPORTED, "basis exponent above 127");
                 b.fac_pow[k][f] = (int8_t)pb.factor_power[k * pl.F + f];
             }
+        }
+        {   // waves of the product program (sweep4.cu): an op joins the current wave unless it reads a result of that wave
+            int nw = 0, w0 = 0;
+            for (int o = 0; o < b.n_ops; o++) {
+                bool dep = false;
+                for (int e = w0; e < o; e++) dep = dep || b.ops[e].dst == b.ops[o].a || b.ops[e].dst == b.ops[o].b;
+                if (dep) { b.opwave_end[nw++] = (int16_t)o; w0 = o; }
+            }
+            if (b.n_ops > 0) b.opwave_end[nw++] = (int16_t)b.n_ops;
+            b.n_opwaves = nw;
         }
         const RowProgram& rp = pl.basis_rows;
         require((int)rp.ops.size() <= kMaxRowOps, LSMC_EUNSUPPORTED, "basis functions need too many product nodes");
@@ -592,6 +616,7 @@ void backward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
         q.ldb = c->ldb;
         q.basis = c->basis.p;
         q.partial = c->partial.p;
+        q.pdl = (c->use_pdl && pdl_enabled()) ? 1 : 0;
         const bool is_current = (p == 0 && s0 == 1);
         double* vout = c->keep_values ? c->Vall.p + (size_t)p * pl.max_grid * Np : c->V(cur ^ 1);
         const double* vnext = c->keep_values ? c->Vall.p + (size_t)(p + 1) * pl.max_grid * Np : c->V(cur);
@@ -629,7 +654,7 @@ void backward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
             if (nowt - last > 0.05) fprintf(stderr, "[rank %d %.6f] backward: period %d reached after %.3f s\n", c->rank, nowt, p, nowt - last);
             last = nowt;
         }
-        CUDA_CHECK(cudaEventRecord(c->event(ev_base), s));
+        if (c->time_kernels) CUDA_CHECK(cudaEventRecord(c->event(ev_base), s));
         const bool use4 = c->TP4 != 0 && sweep4_covers(q);
         DevBuf<long long> trace_buf;
         const char* trace_path = getenv("LSMC_TRACE");   // development: phase timestamps of one mid-horizon sweep
@@ -638,8 +663,7 @@ void backward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
         const int n_parts = use4 ? c->sweep4_blocks : c->sweep_blocks;
         if (use4) CUDA_CHECK(launch_sweep4(q, c->TP4, (int)pl.basis.ops.size(), c->sweep4_blocks, s));
         else CUDA_CHECK(launch_sweep(q, cfg, s));
-        CUDA_CHECK(cudaEventRecord(c->event(ev_base + 1), s));
-        ev_base += 2;
+        if (c->time_kernels) { CUDA_CHECK(cudaEventRecord(c->event(ev_base + 1), s)); ev_base += 2; }
         if (trace_now) {
             std::vector<long long> h(16 * 64 * 8);
             CUDA_CHECK(cudaMemcpyAsync(h.data(), trace_buf.p, h.size() * sizeof(long long), cudaMemcpyDeviceToHost, s));
@@ -662,7 +686,7 @@ void backward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
             tp.solve = sp; tp.partial = c->partial.p; tp.n_parts = n_parts; tp.n_elem = n_elem;
             tp.do_solve = p > 0 ? 1 : 0;
             tp.total_out = c->reduced.p; tp.n_out = 1;   // element 0 at p == 0: sum of the start-inventory values (backward NPV)
-            tp.peers = c->peer.view; tp.error_flag = c->error_flag.p;
+            tp.peers = c->peer.view; tp.error_flag = c->error_flag.p; tp.pdl = q.pdl;
             const int blocks = tail_blocks(n_elem, q.G, c->num_sms);
             c->peer.next(blocks, &tp.parity, &tp.target);
             static const bool tail_trace = getenv("LSMC_TAIL_TRACE") != nullptr;   // development: phase stamps of one mid-horizon tail
@@ -768,7 +792,7 @@ void forward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
     c->fwd_params.upload(hq, s);
     HOST_TRACE(c, "forward: launch");
     Forward2Args fa{};
-    fa.params = c->fwd_params.p; fa.F = F; fa.n_nodes = pl.basis.n_nodes; fa.max_grid = pl.max_grid; fa.ldb = c->ldb;
+    fa.params = c->fwd_params.p; fa.K = K; fa.F = F; fa.n_nodes = pl.basis.n_nodes; fa.max_grid = pl.max_grid; fa.ldb = c->ldb;
     fa.grid_pitch = (pl.max_grid + 1) & ~1; fa.n_parts = c->fwd_parts; fa.basis = c->basis.p;
     fa.beta_all = c->beta_all.p; fa.beta_stride = c->beta_stride(); fa.grid_pad = c->grid_pad.p; fa.pillars = c->fwd_pillars.p;
     fa.warp_sums = c->fwd_sums.p;
@@ -1104,6 +1128,7 @@ int lsmc_comm_init_local(lsmc_ctx** ctxs, int n) {
             require(c->comm == nullptr, LSMC_EINVAL, "context already belongs to an NCCL communicator");
             CUDA_CHECK(cudaSetDevice(c->device));
             c->rank = r; c->world = n; c->group = n > 1 ? group : nullptr;
+            for (int o = 0; o < n; o++) if (o != r && ctxs[o]->device == c->device) c->use_pdl = false;
             if (n == 1) { c->peer.self_only(); continue; }
             c->peer.release();
             c->peer.allocate(n);
@@ -1295,6 +1320,12 @@ int lsmc_intrinsic(const lsmc_problem* problem, double* npv, double* profile) {
 int lsmc_get_timings(const lsmc_ctx* ctx, lsmc_timings* out) {
     if (!ctx || !out) return LSMC_EINVAL;
     *out = ctx->tm;
+    return LSMC_OK;
+}
+
+int lsmc_set_kernel_timing(lsmc_ctx* ctx, int on) {
+    if (!ctx) return LSMC_EINVAL;
+    ctx->time_kernels = on != 0;
     return LSMC_OK;
 }
 

@@ -10,6 +10,16 @@ constexpr int kMaxNodes = 200;    // basis-program nodes (zero, one, spot, F fac
 constexpr int kMaxOps = 192;
 
 // ------------------------------------------------------------------------------------------------
+// Programmatic dependent launch (PDL): the kernels of the backward loop are launched with programmatic stream
+// serialisation (kernels.h launch_pdl), so a kernel's CTAs are scheduled while its predecessor drains and its set-up that
+// does not touch the predecessor's results (shared-memory staging, decision tables, the first regressor copies) overlaps
+// it.  pdl_wait() returns when every prerequisite grid has completed and its memory operations are visible; it is a
+// no-op in a kernel launched without the attribute.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+// ------------------------------------------------------------------------------------------------
 // Arithmetic with the reference's rounding: no contraction unless written as fma().
 // ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(a, b); }
@@ -95,6 +105,10 @@ struct BasisDev {
     int n_rowops, n_rowwaves, n_scratch;
     int16_t rowwave_end[kMaxRowOps];
     RowOpDev rowops[kMaxRowOps];
+    // `ops` in waves of mutually independent multiplies (a wave ends before the first op that reads a result of the same wave;
+    // compile_basis emits operands first): used by the pipelined sweep, computed once on the host
+    int n_opwaves;
+    int16_t opwave_end[kMaxOps + 1];
 };
 
 // Per-period regression preconditioner: T = R_sub^-1 (upper triangular, K x K, row-major) from a
@@ -141,6 +155,8 @@ struct SweepParams {
     double* partial;          // [gridDim.x][8*MT][ncols] normal-equation partials
     int ncols;                // 8 * (ceil(G/8) + MT)
     long long* trace;         // development (LSMC_TRACE): per-warp phase timestamps of CTA 0, [16][64][8]; NULL otherwise
+    int pdl;                  // host side: launch with programmatic stream serialisation (kernels.h launch_pdl)
+    int n_prod;               // product nodes of the basis program (= basis->n_ops; a parameter so that the kernel's set-up does not start with a load)
 };
 
 struct PrecondParams {

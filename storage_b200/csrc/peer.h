@@ -41,6 +41,7 @@ struct TailParams {
     unsigned long long target;  // cumulative arrivals at this rank's counter after this exchange
     int* error_flag;            // set to kPeerTimeout when a spin times out
     long long* trace;           // development (LSMC_TAIL_TRACE): globaltimer stamps of CTA 0, [8]; NULL otherwise
+    int pdl;                    // host side: launch with programmatic stream serialisation
 };
 constexpr int kPeerTimeout = 9;
 

@@ -36,12 +36,16 @@ __device__ __forceinline__ bool solve_stage(const SolveParams& sp, const Red& re
     double* Tm = dscale + K;        // [K][K] preconditioner (when present)
     const int gcol = 8 * sp.NT;
     const double* T = sp.precond;
+#pragma unroll 4   // independent L2 loads: several in flight per thread (K = 56: 25 elements per thread, 22 us -> a few)
     for (int e = tid; e < K * K; e += blockDim.x) {
         int r = e / K, c = e % K;
         // symmetrise: the two triangles come from different DMMA tiles and may differ in the last bit
         Graw[e] = 0.5 * (red(r, gcol + c) + red(c, gcol + r));
     }
-    if (T) for (int e = tid; e < K * K; e += blockDim.x) Tm[e] = T[e];
+    if (T) {
+#pragma unroll 4
+        for (int e = tid; e < K * K; e += blockDim.x) Tm[e] = T[e];
+    }
     __syncthreads();
     for (int k = tid; k < K; k += blockDim.x) {
         const double gkk = Graw[k * K + k];
@@ -58,34 +62,55 @@ __device__ __forceinline__ bool solve_stage(const SolveParams& sp, const Red& re
     return true;
 }
 
-// Cholesky of the staged, scaled Gram matrix by warp 0 + reciprocals of the diagonal (CTA-wide call).
+// Cholesky of the staged, scaled Gram matrix by the whole CTA + reciprocals of the diagonal (CTA-wide call).
+// Right-looking with the scaling deferred: at column j every thread reads the pivot itself and applies
+//     A[i][k] -= A[i][j] A[k][j] / pivot          (j < k <= i)
+// to its share of the trailing triangle — the reads are in column j, the writes in the columns right of it, so one barrier
+// per column suffices and nobody waits for a thread that takes a square root; L = A scaled by 1 / sqrt(pivot) comes in one
+// pass at the end.  (The previous form — warp 0 alone, sqrt and divisions serial on lane 0, three warp barriers per column —
+// took 5.8 us at K = 10 and 104 us at K = 56: tail trace in profiles/.)
 __device__ __forceinline__ void solve_factor(const SolveParams& sp, double* sm, int* dropped) {
-    const int K = sp.K, tid = threadIdx.x;
+    const int K = sp.K, tid = threadIdx.x, nthr = blockDim.x;
     double* A = sm;
     double* Tm = A + 2 * K * K + K;
-    // Cholesky by warp 0 (lane = row, rows lane and lane + 32): no block-wide barriers in the column loop
-    if (tid < 32) {
-        for (int j = 0; j < K; j++) {
-            if (tid == 0) {
-                double piv = A[j * K + j];
-                if (dropped[j] || !(piv > sp.pivot_tol)) { dropped[j] = 1; A[j * K + j] = 1.0; }
-                else A[j * K + j] = sqrt(piv);
-            }
-            __syncwarp();
-            const bool dj = dropped[j];
-            const double ljj = A[j * K + j];
-            for (int i = j + 1 + tid; i < K; i += 32) A[i * K + j] = dj ? 0.0 : A[i * K + j] / ljj;
-            __syncwarp();
-            for (int i = j + 1 + tid; i < K; i += 32) {
-                const double aij = A[i * K + j];
-                for (int k = j + 1; k <= i; k++) A[i * K + k] -= aij * A[k * K + j];
-            }
-            __syncwarp();
+    double* invd = Tm + K * K;      // [K] reciprocals of the factor's diagonal: the substitutions multiply instead of dividing
+    const int ti = tid >> 4, tk = tid & 15, ni = nthr >> 4;   // blockDim.x is a multiple of 32
+    for (int j = 0; j < K; j++) {
+        const double piv = A[j * K + j];
+        const bool dj = dropped[j] != 0 || !(piv > sp.pivot_tol);
+        const double rinv = dj ? 0.0 : __drcp_rn(piv);
+        for (int i = j + 1 + ti; i < K; i += ni) {
+            const double aij = A[i * K + j] * rinv;
+            for (int k = j + 1 + tk; k <= i; k += 16) A[i * K + k] = fma(-aij, A[k * K + j], A[i * K + k]);
         }
+        __syncthreads();
+    }
+    // scaling: l_jj = sqrt(pivot_j), l_ij = a_ij / l_jj; a dropped column becomes the unit column
+    for (int j = tid; j < K; j += nthr) {
+        const double piv = A[j * K + j];
+        const bool dj = dropped[j] != 0 || !(piv > sp.pivot_tol);
+        invd[j] = dj ? 1.0 : rsqrt(piv);
     }
     __syncthreads();
-    double* invd = Tm + K * K;      // [K] reciprocals of the factor's diagonal: the substitutions multiply instead of dividing
-    for (int k = tid; k < K; k += blockDim.x) invd[k] = 1.0 / A[k * K + k];
+    for (int j = tid; j < K; j += nthr) {
+        const double piv = A[j * K + j];
+        if (dropped[j] != 0 || !(piv > sp.pivot_tol)) dropped[j] = 1;
+    }
+    for (int e = tid; e < K * K; e += nthr) {
+        const int i = e / K, j = e - i * K;
+        if (j > i) continue;
+        const double piv = A[j * K + j];
+        const bool dj = !(piv > sp.pivot_tol) || dropped[j] != 0;   // dropped[] of column j may already carry this step's verdict: same value
+        if (i == j) continue;
+        A[e] = dj ? 0.0 : A[e] * invd[j];
+    }
+    __syncthreads();
+    for (int j = tid; j < K; j += nthr) {
+        const double piv = A[j * K + j];
+        A[j * K + j] = dropped[j] ? 1.0 : sqrt(piv);
+    }
+    __syncthreads();
+    for (int j = tid; j < K; j += nthr) invd[j] = 1.0 / A[j * K + j];
     __syncthreads();
 }
 

@@ -239,6 +239,7 @@ __device__ __forceinline__ void terminal_item(const SweepParams& q, const RowTab
 template <int TP, int MT, int NTW>
 __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams q, int nbuf) {
     extern __shared__ __align__(16) double smem[];
+    pdl_launch_dependents();   // PDL: see lsmc_device.cuh
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, t = lane & 3;
     const BasisDev* __restrict__ bd = q.basis;
@@ -292,6 +293,7 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
         smem[L.cst + LD + path] = 1.0;
         if (!need_sp) { sRaw[path] = q.spot_const; if (nbuf == 2) sRaw[(size_t)L.raw_rows * LD + path] = q.spot_const; }   // every tile buffer
     }
+    pdl_wait();   // everything above reads only per-problem constants; the coefficients and V_next come from the previous kernels
     if (need_fp) {
         for (int i = tid; i < q.Gn * Kp4; i += blockDim.x) {
             const int l = i / Kp4, k = i - l * Kp4;
@@ -534,8 +536,7 @@ template <int TP, int MT, int NTW>
 static cudaError_t launch_sweep_t(const SweepParams& q, int blocks, size_t smem, int nbuf, cudaStream_t stream) {
     auto kern = sweep_kernel<TP, MT, NTW>;
     if (cudaError_t e = ensure_dynamic_smem((const void*)kern, smem)) return e;
-    kern<<<blocks, kSweepWarps * 32, smem, stream>>>(q, nbuf);
-    return cudaGetLastError();
+    return launch_pdl(q.pdl != 0, kern, blocks, kSweepWarps * 32, smem, stream, q, nbuf);
 }
 
 template <int TP>
@@ -548,7 +549,7 @@ static cudaError_t launch_sweep_tp(const SweepParams& q, int MT, int NTW, int bl
 #ifdef LSMC_FAST_BUILD   // development builds: only the shapes of configs C1-C3/C5
     ROW(1) ROW(2)
 #else
-    ROW(1) ROW(2) ROW(4) ROW(8)
+    ROW(1) ROW(2) ROW(4) ROW(7) ROW(8)
 #endif
 #undef ROW
     return cudaErrorInvalidValue;

@@ -396,12 +396,15 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
                                                                 const __grid_constant__ CUtensorMap mapSp, const __grid_constant__ CUtensorMap mapFp,
                                                                 const __grid_constant__ CUtensorMap mapSm, const __grid_constant__ CUtensorMap mapFm) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
+    // PDL: the kernel after this one (tail.cu) may be scheduled as soon as SMs free up; it waits for this grid's completion itself
+    pdl_launch_dependents();
+    if (q.trace && blockIdx.x == 0 && threadIdx.x == 0) q.trace[(0 * 64 + 63) * 8 + 6] = clock64();   // kernel entry (development)
     constexpr int MT = MTD + (KS > 0 ? 1 : 0);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, t = lane & 3;
     const int K = q.K, F = q.F;
     const BasisDev* __restrict__ bd = q.basis;
-    const int n_prod = bd->n_ops;
+    const int n_prod = q.n_prod;
     const Layout4 L = layout4(TP, q.Gn, K, F, n_prod);
     const int GnP = L.GnP;
     constexpr size_t ROW = (size_t)TP * 8;
@@ -440,17 +443,10 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
         for (int b = 0; b < 2; b++) { mbar_init(&vfull[b], 1); mbar_init(&cready[b], kAuxWarps * 32); mbar_init(&dfree[b], NT * 32); }
         for (int s = 0; s < kRawStages; s++) mbar_init(&rfull[s], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        // a wave ends before the first node that reads a node of the same wave (host_plan.cpp compile_basis emits operands first)
-        int nw = 0, w0 = 0;
-        for (int o = 0; o < n_prod; o++) {
-            const BasisOpDev op = bd->ops[o];
-            bool dep = false;
-            for (int e = w0; e < o; e++) dep = dep || bd->ops[e].dst == op.a || bd->ops[e].dst == op.b;
-            if (dep) { sWaveEnd[nw++] = o; w0 = o; }
-        }
-        if (n_prod > 0) sWaveEnd[nw++] = n_prod;
-        sNWaves = nw;
     }
+    // waves of mutually independent product nodes: computed once on the host (BasisDev::opwave_end)
+    for (int w = tid; w < bd->n_opwaves; w += blockDim.x) sWaveEnd[w] = bd->opwave_end[w];
+    if (tid == 32) sNWaves = bd->n_opwaves;
     __syncthreads();
 
     if (warp < kDecWarps) {
@@ -489,6 +485,8 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
             *reinterpret_cast<int4*>(ent) = make_int4(__double2loint(wl), __double2hiint(wl), rl * (TP + kVPad) * 8, rh * (TP + kVPad) * 8);
         }
         __syncwarp();
+        pdl_wait();   // (the decision warps are gated by the aux warps' barriers anyway; this orders their V stores after the predecessors)
+        if (q.trace && blockIdx.x == 0 && threadIdx.x == 0) q.trace[(0 * 64 + 63) * 8 + 7] = clock64();   // dependency wait over
         const Pipe4 P{sm, vfull, cready, dfree, rfull};
 #if AB_NO_DECIDE
         decision_loop_empty(q, P, TP);
@@ -549,13 +547,19 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
             constexpr int NB = ROLE == 0 ? 1 : kFitTiles;
             const int mt_base = ROLE == 0 ? 2 * kFitTiles : (aw - 1) * kFitTiles;
             const int mt_cnt = max(0, min(n_mt - mt_base, NB));
+            // the first tile's regressor rows are inputs of the whole valuation (simulation panels): on their way before the
+            // dependency wait.  Nothing else may be: under PDL "my predecessor has STARTED" is all a CTA knows until its own wait
+            // returns, and when the grids are smaller than the GPU (few paths) the sweep before the tail kernel can still be
+            // running — V_next, its output, must not be touched before the wait (a hoisted V_next copy read unfinished rows).
+            if (ROLE == 0 && lane == 0 && (int64_t)blockIdx.x < n_tiles) produce_raw(blockIdx.x, 0);
+            pdl_wait();   // the coefficients (tail kernel) and V_next (the sweep before it) are complete and visible from here on
             // beta fragments (DMMA A operand: A[g][t] = beta[8 mt + g][4 ks + t]) stay in registers for the whole launch
             double bfrag[NB][KSTEPS];
 #pragma unroll
             for (int mi = 0; mi < NB; mi++)
 #pragma unroll
                 for (int ks = 0; ks < KSTEPS; ks++)
-                    bfrag[mi][ks] = (mi < mt_cnt) ? __ldg(q.beta + (size_t)(8 * (mt_base + mi) + g) * q.ldb + 4 * ks + t) : 0.0;
+                    bfrag[mi][ks] = (mi < mt_cnt) ? __ldcg(q.beta + (size_t)(8 * (mt_base + mi) + g) * q.ldb + 4 * ks + t) : 0.0;
             // descriptors of the basis rows this lane feeds as DMMA B operand: B[t][g] = x[4 ks + t][8 nt + g]
             uint32_t descP[KSTEPS], descM[KSTEPS];
 #pragma unroll
@@ -581,7 +585,6 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
 
             int stage = 0, sphase = 0;
             int it = 0;
-            if (ROLE == 0 && lane == 0 && (int64_t)blockIdx.x < n_tiles) produce_raw(blockIdx.x, 0);
             for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, it++) {
                 const int b = it & 1;
                 long long* tr = (q.trace && blockIdx.x == 0 && it < 64 && lane == 0) ? q.trace + ((size_t)warp * 64 + it) * 8 : nullptr;
@@ -779,21 +782,21 @@ int sweep4_tile(int max_grid, int K, int F, int n_prod) {
 }
 
 template <int TP, int MTD, int KS, int KSTEPS>
-static cudaError_t launch4_t(const SweepParams& q, int n_prod, int blocks, cudaStream_t stream) {
+static cudaError_t launch4_t(SweepParams& q, int n_prod, int blocks, cudaStream_t stream) {
     auto kern = sweep4_kernel<TP, MTD, KS, KSTEPS>;
     const size_t smem = layout4(TP, q.Gn, q.K, q.F, n_prod).total;
+    q.n_prod = n_prod;
     if (cudaError_t e = ensure_dynamic_smem((const void*)kern, smem)) return e;
     CUtensorMap mv, msp, mfp, msm, mfm;
     if (!make_map(&mv, q.Vnext, q.Npad, q.Gn, TP + kVPad, q.Gn) || !make_map(&msp, q.spot_p, q.Npad, 1, TP, 1) ||
         !make_map(&mfp, q.fac_p, q.Npad, q.F, TP, q.F) || !make_map(&msm, q.spot_m, q.Npad, 1, TP, 1) ||
         !make_map(&mfm, q.fac_m, q.Npad, q.F, TP, q.F))
         return cudaErrorInvalidValue;
-    kern<<<blocks, kWarps * 32, smem, stream>>>(q, mv, msp, mfp, msm, mfm);
-    return cudaGetLastError();
+    return launch_pdl(q.pdl != 0, kern, blocks, kWarps * 32, smem, stream, q, mv, msp, mfp, msm, mfm);
 }
 
 template <int TP>
-static cudaError_t launch4_tp(const SweepParams& q, int n_prod, int blocks, cudaStream_t stream) {
+static cudaError_t launch4_tp(SweepParams& q, int n_prod, int blocks, cudaStream_t stream) {
     const int K = q.K;
     // whole blocks of 8 basis rows go through DMMA, a remainder of 1..3 rows through DFMA
 #ifdef LSMC_ALL_DMMA   // development: remainder rows through a padded DMMA block as well

@@ -25,19 +25,34 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
     return v;
 }
 
-// One thread per CTA: publish this CTA's slot stores, arrive everywhere, wait for everybody.
+__device__ __forceinline__ unsigned long long ld_acquire_gpu(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// One thread per CTA: publish this CTA's slot stores, arrive everywhere, wait for everybody.  With one rank this is a plain
+// grid barrier: device scope is enough (no system-scope fence, no system-scope atomic: about 2 us less per period).
 __device__ __forceinline__ void arrive_and_wait(const PeerView& pv, unsigned long long target, int* error_flag) {
     __syncthreads();   // every thread's slot stores happen-before the fence below
     if (threadIdx.x == 0) {
-        __threadfence_system();
-        for (int r = 0; r < pv.world; r++) atomicAdd_system(pv.counter[r], 1ULL);
         const unsigned long long* mine = pv.counter[pv.rank];
         const long long t0 = clock64();
-        // a peer that failed or was cancelled never arrives: give up after ~2 s, and at once in every later exchange
-        while (ld_acquire_sys(mine) < target) {
-            if (*reinterpret_cast<volatile int*>(error_flag) == kPeerTimeout) break;
-            if (clock64() - t0 > 4000000000LL) { atomicExch(error_flag, kPeerTimeout); break; }
-            __nanosleep(20);
+        if (pv.world == 1) {
+            __threadfence();
+            atomicAdd(pv.counter[0], 1ULL);
+            while (ld_acquire_gpu(mine) < target) {
+                if (clock64() - t0 > 4000000000LL) { atomicExch(error_flag, kPeerTimeout); break; }
+            }
+        } else {
+            __threadfence_system();
+            for (int r = 0; r < pv.world; r++) atomicAdd_system(pv.counter[r], 1ULL);
+            // a peer that failed or was cancelled never arrives: give up after ~2 s, and at once in every later exchange
+            while (ld_acquire_sys(mine) < target) {
+                if (*reinterpret_cast<volatile int*>(error_flag) == kPeerTimeout) break;
+                if (clock64() - t0 > 4000000000LL) { atomicExch(error_flag, kPeerTimeout); break; }
+                __nanosleep(20);
+            }
         }
     }
     __syncthreads();
@@ -61,6 +76,8 @@ template <int R>   // rows of the system per lane: 1 (K <= 32) or 2 (K <= 64)
 __global__ void __launch_bounds__(kTailThreads) tail_kernel(const TailParams tp) {
     extern __shared__ double tsm[];
     __shared__ int dropped[64];
+    pdl_launch_dependents();   // PDL: the next sweep's CTAs set themselves up while this kernel runs ...
+    pdl_wait();                // ... and this one starts the moment the sweep before it has completed
     long long* tr = (tp.trace && blockIdx.x == 0 && threadIdx.x == 0) ? tp.trace : nullptr;
     if (tr) tr[0] = gtimer();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = kTailThreads / 32;
@@ -141,10 +158,10 @@ void launch_tail(const TailParams& tp, int blocks, cudaStream_t stream) {
     const size_t smem = tp.do_solve ? solve_smem_bytes(K) : 0;
     if (K <= 32) {
         if (ensure_dynamic_smem((const void*)tail_kernel<1>, smem) != cudaSuccess) return;
-        tail_kernel<1><<<blocks, kTailThreads, smem, stream>>>(tp);
+        launch_pdl(tp.pdl != 0, tail_kernel<1>, blocks, kTailThreads, smem, stream, tp);
     } else {
         if (ensure_dynamic_smem((const void*)tail_kernel<2>, smem) != cudaSuccess) return;
-        tail_kernel<2><<<blocks, kTailThreads, smem, stream>>>(tp);
+        launch_pdl(tp.pdl != 0, tail_kernel<2>, blocks, kTailThreads, smem, stream, tp);
     }
 }
 
