@@ -106,23 +106,25 @@ struct PeerComm {
     int alloc_world = 0;
     PeerView view{};
     unsigned long long target = 0;    // cumulative arrivals expected at this rank's counter
+    unsigned long long local_target = 0;   // cumulative tickets of this rank's own CTAs
     unsigned long long epoch = 0;     // exchanges started (the same sequence on every rank)
     std::vector<void*> opened;        // cudaIpcOpenMemHandle mappings to close
 
     static size_t bytes(int world) { return (size_t)2 * world * kPeerSlotDoubles * sizeof(double) + 256; }
     unsigned long long* counter_of(double* base, int world) const { return reinterpret_cast<unsigned long long*>(base + (size_t)2 * world * kPeerSlotDoubles); }
+    unsigned long long* ticket_of(double* base, int world) const { return counter_of(base, world) + 16; }   // own GPU only, its own 128-byte line
     void allocate(int world) {
         if (buf && alloc_world == world) return;
         release();
         CUDA_CHECK(cudaMalloc(&buf, bytes(world)));
         CUDA_CHECK(cudaMemset(buf, 0, bytes(world)));
         alloc_world = world;
-        target = 0; epoch = 0;
+        target = 0; local_target = 0; epoch = 0;
     }
     void self_only() {   // one rank: the "exchange" is the grid barrier of the tail kernel
         allocate(1);
         view = PeerView{};
-        view.rank = 0; view.world = 1; view.slots[0] = buf; view.counter[0] = counter_of(buf, 1);
+        view.rank = 0; view.world = 1; view.slots[0] = buf; view.counter[0] = counter_of(buf, 1); view.ticket = ticket_of(buf, 1);
         ready = true;
     }
     void release() {
@@ -132,11 +134,12 @@ struct PeerComm {
         buf = nullptr; alloc_world = 0; ready = false;
     }
     // parity and cumulative target of the next exchange in which every rank arrives with `ctas` CTAs
-    void next(int ctas, int* parity, unsigned long long* tgt) {
+    void next(int ctas, int* parity, unsigned long long* tgt, unsigned long long* local_tgt) {
         *parity = (int)(epoch & 1);
         epoch++;
         target += (unsigned long long)ctas * (unsigned long long)view.world;
-        *tgt = target;
+        local_target += (unsigned long long)ctas;
+        *tgt = target; *local_tgt = local_target;
     }
     ~PeerComm() { release(); }
 };
@@ -229,7 +232,7 @@ struct lsmc_ctx {
             PeerSmallParams pp{};
             pp.buf = buf + o; pp.count = (int)std::min<size_t>(kPeerSlotDoubles, count - o); pp.root = root;
             pp.peers = peer.view; pp.error_flag = error_flag.p;
-            peer.next(1, &pp.parity, &pp.target);
+            peer.next(1, &pp.parity, &pp.target, &pp.local_target);
             launch_peer_small(pp, stream);
             tm.kernel_launches++;
         }
@@ -342,6 +345,7 @@ void map_peers_over_ipc(lsmc_ctx* c) {
         v.slots[r] = base;
         v.counter[r] = c->peer.counter_of(base, world);
     }
+    v.ticket = c->peer.ticket_of(c->peer.buf, world);
     // agreement: the minimum of the ranks' flags
     DevBuf<double> flag;
     flag.alloc(1);
@@ -688,7 +692,7 @@ void backward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
             tp.total_out = c->reduced.p; tp.n_out = 1;   // element 0 at p == 0: sum of the start-inventory values (backward NPV)
             tp.peers = c->peer.view; tp.error_flag = c->error_flag.p; tp.pdl = q.pdl;
             const int blocks = tail_blocks(n_elem, q.G, c->num_sms);
-            c->peer.next(blocks, &tp.parity, &tp.target);
+            c->peer.next(blocks, &tp.parity, &tp.target, &tp.local_target);
             static const bool tail_trace = getenv("LSMC_TAIL_TRACE") != nullptr;   // development: phase stamps of one mid-horizon tail
             DevBuf<long long> tail_tr;
             if (tail_trace && p == P / 2) { tail_tr.alloc(8); CUDA_CHECK(cudaMemsetAsync(tail_tr.p, 0, 64, s)); tp.trace = tail_tr.p; }
@@ -1148,6 +1152,7 @@ int lsmc_comm_init_local(lsmc_ctx** ctxs, int n) {
             PeerView v{};
             v.rank = r; v.world = n;
             for (int o = 0; o < n; o++) { v.slots[o] = ctxs[o]->peer.buf; v.counter[o] = ctxs[o]->peer.counter_of(ctxs[o]->peer.buf, n); }
+            v.ticket = ctxs[r]->peer.ticket_of(ctxs[r]->peer.buf, n);
             c->peer.view = v; c->peer.ready = true;
         }
         CUDA_CHECK(cudaSetDevice(ctxs[0]->device));

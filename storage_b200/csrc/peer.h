@@ -5,7 +5,8 @@
 //     counter one 64-bit arrival counter
 // and holds device pointers to the buffers of all ranks (cudaIpc-mapped across processes, plain pointers inside one
 // process).  An exchange is: write my block into slot [parity][my rank] of EVERY rank's buffer with plain peer stores,
-// fence at system scope, add my CTA count to every rank's counter; spin until my own counter has reached the cumulative
+// fence at system scope, take a ticket on this GPU; the CTA with the last ticket adds the rank's CTA count to every rank's
+// counter (world remote atomics per rank and exchange, not CTAs x world); spin until my own counter has reached the cumulative
 // target (every CTA of every rank has arrived); sum the world blocks of my buffer in rank order.  All ranks sum the same
 // values in the same order, so the result — and the regression coefficients solved from it — is bit-identical on every
 // rank and does not depend on a collective library's ring order.  Two parities suffice: nobody can start exchange e+2
@@ -27,6 +28,7 @@ struct PeerView {
     int rank, world;
     double* slots[kMaxPeers];                 // rank r's slot array
     unsigned long long* counter[kMaxPeers];   // rank r's arrival counter
+    unsigned long long* ticket;               // this rank's own CTA ticket (device scope): the last CTA of an exchange signals the peers
 };
 
 struct TailParams {
@@ -39,6 +41,7 @@ struct TailParams {
     PeerView peers;
     int parity;                 // this exchange's slot parity
     unsigned long long target;  // cumulative arrivals at this rank's counter after this exchange
+    unsigned long long local_target;   // cumulative tickets of this rank's own CTAs after this exchange
     int* error_flag;            // set to kPeerTimeout when a spin times out
     long long* trace;           // development (LSMC_TAIL_TRACE): globaltimer stamps of CTA 0, [8]; NULL otherwise
     int pdl;                    // host side: launch with programmatic stream serialisation
@@ -55,7 +58,7 @@ struct PeerSmallParams {
     int count, root;            // root < 0: all-reduce; root >= 0: broadcast from that rank
     PeerView peers;
     int parity;
-    unsigned long long target;
+    unsigned long long target, local_target;
     int* error_flag;
 };
 void launch_peer_small(const PeerSmallParams& pp, cudaStream_t stream);

@@ -85,32 +85,23 @@ __device__ __forceinline__ void solve_factor(const SolveParams& sp, double* sm, 
         }
         __syncthreads();
     }
-    // scaling: l_jj = sqrt(pivot_j), l_ij = a_ij / l_jj; a dropped column becomes the unit column
+    // scaling in two passes: rs_j = 1 / sqrt(pivot_j) (0 for a dropped column, which becomes the unit column), then
+    // l_ij = a_ij rs_j, l_jj = pivot_j rs_j, 1 / l_jj = rs_j
     for (int j = tid; j < K; j += nthr) {
         const double piv = A[j * K + j];
         const bool dj = dropped[j] != 0 || !(piv > sp.pivot_tol);
-        invd[j] = dj ? 1.0 : rsqrt(piv);
+        dropped[j] = dj ? 1 : 0;
+        invd[j] = dj ? 0.0 : rsqrt(piv);
     }
     __syncthreads();
-    for (int j = tid; j < K; j += nthr) {
-        const double piv = A[j * K + j];
-        if (dropped[j] != 0 || !(piv > sp.pivot_tol)) dropped[j] = 1;
-    }
     for (int e = tid; e < K * K; e += nthr) {
         const int i = e / K, j = e - i * K;
         if (j > i) continue;
-        const double piv = A[j * K + j];
-        const bool dj = !(piv > sp.pivot_tol) || dropped[j] != 0;   // dropped[] of column j may already carry this step's verdict: same value
-        if (i == j) continue;
-        A[e] = dj ? 0.0 : A[e] * invd[j];
+        const double rs = invd[j];
+        A[e] = (i == j) ? (rs == 0.0 ? 1.0 : A[e] * rs) : A[e] * rs;
     }
     __syncthreads();
-    for (int j = tid; j < K; j += nthr) {
-        const double piv = A[j * K + j];
-        A[j * K + j] = dropped[j] ? 1.0 : sqrt(piv);
-    }
-    __syncthreads();
-    for (int j = tid; j < K; j += nthr) invd[j] = 1.0 / A[j * K + j];
+    for (int j = tid; j < K; j += nthr) if (invd[j] == 0.0) invd[j] = 1.0;
     __syncthreads();
 }
 
@@ -226,33 +217,46 @@ __device__ __forceinline__ void solve_cta_warps(const SolveParams& sp, const Red
         }
 #pragma unroll 1
         for (int pass = 0; pass < 2; pass++) {
+            // Both substitutions in "unit diagonal" form: the column (row) of L is scaled by 1 / l_jj when it is applied, so the value
+            // that travels down the dependency chain is the lane's running right-hand side itself — one shuffle and one FMA per
+            // step — and the division by the diagonal happens once per lane after the loop.
             double b[R], y[R];
 #pragma unroll
-            for (int q = 0; q < R; q++) { b[q] = r[q] * sc[q]; y[q] = 0.0; }
+            for (int q = 0; q < R; q++) b[q] = r[q] * sc[q];
             // L y = D r, column by column
 #pragma unroll
-            for (int qj = 0; qj < R; qj++)
+            for (int qj = 0; qj < R; qj++) {
+#pragma unroll 4
                 for (int j = 32 * qj; j < min(K, 32 * qj + 32); j++) {
-                    const double yj = __shfl_sync(0xffffffffu, dr[qj] ? 0.0 : b[qj] * iv[qj], j & 31);
+                    const double zj = __shfl_sync(0xffffffffu, dr[qj] ? 0.0 : b[qj], j & 31);
+                    const double ivj = invd[j];
 #pragma unroll
                     for (int q = 0; q < R; q++) {
                         const int k = lane + 32 * q;
-                        if (k == j) y[q] = yj;
-                        else if (k > j && k < K) b[q] -= A[k * K + j] * yj;
+                        const double lkj = (k > j && k < K) ? A[k * K + j] * ivj : 0.0;
+                        b[q] = fma(-lkj, zj, b[q]);
                     }
                 }
+            }
+#pragma unroll
+            for (int q = 0; q < R; q++) y[q] = dr[q] ? 0.0 : b[q] * iv[q];
             // L^T z = y, from the last column up; z overwrites y
 #pragma unroll
-            for (int qj = R - 1; qj >= 0; qj--)
+            for (int qj = R - 1; qj >= 0; qj--) {
+#pragma unroll 4
                 for (int j = min(K, 32 * qj + 32) - 1; j >= 32 * qj; j--) {
-                    const double zj = __shfl_sync(0xffffffffu, dr[qj] ? 0.0 : y[qj] * iv[qj], j & 31);
+                    const double wj = __shfl_sync(0xffffffffu, dr[qj] ? 0.0 : y[qj], j & 31);
+                    const double ivj = invd[j];
 #pragma unroll
                     for (int q = 0; q < R; q++) {
                         const int k = lane + 32 * q;
-                        if (k == j) y[q] = zj;
-                        else if (k < j) y[q] -= A[j * K + k] * zj;
+                        const double ljk = (k < j) ? A[j * K + k] * ivj : 0.0;
+                        y[q] = fma(-ljk, wj, y[q]);
                     }
                 }
+            }
+#pragma unroll
+            for (int q = 0; q < R; q++) y[q] = dr[q] ? 0.0 : y[q] * iv[q];
 #pragma unroll
             for (int q = 0; q < R; q++) x[q] += y[q] * sc[q];
             if (pass == 0) {   // residual of the unscaled system

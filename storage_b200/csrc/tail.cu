@@ -32,8 +32,11 @@ __device__ __forceinline__ unsigned long long ld_acquire_gpu(const unsigned long
 }
 
 // One thread per CTA: publish this CTA's slot stores, arrive everywhere, wait for everybody.  With one rank this is a plain
-// grid barrier: device scope is enough (no system-scope fence, no system-scope atomic: about 2 us less per period).
-__device__ __forceinline__ void arrive_and_wait(const PeerView& pv, unsigned long long target, int* error_flag) {
+// grid barrier: device scope is enough (no system-scope fence, no system-scope atomic: about 2 us less per period).  With
+// several ranks every CTA fences its peer stores at system scope and takes a device-scope ticket; the CTA that draws the last
+// ticket of the exchange (fence - atomic - fence: it has observed all the others' fences) adds the rank's CTA count to every
+// rank's counter.
+__device__ __forceinline__ void arrive_and_wait(const PeerView& pv, unsigned long long target, unsigned long long local_target, int* error_flag) {
     __syncthreads();   // every thread's slot stores happen-before the fence below
     if (threadIdx.x == 0) {
         const unsigned long long* mine = pv.counter[pv.rank];
@@ -46,7 +49,10 @@ __device__ __forceinline__ void arrive_and_wait(const PeerView& pv, unsigned lon
             }
         } else {
             __threadfence_system();
-            for (int r = 0; r < pv.world; r++) atomicAdd_system(pv.counter[r], 1ULL);
+            if (atomicAdd(pv.ticket, 1ULL) + 1ULL == local_target) {
+                __threadfence_system();
+                for (int r = 0; r < pv.world; r++) atomicAdd_system(pv.counter[r], (unsigned long long)gridDim.x);
+            }
             // a peer that failed or was cancelled never arrives: give up after ~2 s, and at once in every later exchange
             while (ld_acquire_sys(mine) < target) {
                 if (*reinterpret_cast<volatile int*>(error_flag) == kPeerTimeout) break;
@@ -111,7 +117,7 @@ __global__ void __launch_bounds__(kTailThreads) tail_kernel(const TailParams tp)
     }
     // ---- 2: exchange ----
     if (tr) tr[1] = gtimer();
-    arrive_and_wait(pv, tp.target, tp.error_flag);
+    arrive_and_wait(pv, tp.target, tp.local_target, tp.error_flag);
     if (tr) tr[2] = gtimer();
     const SlotRed red{pv.slots[pv.rank] + par_off, pv.world, tp.solve.ncols};
     if (blockIdx.x == 0 && (int)threadIdx.x < tp.n_out) tp.total_out[threadIdx.x] = red.at(threadIdx.x);
@@ -131,7 +137,7 @@ __global__ void __launch_bounds__(256) peer_small_kernel(const PeerSmallParams p
             const double v = pp.buf[i];
             for (int r = 0; r < pv.world; r++) pv.slots[r][par_off + (size_t)pv.rank * kPeerSlotDoubles + i] = v;
         }
-    arrive_and_wait(pv, pp.target, pp.error_flag);
+    arrive_and_wait(pv, pp.target, pp.local_target, pp.error_flag);
     const double* mine = pv.slots[pv.rank] + par_off;
     for (int i = threadIdx.x; i < pp.count; i += blockDim.x) {
         double s;

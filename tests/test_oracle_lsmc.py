@@ -150,6 +150,17 @@ def test_very_low_vol_one_factor_matches_intrinsic(storage_fn, tol):   # LSMCTes
     assert abs(res.npv / intrinsic - 1.0) < tol + 5e-4   # + the test DP's own grid error (600 pts vs the reference's exact DP)
 
 
+@pytest.mark.parametrize("storage_fn", [simple_daily_storage, ratchet_daily_storage])
+def test_zero_mean_reversion_one_factor_is_within_4_percent_of_intrinsic(storage_fn):   # LSMCTest:527-565 (degree-5 basis, 4 %)
+    basis = "1 + x0 + x0**2 + x0**3 + x0**4 + x0**5"   # Ones + AllMarkovFactorAllPositiveIntegerPowersUpTo(5, 1)
+    pb = reference_problem(storage=storage_fn(), num_sims=1000, mean_reversion=0.0, basis=basis)
+    res = run(pb).results
+    from storage_b200 import _native
+    intrinsic, _ = _native.intrinsic(pb)   # IntrinsicStorageValuation restated on the host (pinned bit for bit: tests/test_intrinsic.py)
+    assert abs(intrinsic / intrinsic_value(pb, 100) - 1.0) < 5e-3   # and the test's own coarse DP agrees with it
+    assert res.npv > 0.0 and abs(res.npv / intrinsic - 1.0) < 0.04
+
+
 def test_forced_inject_and_withdraw_npv_equals_the_schedule_valued_on_the_forward_curve():   # LSMCTest:686-837
     pb, expected = forced_inject_withdraw_problem(num_sims=1_000)
     res = run(pb, seed=11, fwd_seed=22).results
