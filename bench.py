@@ -111,9 +111,9 @@ def measured_peak_gbs():
 
 def ncu_traffic(config, n_local):
     """dram__bytes_read.sum + dram__bytes_write.sum per sweep launch from the committed `ncu --set full` capture of this
-    workload (profiles/r01_sweep4_traffic.json); None when no capture exists for the configuration being run."""
+    workload (profiles/r02_sweep4_traffic.json); None when no capture exists for the configuration being run."""
     try:
-        with open(os.path.join(ROOT, "profiles", "r01_sweep4_traffic.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "r02_sweep4_traffic.json")) as f:
             for row in json.load(f)["captures"]:
                 if row["config"] == config and int(row["paths_per_gpu"]) == int(n_local):
                     return float(row["dram_bytes_per_launch"])

@@ -21,7 +21,7 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-fi
 echo "launch list exit $?"
 ncu --set full --clock-control none --import-source on -k regex:"sweep4_kernel" -s 200 -c 1 -o $OUT/sweep4_$TAG -f $CMD > $OUT/ncu_sweep_$TAG.log 2>&1
 echo "sweep capture exit $?"
-ncu --set full --clock-control none --import-source on -k regex:"forward2_kernel|forward_fast_kernel|simulate_pair_kernel|tail_kernel" -s 1 -c 3 -o $OUT/fwdsim_$TAG -f $CMD > $OUT/ncu_fwdsim_$TAG.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:"forward2_kernel|simulate_pair_kernel" -c 3 -o $OUT/fwdsim_$TAG -f $CMD > $OUT/ncu_fwdsim_$TAG.log 2>&1
 echo "fwd/sim capture exit $?"
 CMD4="python bench.py --config c4 --steps 1 --warmup 1 --no-cpu-baseline --no-parity --no-panels --paths-total 131072"
 $CMD4 > $OUT/plain_c4_$TAG.log 2>&1 &&

@@ -414,6 +414,26 @@ def test_backward_refuses_factors_of_the_valuation_set(ctx):
     assert ctx.get_results().npv == first.npv
 
 
+def test_kernel_timing_serialises_the_backward_kernels_without_changing_a_bit(ctx):
+    """lsmc_set_kernel_timing puts a CUDA event on either side of every sweep launch, which serialises kernels that otherwise
+    overlap by programmatic dependent launch (set-up of a kernel under the tail of its predecessor): a read of a predecessor's
+    result placed before the dependency wait would show up as a difference between the two modes.  Few paths, so that the
+    grids are smaller than the GPU and several kernels of the chain are resident at once."""
+    pb = build_config("c3", num_sims=2048)
+    free = ctx.calculate(pb, Rng.philox(5), Rng.philox(6), panels=("inject_withdraw",))
+    assert ctx.timings()["backward_sweep_kernel_ms"] == 0.0
+    ctx.set_kernel_timing(True)
+    try:
+        timed = ctx.calculate(pb, Rng.philox(5), Rng.philox(6), panels=("inject_withdraw",))
+        tm = ctx.timings()
+    finally:
+        ctx.set_kernel_timing(False)
+    assert tm["backward_sweep_kernel_ms"] > 0.0 and tm["backward_sweep_launches"] == pb.n_periods
+    assert timed.npv == free.npv and timed.npv_std_error == free.npv_std_error
+    assert np.array_equal(timed.deltas, free.deltas) and np.array_equal(timed.inject_withdraw, free.inject_withdraw)
+    assert np.array_equal(timed.trigger_summary, free.trigger_summary, equal_nan=True)
+
+
 def test_smoke_entry_point():
     import __graft_entry__
     __graft_entry__.smoke()
