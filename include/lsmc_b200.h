@@ -53,7 +53,12 @@ enum {
 enum {
     LSMC_RNG_PHILOX = 0,    /* device Philox4x32-10 + Box-Muller */
     LSMC_RNG_NORMALS = 1,   /* caller-injected standard normals (parity mode) */
-    LSMC_RNG_PANELS = 2     /* caller-injected spot/factor panels (e.g. from Cmdty.Core's own simulator) */
+    LSMC_RNG_PANELS = 2,    /* caller-injected spot/factor panels (e.g. from Cmdty.Core's own simulator) */
+    LSMC_RNG_MT19937 = 3,   /* the reference's seeded stream (LsmcValuationParameters.cs:181-191: MersenneTwisterGenerator(seed,
+                               antithetic)): MathNet MT19937 + Normal.Samples, one generator call per path, generated serially on
+                               the host (csrc/mt19937.h) and injected; reproduces the reference's seeded golden values */
+    LSMC_RNG_MT19937_CONTINUE = 4   /* the same generator continues after the context's previous MT19937 simulation
+                                       (LVP.cs:186-187: valuationSimSeed == null) */
 };
 
 /*
@@ -122,7 +127,7 @@ typedef struct lsmc_problem {
 typedef struct lsmc_rng {
     int32_t mode;             /* LSMC_RNG_* */
     int32_t antithetic;       /* Philox mode: global paths 2m and 2m+1 share draw m with opposite signs */
-    uint64_t seed;            /* Philox key */
+    uint64_t seed;            /* Philox key; MT19937: the low 32 bits are MathNet's int seed */
     const double* normals;    /* LSMC_RNG_NORMALS: [S][F][N] standard normals, S = simulated periods */
     const double* spot;       /* LSMC_RNG_PANELS: [S][N] */
     const double* factors;    /* LSMC_RNG_PANELS: [S][F][N] */
@@ -225,6 +230,9 @@ int lsmc_simulate(lsmc_ctx* ctx, int set /*0 regression, 1 valuation*/, const ls
 int lsmc_backward(lsmc_ctx* ctx, lsmc_progress_cb progress, void* progress_user);
 int lsmc_forward(lsmc_ctx* ctx, lsmc_progress_cb progress, void* progress_user);
 int lsmc_get_results(lsmc_ctx* ctx, lsmc_results* results);             /* D2H of whatever is non-NULL */
+/* The standard normals LSMC_RNG_MT19937 injects for a run of n_sims paths x n_steps x n_factors, [n_steps][n_factors][n_sims]
+ * (host only, no GPU needed): what Cmdty.Core's MultiFactorSpotPriceSimulator draws from MersenneTwisterGenerator(seed, antithetic). */
+int lsmc_mt19937_normals(uint64_t seed, int antithetic, int64_t n_sims, int32_t n_steps, int32_t n_factors, double* out);
 int lsmc_get_timings(const lsmc_ctx* ctx, lsmc_timings* out);
 /* Per-launch CUDA events around every sweep kernel of the following lsmc_backward calls (fills backward_sweep_kernel_ms;
  * the reference's Stopwatches.cs has no finer counterpart).  Off by default: an event between two kernels serialises them,

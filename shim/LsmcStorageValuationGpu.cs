@@ -31,6 +31,7 @@ namespace Cmdty.Storage
         internal const int Ok = 0, EInval = 1, EConstraint = 2, ECancelled = 3, ECuda = 4, EUnsupported = 5;
         internal const int ConstraintConstant = 0, ConstraintPiecewiseLinear = 1, ConstraintStep = 2, ConstraintPolynomial = 3;
         internal const int RngPhilox = 0;
+        internal const int RngMt19937 = 3, RngMt19937Continue = 4;   // the reference's seeded stream (include/lsmc_b200.h LSMC_RNG_MT19937)
         internal const int NumTriggerVolumes = 10;
 
         [StructLayout(LayoutKind.Sequential)]
@@ -93,10 +94,17 @@ namespace Cmdty.Storage
         public int NumSims { get; }
         public ulong RegressionSeed { get; }
         public ulong ValuationSeed { get; }
+        /// <summary>True (the default): seeded runs draw the reference's own stream — MathNet MT19937 + Normal.Samples in
+        /// Cmdty.Core's draw order, generated on the host by the native library — so that the same seeds give the same numbers as
+        /// LsmcStorageValuation.Calculate on the CPU (its seeded golden NPVs come out to 1e-15).  False: the device Philox stream,
+        /// for runs with millions of paths where a serial generator would dominate.</summary>
+        public bool ReferenceCompatibleStream { get; }
+        public bool ValuationContinuesRegressionStream { get; }   // no valuation seed was given (LVP.cs:186-187)
         public IReadOnlyList<int> Devices { get; }   // CUDA device indices; more than one: paths are split over them
 
         public GpuSimulationSpec(IReadOnlyList<(double, TimeSeries<T, double>)> factors, double[,] factorCorrelations, int numSims,
-                                 ulong regressionSeed, ulong? valuationSeed = null, IReadOnlyList<int> devices = null)
+                                 ulong regressionSeed, ulong? valuationSeed = null, IReadOnlyList<int> devices = null,
+                                 bool referenceCompatibleStream = true)
         {
             if (factors == null || factors.Count == 0) throw new ArgumentException("factors cannot be empty.", nameof(factors));
             if (factorCorrelations.GetLength(0) != factors.Count || factorCorrelations.GetLength(1) != factors.Count)
@@ -107,6 +115,8 @@ namespace Cmdty.Storage
             // no valuation seed: the reference continues the regression generator's stream (LVP.cs:187-189); with a
             // counter-based generator that is a distinct key derived from the same seed
             ValuationSeed = valuationSeed ?? unchecked(regressionSeed + 0x9E3779B97F4A7C15UL);
+            ValuationContinuesRegressionStream = valuationSeed == null;
+            ReferenceCompatibleStream = referenceCompatibleStream;
             Devices = devices ?? new[] { 0 };
         }
     }
@@ -305,8 +315,11 @@ namespace Cmdty.Storage
                     };
                     for (int i = 0; i < 4; i++) problem.terminal_coef[i] = terminal[i];
                     // antithetic = 1: the reference always constructs MersenneTwisterGenerator(seed, antithetic: true) (LVP.cs:185-189)
-                    var regressionRng = new LsmcNative.Rng { mode = LsmcNative.RngPhilox, antithetic = 1, seed = sim.RegressionSeed };
-                    var valuationRng = new LsmcNative.Rng { mode = LsmcNative.RngPhilox, antithetic = 1, seed = sim.ValuationSeed };
+                    var regressionRng = new LsmcNative.Rng { mode = sim.ReferenceCompatibleStream ? LsmcNative.RngMt19937 : LsmcNative.RngPhilox,
+                                                             antithetic = 1, seed = sim.RegressionSeed };
+                    var valuationRng = new LsmcNative.Rng { antithetic = 1, seed = sim.ValuationSeed,
+                        mode = !sim.ReferenceCompatibleStream ? LsmcNative.RngPhilox
+                             : sim.ValuationContinuesRegressionStream ? LsmcNative.RngMt19937Continue : LsmcNative.RngMt19937 };
                     var results = new LsmcNative.Results
                     {
                         struct_size = sizeof(LsmcNative.Results), deltas = pDeltas, profile = pProfile, trigger_summary = pTrigSum,

@@ -7,7 +7,7 @@ import numpy as np
 
 LSMC_OK, LSMC_EINVAL, LSMC_ECONSTRAINT, LSMC_ECANCELLED, LSMC_ECUDA, LSMC_EUNSUPPORTED = range(6)
 CONSTRAINT_CONSTANT, CONSTRAINT_PIECEWISE_LINEAR, CONSTRAINT_STEP, CONSTRAINT_POLYNOMIAL = 0, 1, 2, 3
-RNG_PHILOX, RNG_NORMALS, RNG_PANELS = 0, 1, 2
+RNG_PHILOX, RNG_NORMALS, RNG_PANELS, RNG_MT19937, RNG_MT19937_CONTINUE = 0, 1, 2, 3, 4
 MAX_FACTORS, MAX_BASIS, NUM_TRIGGER_VOLUMES = 8, 64, 10
 
 _dp = C.POINTER(C.c_double)
@@ -167,6 +167,16 @@ class Rng:
     @staticmethod
     def philox(seed, antithetic=True):
         return Rng(RNG_PHILOX, seed, antithetic)
+
+    @staticmethod
+    def mt19937(seed, antithetic=True):
+        """The reference's seeded stream: MersenneTwisterGenerator(seed, antithetic) of LsmcValuationParameters.cs:181-191."""
+        return Rng(RNG_MT19937, int(seed) & 0xFFFFFFFF, antithetic)
+
+    @staticmethod
+    def mt19937_continue(antithetic=True):
+        """The generator of the context's previous MT19937 simulation continues (LVP.cs:186-187: valuationSimSeed == null)."""
+        return Rng(RNG_MT19937_CONTINUE, 0, antithetic)
 
     @staticmethod
     def from_normals(normals):

@@ -16,7 +16,7 @@ EXPORTS = (
     "lsmc_version", "lsmc_create", "lsmc_destroy", "lsmc_last_error", "lsmc_comm_unique_id", "lsmc_comm_init", "lsmc_comm_init_local",
     "lsmc_calculate_multi", "lsmc_intrinsic", "lsmc_host_alloc", "lsmc_host_free",
     "lsmc_calculate", "lsmc_set_problem", "lsmc_get_layout", "lsmc_request_outputs", "lsmc_simulate", "lsmc_backward",
-    "lsmc_forward", "lsmc_get_results", "lsmc_get_timings", "lsmc_set_kernel_timing", "lsmc_get_grid", "lsmc_get_inventory_space",
+    "lsmc_forward", "lsmc_get_results", "lsmc_get_timings", "lsmc_set_kernel_timing", "lsmc_mt19937_normals", "lsmc_get_grid", "lsmc_get_inventory_space",
     "lsmc_get_regression_coeffs", "lsmc_get_sim_panel", "lsmc_debug_set_regression_coeffs", "lsmc_debug_keep_values",
     "lsmc_debug_get_values", "lsmc_npv_stats_noalloc",
 )
@@ -242,6 +242,19 @@ def intrinsic(problem):
     if rc != 0:
         raise LsmcError(rc, lib().lsmc_last_error(None).decode())
     return npv.value, profile
+
+
+def mt19937_normals(seed, antithetic, n_sims, n_steps, n_factors):
+    """lsmc_mt19937_normals: the standard normals of the reference's seeded stream, [n_steps][n_factors][n_sims] (host only)."""
+    out = np.zeros((int(n_steps), int(n_factors), int(n_sims)))
+    fn = lib().lsmc_mt19937_normals
+    fn.argtypes = [C.c_uint64, C.c_int, C.c_int64, C.c_int32, C.c_int32, C.c_void_p]
+    fn.restype = C.c_int
+    rc = fn(C.c_uint64(int(seed) & 0xFFFFFFFF), C.c_int(1 if antithetic else 0), C.c_int64(int(n_sims)), C.c_int32(int(n_steps)),
+            C.c_int32(int(n_factors)), out.ctypes.data_as(C.c_void_p))
+    if rc != 0:
+        raise LsmcError(rc, "lsmc_mt19937_normals: invalid argument")
+    return out
 
 
 class Group:

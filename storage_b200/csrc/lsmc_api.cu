@@ -19,6 +19,7 @@
 
 #include "host_plan.h"
 #include "kernels.h"
+#include "mt19937.h"
 #include "peer.h"
 
 using namespace lsmc;
@@ -195,6 +196,8 @@ struct lsmc_ctx {
     void* comm = nullptr;
     int rank = 0, world = 1;
     PeerComm peer;                       // exchange over peer memory (world == 1: the tail kernel's grid barrier)
+    Mt19937 mt;                          // LSMC_RNG_MT19937: the reference's seeded generator, kept so that the valuation set can continue it
+    std::vector<double> mt_normals;      // its normals for this rank's paths, [S][F][N]
     bool use_pdl = true;                 // programmatic dependent launch of the backward loop's kernels.  Off when another rank of the
                                          // group runs on the same GPU: its CTAs, parked at their dependency wait, could hold the SMs that
                                          // the other rank's kernels — which this rank's exchange is waiting for — need to become resident.
@@ -562,6 +565,18 @@ void simulate(lsmc_ctx* c, int set, const lsmc_rng* rng) {
             c->normals_stage.alloc(S * F * N);
             CUDA_CHECK(cudaMemcpyAsync(c->normals_stage.p, rng->normals, S * F * N * sizeof(double), cudaMemcpyHostToDevice, s));
             sp.normals = c->normals_stage.p;
+        } else if (rng->mode == LSMC_RNG_MT19937 || rng->mode == LSMC_RNG_MT19937_CONTINUE) {
+            // the reference's seeded stream: one serial generator walks ALL paths of the valuation (every rank of a sharded
+            // run generates the whole run and keeps its own columns), then the draws are injected like LSMC_RNG_NORMALS
+            if (rng->mode == LSMC_RNG_MT19937) c->mt.seed((uint32_t)rng->seed);
+            else require(c->mt.seeded(), LSMC_EINVAL, "LSMC_RNG_MT19937_CONTINUE needs an earlier LSMC_RNG_MT19937 simulation on this context");
+            c->mt_normals.resize(S * F * N);
+            mt19937_path_normals(c->mt, rng->antithetic != 0, c->Nglobal, pl.problem.pb.sim_offset, c->N, (int)S, (int)F, c->mt_normals.data());
+            c->normals_stage.alloc(S * F * N);
+            CUDA_CHECK(cudaMemcpyAsync(c->normals_stage.p, c->mt_normals.data(), S * F * N * sizeof(double), cudaMemcpyHostToDevice, s));
+            CUDA_CHECK(cudaStreamSynchronize(s));   // pageable source
+            sp.mode = LSMC_RNG_NORMALS;
+            sp.normals = c->normals_stage.p;
         } else require(rng->mode == LSMC_RNG_PHILOX, LSMC_EINVAL, "unknown rng mode");
         sp.decay = c->s_decay.p; sp.chol = c->s_chol.p; sp.vol = c->s_vol.p; sp.drift = c->s_drift.p; sp.fwd = c->s_fwd.p;
         sp.spot = c->spot[set].p; sp.fac = c->fac.p;
@@ -580,7 +595,7 @@ void simulate(lsmc_ctx* c, int set, const lsmc_rng* rng) {
         c->broadcast0(c->precond.p, (size_t)pl.S * precond_stride(pl.K));
     }
     HOST_TRACE(c, set == 0 ? "simulate 0: launched" : "simulate 1: launched");
-    if (set == 1) c->valuation_antithetic = (rng->mode == LSMC_RNG_PHILOX && rng->antithetic) ? 1 : 0;
+    if (set == 1) c->valuation_antithetic = ((rng->mode == LSMC_RNG_PHILOX || rng->mode == LSMC_RNG_MT19937 || rng->mode == LSMC_RNG_MT19937_CONTINUE) && rng->antithetic) ? 1 : 0;
     CUDA_CHECK(cudaEventRecord(c->event(set == 0 ? 1 : 5), s));
     c->sims_ready[set] = true;
     c->fac_set = set;
@@ -1283,7 +1298,8 @@ static int calculate_impl(lsmc_ctx* ctx, const lsmc_problem* problem, const lsmc
         // every allocation the passes below would make lazily: no cudaMalloc / cudaFree (device-wide synchronisation) once
         // the ranks of a group have started to wait for each other on the device
         ctx->fwd_params.alloc((size_t)(ctx->plan.P - 1));
-        if (regression_rng->mode == LSMC_RNG_NORMALS || valuation_rng->mode == LSMC_RNG_NORMALS)
+        auto injected = [](const lsmc_rng* r) { return r->mode == LSMC_RNG_NORMALS || r->mode == LSMC_RNG_MT19937 || r->mode == LSMC_RNG_MT19937_CONTINUE; };
+        if (injected(regression_rng) || injected(valuation_rng))
             ctx->normals_stage.alloc((size_t)ctx->plan.S * ctx->plan.F * (size_t)ctx->N);
         setup_done = true;
         if (after_setup && !after_setup()) throw Error(LSMC_ECANCELLED, "Another GPU of the group failed during set-up.");
@@ -1325,6 +1341,14 @@ int lsmc_intrinsic(const lsmc_problem* problem, double* npv, double* profile) {
 int lsmc_get_timings(const lsmc_ctx* ctx, lsmc_timings* out) {
     if (!ctx || !out) return LSMC_EINVAL;
     *out = ctx->tm;
+    return LSMC_OK;
+}
+
+int lsmc_mt19937_normals(uint64_t seed, int antithetic, int64_t n_sims, int32_t n_steps, int32_t n_factors, double* out) {
+    if (!out || n_sims < 1 || n_steps < 1 || n_factors < 1) return LSMC_EINVAL;
+    Mt19937 g;
+    g.seed((uint32_t)seed);
+    mt19937_path_normals(g, antithetic != 0, n_sims, 0, n_sims, n_steps, n_factors, out);
     return LSMC_OK;
 }
 

@@ -102,6 +102,24 @@ def _seeds(seed, fwd_sim_seed):
     return seed, fwd
 
 
+# Which draw stream a SEEDED call uses.  "mt19937": the reference's own (MathNet MT19937 + Normal.Samples, generated serially
+# on the host, csrc/mt19937.h): the same seed gives the reference's numbers (its golden NPVs 1780380.7581833513 and
+# 1766460.137569665 to about 1e-12, test_multi_factor.py:226,298).  "philox": the device stream, for seeded runs with
+# millions of paths where a serial host generator (about 15 ns per normal) would dominate.  Unseeded calls always use Philox.
+SEEDED_RNG = "mt19937"
+
+
+def _rngs(seed, fwd_sim_seed):
+    """multi_factor.py:436-440 / LVP.cs:181-191: regression generator from `seed`; the valuation generator is a new one from
+    `fwd_sim_seed`, or the regression generator continuing its sequence when that is None."""
+    if seed is None or SEEDED_RNG != "mt19937":
+        reg_seed, val_seed = _seeds(seed, fwd_sim_seed)
+        return _abi.Rng.philox(reg_seed, antithetic=True), _abi.Rng.philox(val_seed, antithetic=True)
+    reg = _abi.Rng.mt19937(seed, antithetic=True)
+    val = _abi.Rng.mt19937_continue(antithetic=True) if fwd_sim_seed is None else _abi.Rng.mt19937(fwd_sim_seed, antithetic=True)
+    return reg, val
+
+
 def three_factor_seasonal_value(cmdty_storage: CmdtyStorage,
                                 val_date: utils.TimePeriodSpecType,
                                 inventory: float,
@@ -191,12 +209,11 @@ def _lsmc_calc(cmdty_storage, fwd_curve, interest_rates, inventory, factors, fac
     logger.info('Calculating intrinsic value.')
     intrinsic = intrinsic_of_problem(problem)
     logger.info('Calculation of intrinsic value complete.')
-    reg_seed, val_seed = _seeds(seed, fwd_sim_seed)
+    reg_rng, val_rng = _rngs(seed, fwd_sim_seed)
     panels = "all" if RETURN_SIM_PANELS else ()
     logger.info('Calculating LSMC value.')
     with _native.Context(DEVICE) as ctx:
-        res = ctx.calculate(problem, _abi.Rng.philox(reg_seed, antithetic=True), _abi.Rng.philox(val_seed, antithetic=True),
-                            panels=panels, on_progress=on_progress_update)
+        res = ctx.calculate(problem, reg_rng, val_rng, panels=panels, on_progress=on_progress_update)
         timings = ctx.timings()
     logger.info('Calculation of LSMC value complete.')
     logger.info('device ms: regression sim %.2f, backward %.2f, valuation sim %.2f, forward %.2f',
@@ -244,6 +261,7 @@ class MultiFactorSpotSim:
             raise ValueError("sim_periods cannot be empty.")
         self._current = pd.Timestamp(current_date.start_time if isinstance(current_date, pd.Period) else current_date)
         self._fwd = fwd_curve
+        self._given_seed = seed
         self._seed, _ = _seeds(seed, None)
         self._antithetic = bool(antithetic)
         self._calls = 0
@@ -269,7 +287,16 @@ class MultiFactorSpotSim:
         with _native.Context(DEVICE) as ctx:
             ctx.set_problem(pb)
             # successive calls continue the stream like one MersenneTwisterGenerator instance would
-            ctx.simulate(0, _abi.Rng.philox((self._seed + self._calls) & 0xFFFFFFFFFFFFFFFF, antithetic=self._antithetic))
+            if self._given_seed is not None and SEEDED_RNG == "mt19937":
+                # the reference's stream; successive calls continue it like one MersenneTwisterGenerator instance
+                if self._calls == 0:
+                    self._sims_drawn = 0
+                # (the dummy terminal period of the problem below is not part of the reference's draw: S steps, padded with zeros)
+                z = _native.mt19937_normals(self._given_seed, self._antithetic, self._sims_drawn + int(num_sims), S, F)[:, :, self._sims_drawn:]
+                self._sims_drawn += int(num_sims)
+                ctx.simulate(0, _abi.Rng.from_normals(np.ascontiguousarray(np.concatenate([z, np.zeros((1, F, int(num_sims)))]))))
+            else:
+                ctx.simulate(0, _abi.Rng.philox((self._seed + self._calls) & 0xFFFFFFFFFFFFFFFF, antithetic=self._antithetic))
             spot = ctx.sim_panel(0)
         self._calls += 1
         return pd.DataFrame(data=spot[:S], index=self._periods)

@@ -2,8 +2,10 @@
 (multi_factor_value, three_factor_seasonal_value, MultiFactorSpotSim; src/Cmdty.Storage.Python/cmdty_storage/
 multi_factor.py:49-92,324-455), run on the GPU and held to the reference's own wrapper tests
 (src/Cmdty.Storage.Python/tests/test_multi_factor.py:167-311): result shapes, 123 deltas, 245 progress calls, the golden
-intrinsic NPV, and the seeded LSMC NPVs 1780380.76 / 1766460.14 as Monte-Carlo bands (they are functions of MathNet's
-MT19937 stream, which is not reproduced: DESIGN.md 3).  The same valuation through the CPU oracle must agree to 1e-9."""
+intrinsic NPV, and the SEEDED LSMC NPVs 1780380.7581833513 / 1766460.137569665 — seeded calls draw the reference's own stream
+(LSMC_RNG_MT19937: MathNet MT19937 + Normal.Samples in Cmdty.Core's draw order, csrc/mt19937.h), which the CPU oracle turns into
+those numbers bit for bit (tests/test_reference_goldens.py) and the device path to 1e-9 or better (its regression solves
+preconditioned normal equations instead of a Householder QR).  The twelve seeded spot prices of the simulator test too."""
 import numpy as np
 import pandas as pd
 import pytest
@@ -45,11 +47,14 @@ def test_multi_factor_value_regression():   # test_multi_factor.py:167-239
                                           '1 + x0 + x0**2 + x1 + x1*x1', False, seed=SEED, fwd_sim_seed=SEED,
                                           on_progress_update=progresses.append)
     check_result_structure(res, progresses)
-    assert abs(res.npv / 1780380.7581833513 - 1.0) < 0.03        # the reference's seeded value (:226), as a Monte-Carlo band
-    # the same flattened problem and Philox seeds through the CPU oracle
+    print("multi_factor_value: npv %.10f, relative to the reference's golden value %.3e" % (res.npv, res.npv / 1780380.7581833513 - 1.0))
+    assert round(res.npv - 1780380.7581833513, 6) == 0           # the reference's own assertion (:226, assertAlmostEqual places=6)
+    # the same flattened problem and draws through the CPU oracle
     pb = flatten_problem(storage, VAL_DATE, 0.0, fwd, rates, twentieth_of_next_month, factors, np.array([[1.0, 0.64], [0.64, 1.0]]),
                          NUM_SIMS, '1 + x0 + x0**2 + x1 + x1*x1', False)
-    ref = oracle.calculate(pb, Rng.philox(SEED), Rng.philox(SEED)).results
+    z = storage_b200._native.mt19937_normals(SEED, True, NUM_SIMS, pb.n_sim_periods, pb.n_factors)
+    ref = oracle.calculate(pb, Rng.from_normals(z), Rng.from_normals(z)).results
+    assert ref.npv == 1780380.7581833513
     assert abs(res.npv / ref.npv - 1.0) < 1e-9
     assert np.max(np.abs(res.deltas.values - ref.deltas)) < 1e-9 * np.max(np.abs(ref.deltas))
     assert np.max(np.abs(res.expected_profile.values - ref.profile)) < 1e-9 * np.max(np.abs(ref.profile))
@@ -62,7 +67,49 @@ def test_three_factor_seasonal_regression():   # test_multi_factor.py:241-311
                                                    NUM_SIMS, '1 + x_st + x_sw + x_lt + x_st**2 + x_sw**2 + x_lt**2', False,
                                                    seed=SEED, fwd_sim_seed=SEED, on_progress_update=progresses.append)
     check_result_structure(res, progresses)
-    assert abs(res.npv / 1766460.137569665 - 1.0) < 0.03         # :298
+    print("three_factor_seasonal_value: npv %.10f, relative to the reference's golden value %.3e" % (res.npv, res.npv / 1766460.137569665 - 1.0))
+    assert round(res.npv - 1766460.137569665, 6) == 0            # the reference's own assertion (:298, places=6)
+
+
+def test_seeded_runs_continue_the_regression_generator_when_no_forward_seed_is_given():
+    """LVP.cs:186-187: valuationSimSeed == null -> the regression generator continues its sequence for the valuation set
+    (LSMC_RNG_MT19937_CONTINUE), so the two sets differ and the NPV differs from the fwd_sim_seed = seed run; Philox stays
+    available for seeded runs with very many paths (multi_factor.SEEDED_RNG)."""
+    storage, fwd, rates = wrapper_test_inputs()
+    idx = pd.period_range(VAL_DATE, '2020-06-01', freq='D')
+    factors = [(0.0, pd.Series(0.14, index=idx)), (16.2, pd.Series(1.15, index=idx))]
+    args = (storage, VAL_DATE, 0.0, fwd, rates, twentieth_of_next_month, factors, 0.64, NUM_SIMS, '1 + x0 + x0**2 + x1 + x1*x1', False)
+    cont = storage_b200.multi_factor_value(*args, seed=SEED)
+    pb = flatten_problem(storage, VAL_DATE, 0.0, fwd, rates, twentieth_of_next_month, factors, np.array([[1.0, 0.64], [0.64, 1.0]]),
+                         NUM_SIMS, '1 + x0 + x0**2 + x1 + x1*x1', False)
+    z = storage_b200._native.mt19937_normals(SEED, True, 2 * NUM_SIMS, pb.n_sim_periods, pb.n_factors)   # one generator, 2 x 500 calls
+    ref = oracle.calculate(pb, Rng.from_normals(np.ascontiguousarray(z[:, :, :NUM_SIMS])), Rng.from_normals(np.ascontiguousarray(z[:, :, NUM_SIMS:]))).results
+    assert abs(cont.npv / ref.npv - 1.0) < 1e-9
+    assert not np.array_equal(cont.sim_spot_regress.values, cont.sim_spot_valuation.values)
+    assert abs(cont.npv / 1780380.7581833513 - 1.0) < 0.03 and cont.npv != 1780380.7581833513
+    multi_factor.SEEDED_RNG = "philox"
+    try:
+        dev = storage_b200.multi_factor_value(*args, seed=SEED, fwd_sim_seed=SEED)
+    finally:
+        multi_factor.SEEDED_RNG = "mt19937"
+    assert abs(dev.npv / 1780380.7581833513 - 1.0) < 0.03 and abs(dev.npv / 1780380.7581833513 - 1.0) > 1e-9
+
+
+def test_seeded_spot_prices_of_the_reference_simulator_on_the_device():   # test_multi_factor.py:34-91
+    from datetime import date
+    factors = [(0.0, {date(2020, 8, 1): 0.35, '2021-01-15': 0.29, date(2021, 7, 30): 0.32}),
+               (2.5, pd.Series(data=[0.15, 0.18, 0.21], index=pd.PeriodIndex(data=['2020-08-01', '2021-01-15', '2021-07-30'], freq='D'))),
+               (16.2, {date(2020, 8, 1): 0.95, '2021-01-15': 0.92, date(2021, 7, 30): 0.89})]
+    corrs = np.array([[1.0, 0.6, 0.3], [0.6, 1.0, 0.4], [0.3, 0.4, 1.0]])
+    fwd_curve = {'2020-08-01': 56.85, pd.Period('2021-01-15', freq='D'): 59.08, date(2021, 7, 30): 62.453}
+    sim = multi_factor.MultiFactorSpotSim('D', factors, corrs, date(2020, 7, 27), fwd_curve,
+                                          [pd.Period('2020-08-01'), '2021-01-15', date(2021, 7, 30)], 12)
+    spots = sim.simulate(4)
+    golden = np.array([[52.59976397688973, 46.1206448628463, 58.15838580682589, 65.500441945042979],
+                       [57.559631642935514, 72.0381089486175, 82.49607173562342, 42.812676607997183],
+                       [89.40526992772634, 85.18869803117379, 138.68587285875978, 76.586790647813046]])
+    assert spots.shape == (3, 4)
+    assert np.max(np.abs(spots.values / golden - 1.0)) < 4e-16 and int((spots.values == golden).sum()) >= 11
 
 
 def test_wrapper_validates_like_the_reference():
