@@ -149,3 +149,26 @@ def test_multi_factor_spot_sim_shapes_mean_and_variance():   # multi_factor.py:4
     assert np.allclose(np.log(spots.values).var(axis=1), var, rtol=0.05)
     again = multi_factor.MultiFactorSpotSim('D', [(12.0, vol)], None, '2020-08-01', fwd, sim_periods, seed=12, antithetic=True).simulate(n)
     assert np.array_equal(again.values, spots.values)                                # seeded: reproducible
+
+
+def test_readme_and_notebook_values_through_the_wrappers_on_the_device():
+    """README.md:137-173 and samples/python/multifactor_storage.ipynb cells 21-31, called exactly as written there (the printed numbers
+    are those of the notebook's injection / withdrawal costs 0.1 / 0.25: tests/test_reference_goldens.py)."""
+    from test_reference_goldens import readme_inputs
+    storage, fwd, rates = readme_inputs(0.1, 0.25)
+
+    def settlement_rule(delivery_date):
+        return delivery_date.asfreq('M').asfreq('D', 'end') + 20
+    basis = '1 + x_st + x_sw + x_lt + s + x_st**2 + x_sw**2 + x_lt**2 + s**2 + s * x_st'
+    readme = storage_b200.three_factor_seasonal_value(cmdty_storage=storage, val_date='2021-04-25', inventory=1500.0, fwd_curve=fwd,
+                                                      interest_rates=rates, settlement_rule=settlement_rule, num_sims=2000, seed=12,
+                                                      spot_mean_reversion=91.0, spot_vol=0.85, long_term_vol=0.30, seasonal_vol=0.19,
+                                                      basis_funcs=basis, discount_deltas=True)
+    assert '{0:,.0f}'.format(readme.npv) == '69,496'                # README.md:171
+    assert '{0:,.0f}'.format(readme.intrinsic_npv) == '38,446'      # :172
+    assert '{0:,.0f}'.format(readme.extrinsic_npv) == '31,049'      # :173
+    notebook = storage_b200.three_factor_seasonal_value(cmdty_storage=storage, val_date='2021-04-25', inventory=1500.0, fwd_curve=fwd,
+                                                        interest_rates=rates, settlement_rule=settlement_rule, discount_deltas=True,
+                                                        num_sims=500, seed=12, fwd_sim_seed=25, spot_mean_reversion=91.0, spot_vol=0.85,
+                                                        long_term_vol=0.30, seasonal_vol=0.19, basis_funcs=basis)
+    assert '{0:,.0f}'.format(notebook.npv) == '69,524' and '{0:,.0f}'.format(notebook.extrinsic_npv) == '31,078'   # notebook cells 21, 31

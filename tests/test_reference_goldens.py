@@ -99,3 +99,51 @@ def test_product_generator_equals_the_test_side_restatement():
         got = _native.mt19937_normals(seed, anti, n, s, f)
         want, _ = mt19937_ref.path_normals(seed, anti, n, s, f)
         assert np.array_equal(got, want), (seed, anti, n, s, f)
+
+
+# ---- the values the reference PRINTS for its ratchet storage (README.md:168-173, samples/python/multifactor_storage.ipynb cells 21-31) --------
+def readme_inputs(injection_cost, withdrawal_cost):   # README.md:104-163 / notebook cells 4-19
+    from storage_b200 import RatchetInterp
+    storage = CmdtyStorage(freq='D', storage_start='2021-04-01', storage_end='2022-04-01', injection_cost=injection_cost, withdrawal_cost=withdrawal_cost,
+                           ratchets=[('2021-04-01', [(0.0, -150.0, 250.0), (2000.0, -200.0, 175.0), (5000.0, -260.0, 155.0), (7000.0, -275.0, 132.0)]),
+                                     ('2022-10-01', [(0.0, -130.0, 260.0), (2000.0, -190.0, 190.0), (5000.0, -230.0, 165.0), (7000.0, -245.0, 148.0)])],
+                           ratchet_interp=RatchetInterp.LINEAR)
+    prices = [16.61, 15.68, 15.42, 15.31, 15.27, 15.13, 15.96, 17.22, 17.32, 17.66, 17.59, 16.81, 15.36, 14.49, 14.28, 14.25, 14.32, 14.33, 15.30,
+              16.58, 16.64, 16.79, 16.64, 15.90, 14.63]
+    fwd = pd.Series(data=prices, index=pd.period_range(start='2021-04-25', periods=25, freq='M')).resample('D').ffill()
+    pillars = pd.PeriodIndex(freq='D', data=['2021-04-25', '2021-06-01', '2021-08-01', '2021-12-01', '2022-04-01', '2022-12-01', '2023-12-01'])
+    rates = pd.Series(data=[0.005, 0.006, 0.0072, 0.0087, 0.0101, 0.0115, 0.0126], index=pillars).resample('D').asfreq('D').interpolate(method='linear')
+    return storage, fwd, rates
+
+
+def test_values_printed_by_the_readme_and_the_notebook():
+    """Ratchets, injection / withdrawal costs, discounted deltas, spot price among the ten basis functions, seeds 12 and 25, and a
+    valuation set that CONTINUES the regression generator (README: no fwd_sim_seed).  The README's code block shows costs 0.01 / 0.025
+    but its printed numbers are those of the notebook's 0.1 / 0.25 (the intrinsic value, which needs no random numbers, says so)."""
+    from storage_b200 import intrinsic_value
+    storage, fwd, rates = readme_inputs(0.1, 0.25)
+    args = (storage, '2021-04-25', 1500.0, fwd, rates, twentieth_of_next_month)
+    intrinsic = intrinsic_value(*args).npv
+    assert '{0:,.0f}'.format(intrinsic) == '38,446'                                              # README.md:172, notebook cell 31
+    assert '{0:,.0f}'.format(intrinsic_value(*((readme_inputs(0.01, 0.025)[0],) + args[1:])).npv) != '38,446'
+    factors, corrs = create_3_factor_season_params('D', 91.0, 0.85, 0.30, 0.19, utils.to_period('2021-04-25', 'D'), storage.end)
+    basis = '1 + x_st + x_sw + x_lt + s + x_st**2 + x_sw**2 + x_lt**2 + s**2 + s * x_st'.replace('x_st', 'x0').replace('x_lt', 'x1').replace('x_sw', 'x2')
+
+    def lsmc(factors, corrs, basis, num_sims, seed, fwd_seed):
+        pb = flatten_problem(*args, factors, corrs, num_sims, basis, True, None, 100, 1e-12)
+        S, F = pb.n_sim_periods, pb.n_factors
+        if fwd_seed is None:   # one generator, 2 x num_sims calls
+            z = _native.mt19937_normals(seed, True, 2 * num_sims, S, F)
+            zr, zv = np.ascontiguousarray(z[:, :, :num_sims]), np.ascontiguousarray(z[:, :, num_sims:])
+        else:
+            zr, zv = _native.mt19937_normals(seed, True, num_sims, S, F), _native.mt19937_normals(fwd_seed, True, num_sims, S, F)
+        return oracle.calculate(pb, Rng.from_normals(zr), Rng.from_normals(zv)).results.npv
+
+    notebook = lsmc(factors, corrs, basis, 500, 12, 25)
+    assert '{0:,.0f}'.format(notebook) == '69,524' and '{0:,.0f}'.format(notebook - intrinsic) == '31,078'     # notebook cells 21, 31
+    readme = lsmc(factors, corrs, basis, 2000, 12, None)
+    assert '{0:,.0f}'.format(readme) == '69,496' and '{0:,.0f}'.format(readme - intrinsic) == '31,049'         # README.md:171-173
+    vol = pd.Series(0.64, index=pd.period_range(start='2021-04-25', end=storage.end, freq='D'))
+    two_factor = lsmc([(16.2, vol), (0.0, vol)], np.array([[1.0, 0.64], [0.64, 1.0]]),
+                      '1 + x0 + x1 + s + x0**2 + x1**2 + s**2 + x0*x1 + x1*s + x0*s', 500, 12, 25)
+    assert '{0:,.0f}'.format(two_factor) == '63,505'                                              # notebook cell 29
