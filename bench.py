@@ -194,7 +194,30 @@ def parity_gates(ctx, config):
     gates["philox_npv_sigma"] = abs(got_p.npv - ref_p.npv) / max(ref_p.npv_std_error, 1e-300)
     # trigger prices: 1e-9 of the price scale unless the period's own formula is noisier (tests/test_gpu_parity.py); C5's first
     # half-hourly steps are (cond(X) ~ 1e14), so the gate flag only covers NPV, deltas, decisions and the 3-sigma rule
-    gates["pass"] = bool(gates["npv_rel"] < 1e-9 and gates["delta_rel"] < 1e-9 and gates["decision_flips"] == 0 and gates["philox_npv_sigma"] < 3.0)
+    # the reference's own seeded golden value (src/Cmdty.Storage.Python/tests/test_multi_factor.py:167-226: two factors, 500 sims,
+    # seed = fwd_sim_seed = 11) through the public wrapper on the device, drawing the reference's MT19937 stream
+    try:
+        import pandas as pd
+        import storage_b200
+        storage = storage_b200.CmdtyStorage('D', '2019-12-01', '2020-04-01', 1.23, 0.98, min_inventory=0.0, max_inventory=100000.0,
+                                            max_injection_rate=700.0, max_withdrawal_rate=700.0)
+        idx = pd.PeriodIndex([pd.Period(d, freq='D') for d in ['2019-08-29', '2020-03-12', '2020-04-01']])
+        fwd = pd.Series([23.87, 150.32, 150.32], idx).resample('D').ffill()
+        curve = pd.period_range('2019-08-29', '2020-06-01', freq='D')
+        rates = pd.Series(0.03, index=curve)
+        from storage_b200 import multi_factor as _mf
+        _mf.RETURN_SIM_PANELS = False
+        val = storage_b200.multi_factor_value(storage, '2019-08-29', 0.0, fwd, rates, lambda p: p.asfreq('M').asfreq('D', 'end') + 20,
+                                              [(0.0, pd.Series(0.14, index=curve)), (16.2, pd.Series(1.15, index=curve))], 0.64, 500,
+                                              '1 + x0 + x0**2 + x1 + x1*x1', False, seed=11, fwd_sim_seed=11)
+        gates["reference_golden_npv"] = {"expected": 1780380.7581833513, "got": val.npv, "rel": abs(val.npv / 1780380.7581833513 - 1.0),
+                                         "source": "test_multi_factor.py:226 (the reference asserts 6 decimal places)"}
+        golden_ok = abs(val.npv - 1780380.7581833513) < 5e-7
+    except Exception as e:
+        gates["reference_golden_npv"] = {"error": str(e)}
+        golden_ok = False
+    gates["pass"] = bool(gates["npv_rel"] < 1e-9 and gates["delta_rel"] < 1e-9 and gates["decision_flips"] == 0 and gates["philox_npv_sigma"] < 3.0
+                         and golden_ok)
     return gates
 
 
