@@ -15,7 +15,18 @@ from fixtures import (reference_problem, simple_daily_storage, ratchet_daily_sto
 
 
 def run(pb, seed=11, fwd_seed=22, **kw):
-    return oracle.calculate(pb, Rng.philox(seed), Rng.philox(fwd_seed), **kw)
+    """The reference fixture's own draws: SimulateWithMultiFactorModelAndMersenneTwister(params, NumSims, RandomSeed = 11,
+    RandomSeed * 2) (LSMCTest:49,175) — MathNet MT19937 + Normal.Samples in Cmdty.Core's order (tests/test_reference_goldens.py)."""
+    from storage_b200 import _native
+    S, F, N = pb.n_sim_periods, pb.n_factors, int(pb.n_sims)
+    if fwd_seed is None:   # no valuation seed: the regression generator continues its sequence (LVP.cs:186-187)
+        import numpy as np
+        z = _native.mt19937_normals(seed, True, 2 * N, S, F)
+        reg, val = Rng.from_normals(np.ascontiguousarray(z[:, :, :N])), Rng.from_normals(np.ascontiguousarray(z[:, :, N:]))
+    else:
+        reg = Rng.from_normals(_native.mt19937_normals(seed, True, N, S, F))
+        val = Rng.from_normals(_native.mt19937_normals(fwd_seed, True, N, S, F))
+    return oracle.calculate(pb, reg, val, **kw)
 
 
 # ---- trivial exits (LSV.cs:61-84; LSMCTest:206-267) -------------------------------------------------------------------
@@ -153,8 +164,9 @@ def test_very_low_vol_one_factor_matches_intrinsic(storage_fn, tol):   # LSMCTes
 @pytest.mark.parametrize("storage_fn", [simple_daily_storage, ratchet_daily_storage])
 def test_zero_mean_reversion_one_factor_is_within_4_percent_of_intrinsic(storage_fn):   # LSMCTest:527-565 (degree-5 basis, 4 %)
     basis = "1 + x0 + x0**2 + x0**3 + x0**4 + x0**5"   # Ones + AllMarkovFactorAllPositiveIntegerPowersUpTo(5, 1)
-    pb = reference_problem(storage=storage_fn(), num_sims=1000, mean_reversion=0.0, basis=basis)
-    res = run(pb).results
+    # exactly the reference's run: NumSims = 2000, RandomSeed = 11, no valuation seed (LSMCTest:47-49,532) -- the same draws
+    pb = reference_problem(storage=storage_fn(), num_sims=2000, mean_reversion=0.0, basis=basis)
+    res = run(pb, fwd_seed=None).results
     from storage_b200 import _native
     intrinsic, _ = _native.intrinsic(pb)   # IntrinsicStorageValuation restated on the host (pinned bit for bit: tests/test_intrinsic.py)
     assert abs(intrinsic / intrinsic_value(pb, 100) - 1.0) < 5e-3   # and the test's own coarse DP agrees with it
