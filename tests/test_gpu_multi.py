@@ -122,3 +122,19 @@ def test_two_ranks_equal_one_gpu(config, paths, comm, tmp_path):
     assert v["delta_rel"] < 1e-12 and v["profile_rel"] < 1e-12
     assert v["material_flips"] == 0 and v["decision_differences"] < 0.01 * v["decisions"]
     assert v["se_rel"] < 1e-9
+
+
+def test_sharded_valuation_on_the_reference_stream_keeps_the_golden_npv():
+    """LSMC_RNG_MT19937 under path sharding: one serial generator defines the draws of ALL paths, every rank generates the run
+    and keeps its own columns (and with _CONTINUE walks on to the end of the set).  Three ranks, 500 paths: the reference's
+    seeded golden NPV (test_multi_factor.py:226) must come out as on one GPU."""
+    from test_reference_goldens import two_factor_problem, GOLDEN_NPV_2F
+    pb = two_factor_problem()
+    devices = list(range(3)) if _cuda_device_count() >= 3 else [0] * 3
+    with _native.Group(devices) as group:
+        same_seed = group.calculate(pb, Rng.mt19937(11), Rng.mt19937(11))
+        cont = group.calculate(pb, Rng.mt19937(11), Rng.mt19937_continue())
+    assert abs(same_seed.npv - GOLDEN_NPV_2F) < 5e-7          # the reference's own 6-decimal assertion
+    with _native.Context(0) as one:
+        ref = one.calculate(pb, Rng.mt19937(11), Rng.mt19937_continue())
+    assert rel(cont.npv, ref.npv) < 1e-12 and cont.npv != same_seed.npv

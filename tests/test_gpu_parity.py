@@ -394,6 +394,23 @@ def test_error_statuses(ctx):
     assert e.value.status == _abi.LSMC_EINVAL
 
 
+def test_shapes_outside_the_device_path_are_refused_as_unsupported_not_computed(ctx):
+    """The limits include/lsmc_b200.h documents: each must surface as LSMC_EUNSUPPORTED (the shim's
+    NotSupportedException) with a message, never as a wrong number or a CUDA launch error."""
+    for kw, needle in [(dict(extra_decisions=7), "extra_decisions"),                              # more than 6 extra decisions per side
+                       (dict(num_inventory_grid_points=400), "grid")]:                             # ~200 grid rows at most
+        with pytest.raises(_native.LsmcError) as e:
+            ctx.calculate(reference_problem(num_sims=64, **kw), Rng.philox(1), Rng.philox(2))
+        assert e.value.status == _abi.LSMC_EUNSUPPORTED and needle in str(e.value)
+    with pytest.raises(_native.LsmcError) as e:                                                    # continue a generator that never ran
+        fresh = _native.Context(0)
+        try:
+            fresh.calculate(reference_problem(num_sims=64), Rng.mt19937_continue(), Rng.mt19937_continue())
+        finally:
+            fresh.close()
+    assert e.value.status == _abi.LSMC_EINVAL
+
+
 def test_backward_refuses_factors_of_the_valuation_set(ctx):
     """The factor panel is shared by both simulation sets: after the valuation set has been generated a second
     lsmc_backward would regress regression-set spot on valuation-set factors — it must be refused, not computed."""
