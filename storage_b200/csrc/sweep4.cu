@@ -61,17 +61,8 @@ __device__ __forceinline__ double2 lds128(const double* p) { return *reinterpret
 #define LSMC_STEP_UNROLL 1
 #endif
 constexpr int kStepUnroll = LSMC_STEP_UNROLL;
-#ifndef LSMC_STEP_PIPE
-#define LSMC_STEP_PIPE 0
-#endif
-#ifndef LSMC_STEP_PREFETCH
-#define LSMC_STEP_PREFETCH 0
-#endif
-// 1: weight / row offsets of the chosen decision by register selects; 0: from the warp's table in shared memory.  With the
-// rolled step loop the selects win (0.533 -> 0.518 ms); with the straight-line tile body they were a wash.
-#ifndef LSMC_SEL_REG
-#define LSMC_SEL_REG 1
-#endif
+// (Weight and row offsets of the chosen decision come from register selects; a per-warp selection table in shared memory,
+// software-pipelined and register-prefetched step loops were measured slower — DESIGN.md 4.1 — and are gone from the source.)
 #ifndef LSMC_ABLATE   // development only: timing ablations (results are wrong when != 0)
 #define LSMC_ABLATE 0
 #endif
@@ -81,19 +72,11 @@ constexpr int kStepUnroll = LSMC_STEP_UNROLL;
 #define AB_NO_FIT (LSMC_ABLATE == 6 || LSMC_ABLATE == 7 || LSMC_ABLATE == 9)
 // 13: only decision warps 0..6 decide; 14: only warps 0, 4, 8, 12 (one sub-partition) decide
 
-// Pitch of the V_next tile in paths beyond TP.  0 with the 128-bit gathers of LSMC_SEL_REG (rows 448 bytes apart alternate between the two
-// halves of the banks, like the C^ tile: conflict free); 4 with the 64-bit gathers of the selection-table variant.
-#if LSMC_SEL_REG
-constexpr int kVPad = 0;
-#else
-constexpr int kVPad = 4;
-#endif
 constexpr int kWarps = 16;
 constexpr int kDecWarps = 13;          // grid rows <= 104
 constexpr int kAuxWarps = 3;
 constexpr int kRawStages = 3;
 constexpr int kMaxProd = 32;           // product nodes of the basis program
-constexpr int kLutBytes = 4 * 128;        // 24 entries {w_lo, row_lo, row_hi} of 16 bytes, bank-conflict-free placement
 constexpr int kElemReg = 8;          // product elements per aux lane kept as register descriptors
 constexpr int kFitTiles = 6;           // C^ row blocks per fit warp (warps 14, 15; warp 13 takes the 13th)
 
@@ -101,9 +84,9 @@ __host__ __device__ inline size_t al128(size_t b) { return (b + 127) & ~(size_t)
 
 // Shared-memory carve-up in BYTES; every TMA destination is 128-byte aligned.
 struct Layout4 {
-    int GnP, MT, LDP, VP;                                 // VP: pitch of the V_next tile (TP + 4: conflict-free 64-bit gathers)
+    int GnP, MT, LDP, VP;                                 // VP: pitch of the V_next tile in paths (= TP: rows 448 bytes apart alternate bank halves, 128-bit gathers conflict free)
     size_t o_sp, o_fp, o_sm, o_fm, stage;                 // raw stage: spot_p | fac_p[F] | spot_m | fac_m[F]
-    size_t vn, vn_buf, c, raw, prod, xt, zero, ones, ones_last, lut, total;   // vn_buf: bytes of one V_next buffer
+    size_t vn, vn_buf, c, raw, prod, xt, zero, ones, ones_last, total;   // vn_buf: bytes of one V_next buffer
 };
 
 __host__ __device__ inline Layout4 layout4(int TP, int Gn, int K, int F, int n_prod) {
@@ -111,7 +94,7 @@ __host__ __device__ inline Layout4 layout4(int TP, int Gn, int K, int F, int n_p
     L.GnP = (Gn + 7) & ~7;
     L.MT = (K + 7) >> 3;
     L.LDP = TP + 4;
-    L.VP = TP + kVPad;
+    L.VP = TP;
     const size_t row = (size_t)TP * 8;
     L.o_sp = 0; L.o_fp = al128(row); L.o_sm = L.o_fp + al128(F * row); L.o_fm = L.o_sm + al128(row);
     L.stage = L.o_fm + al128(F * row);
@@ -125,7 +108,6 @@ __host__ __device__ inline Layout4 layout4(int TP, int Gn, int K, int F, int n_p
     L.zero = o; o += al128(row);
     L.ones = o; o += al128(row);
     L.ones_last = o; o += al128(row);
-    L.lut = o;  o += (size_t)kDecWarps * kLutBytes;   // per decision warp: {w_lo, byte offsets of row_lo / row_hi} per (decision, row)
     L.total = o;
     return L;
 }
@@ -188,16 +170,11 @@ __device__ __forceinline__ void decision_loop(const SweepParams& q, const Layout
     for (int r = 0; r < (KS > 0 ? KS : 1); r++) accS[r] = 0.0;
     const int i = 8 * j + g;
     double* const vrow = q.Vout + (size_t)(R.row_ok ? i : 0) * q.Npad + 2 * t;
-    // entry (k, g) at 128 (g >> 1) + 16 (g & 1) + 32 k: the <= 6 entries a quarter warp (rows 2q, 2q+1) can ask for lie in
-    // distinct banks, so a 128-bit lookup is conflict free whatever the decisions are
-    [[maybe_unused]] const unsigned char* const lute = P.sm + L.lut + (size_t)j * kLutBytes + 128 * (g >> 1) + 16 * (g & 1);   // + 32 k
 
-#if LSMC_SEL_REG
-    // byte offsets of the interpolation rows of each decision in the V_next tile (pitch TP + kVPad), lo | hi << 16
-    const uint32_t voff0 = (uint32_t)(R.rL[0] * (TP + kVPad) * 8) | ((uint32_t)(R.rH[0] * (TP + kVPad) * 8) << 16);
-    const uint32_t voff1 = (uint32_t)(R.rL[1] * (TP + kVPad) * 8) | ((uint32_t)(R.rH[1] * (TP + kVPad) * 8) << 16);
-    const uint32_t voff2 = (uint32_t)(R.rL[2] * (TP + kVPad) * 8) | ((uint32_t)(R.rH[2] * (TP + kVPad) * 8) << 16);
-#endif
+    // byte offsets of the interpolation rows of each decision in the V_next tile (pitch TP), lo | hi << 16
+    const uint32_t voff0 = (uint32_t)(R.rL[0] * TP * 8) | ((uint32_t)(R.rH[0] * TP * 8) << 16);
+    const uint32_t voff1 = (uint32_t)(R.rL[1] * TP * 8) | ((uint32_t)(R.rH[1] * TP * 8) << 16);
+    const uint32_t voff2 = (uint32_t)(R.rL[2] * TP * 8) | ((uint32_t)(R.rH[2] * TP * 8) << 16);
     int stage = 0, sphase = 0, it = 0;
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, it++) {
         const int b = it & 1;
@@ -222,12 +199,8 @@ __device__ __forceinline__ void decision_loop(const SweepParams& q, const Layout
         double* out = vrow + tile * TP;
 
         double best0, best1, bc0, bc1;   // carried from phase A to phase B
-#if LSMC_SEL_REG
         double sw0, sw1;                 // w_lo of the chosen decision
         uint32_t k0, k1;                 // byte offsets of its interpolation rows in the V_next tile: lo | hi << 16
-#else
-        int k0, k1;
-#endif
         struct StepIn { double2 s2, cl[3], ch[3]; };   // spot and the bracketing fitted values of the three decisions, two paths
         auto loadA = [&](const int u8, StepIn& in) {
             in.s2 = lds128(pS + u8);
@@ -259,24 +232,15 @@ __device__ __forceinline__ void decision_loop(const SweepParams& q, const Layout
             const bool a1 = x0[1] > x0[0], b1 = x1[1] > x1[0];
             best0 = a1 ? x0[1] : x0[0]; best1 = b1 ? x1[1] : x1[0];
             bc0 = a1 ? c0[1] : c0[0]; bc1 = b1 ? c1[1] : c1[0];
-#if LSMC_SEL_REG
             k0 = a1 ? voff1 : voff0; k1 = b1 ? voff1 : voff0;
             sw0 = a1 ? R.wl[1] : R.wl[0]; sw1 = b1 ? R.wl[1] : R.wl[0];
-#else
-            k0 = a1 ? 1 : 0; k1 = b1 ? 1 : 0;
-#endif
             const bool a2 = x0[2] > best0, b2 = x1[2] > best1;
             best0 = a2 ? x0[2] : best0; best1 = b2 ? x1[2] : best1;
             bc0 = a2 ? c0[2] : bc0; bc1 = b2 ? c1[2] : bc1;
-#if LSMC_SEL_REG
             k0 = a2 ? voff2 : k0; k1 = b2 ? voff2 : k1;
             sw0 = a2 ? R.wl[2] : sw0; sw1 = b2 ? R.wl[2] : sw1;
-#else
-            k0 = a2 ? 2 : k0; k1 = b2 ? 2 : k1;
-#endif
         };
         auto phaseA = [&](const int u8) { StepIn in; loadA(u8, in); computeA(in); };
-#if LSMC_SEL_REG
         auto phaseB = [&](const int u8, const double bst0, const double bst1, const double bcc0, const double bcc1, const uint32_t kk0, const uint32_t kk1,
                           const double wl0, const double wl1) {
             // 128-bit gathers: the rows of path 0's decision serve path 1 too when both paths chose the same decision
@@ -288,15 +252,6 @@ __device__ __forceinline__ void decision_loop(const SweepParams& q, const Layout
             }
             const double vl0 = gl0.x, vh0 = gh0.x, vl1 = gl1.y, vh1 = gh1.y;
             // w_hi = 1 - w_lo exactly as host_plan.cpp build_tables forms it (LSV.cs:277: wu = 1 - wl)
-#else
-        auto phaseB = [&](const int u8, const double bst0, const double bst1, const double bcc0, const double bcc1, const int kk0, const int kk1) {
-            const int4 e0 = *reinterpret_cast<const int4*>(lute + 32 * kk0);
-            const int4 e1 = *reinterpret_cast<const int4*>(lute + 32 * kk1);
-            const double vl0 = *reinterpret_cast<const double*>(pV + e0.z + 8 * u8), vh0 = *reinterpret_cast<const double*>(pV + e0.w + 8 * u8);
-            const double vl1 = *reinterpret_cast<const double*>(pV + e1.z + 8 * u8 + 8), vh1 = *reinterpret_cast<const double*>(pV + e1.w + 8 * u8 + 8);
-            // w_hi = 1 - w_lo exactly as host_plan.cpp build_tables forms it (LSV.cs:277: wu = 1 - wl)
-            const double wl0 = __hiloint2double(e0.y, e0.x), wl1 = __hiloint2double(e1.y, e1.x);
-#endif
             const double act0 = add_rn(mul_rn(vh0, sub_rn(1.0, wl0)), mul_rn(vl0, wl0));
             const double act1 = add_rn(mul_rn(vh1, sub_rn(1.0, wl1)), mul_rn(vl1, wl1));
             double v0 = add_rn(bst0, add_rn(-bcc0, act0));
@@ -317,57 +272,11 @@ __device__ __forceinline__ void decision_loop(const SweepParams& q, const Layout
                 accS[r] = fma(a2.y, v1, accS[r]);
             }
         };
-#if LSMC_SEL_REG && !LSMC_STEP_PIPE
 #pragma unroll (kStepUnroll)
         for (int u = 0; u < NIT; u++) {
             phaseA(8 * u);
             phaseB(8 * u, best0, best1, bc0, bc1, k0, k1, sw0, sw1);
         }
-#elif LSMC_SEL_REG
-        phaseA(0);
-#pragma unroll (kStepUnroll)
-        for (int u = 1; u < NIT; u++) {
-            const double pb0 = best0, pb1 = best1, pc0 = bc0, pc1 = bc1, pw0 = sw0, pw1 = sw1;
-            const uint32_t pk0 = k0, pk1 = k1;
-            phaseA(8 * u);
-            phaseB(8 * (u - 1), pb0, pb1, pc0, pc1, pk0, pk1, pw0, pw1);
-        }
-        phaseB(8 * (NIT - 1), best0, best1, bc0, bc1, k0, k1, sw0, sw1);
-#elif LSMC_STEP_PREFETCH
-        // rolled step loop with the next step's shared-memory operands fetched one step ahead (register double buffer)
-        {
-            StepIn cur, nxt;
-            loadA(0, cur);
-            loadA(8, nxt);
-            computeA(cur);
-#pragma unroll 1
-            for (int u = 1; u < NIT; u++) {
-                const double pb0 = best0, pb1 = best1, pc0 = bc0, pc1 = bc1;
-                const int pk0 = k0, pk1 = k1;
-                cur = nxt;
-                loadA(8 * min(u + 1, NIT - 1), nxt);
-                computeA(cur);
-                phaseB(8 * (u - 1), pb0, pb1, pc0, pc1, pk0, pk1);
-            }
-            phaseB(8 * (NIT - 1), best0, best1, bc0, bc1, k0, k1);
-        }
-#elif !LSMC_STEP_PIPE
-#pragma unroll (kStepUnroll)
-        for (int u = 0; u < NIT; u++) {
-            phaseA(8 * u);
-            phaseB(8 * u, best0, best1, bc0, bc1, k0, k1);
-        }
-#else
-        phaseA(0);
-#pragma unroll (kStepUnroll)
-        for (int u = 1; u < NIT; u++) {
-            const double pb0 = best0, pb1 = best1, pc0 = bc0, pc1 = bc1;
-            const int pk0 = k0, pk1 = k1;
-            phaseA(8 * u);
-            phaseB(8 * (u - 1), pb0, pb1, pc0, pc1, pk0, pk1);
-        }
-        phaseB(8 * (NIT - 1), best0, best1, bc0, bc1, k0, k1);
-#endif
         if (tr) tr[3] = clock64();
         mbar_arrive(&P.dfree[b]);
         if (++stage == kRawStages) { stage = 0; sphase ^= 1; }
@@ -477,13 +386,6 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
             if (__any_sync(0xffffffffu, R.invc != 0.0)) R.variant = kCons0 | kCons2 | kInvc;
             else R.variant = (zero1 ? kZero1 : 0) | ((cons0 || (!zero1 && cons1)) ? kCons0 : 0) | (cons2 ? kCons2 : 0);
         }
-        // the warp's selection table: (w_lo, w_hi) and byte offsets of the interpolation rows in the V_next tile, per (decision, row)
-        if (t < 3) {
-            unsigned char* ent = sm + L.lut + (size_t)j * kLutBytes + 128 * (g >> 1) + 16 * (g & 1) + 32 * t;
-            const double wl = t == 0 ? R.wl[0] : t == 1 ? R.wl[1] : R.wl[2];
-            const int rl = t == 0 ? R.rL[0] : t == 1 ? R.rL[1] : R.rL[2], rh = t == 0 ? R.rH[0] : t == 1 ? R.rH[1] : R.rH[2];
-            *reinterpret_cast<int4*>(ent) = make_int4(__double2loint(wl), __double2hiint(wl), rl * (TP + kVPad) * 8, rh * (TP + kVPad) * 8);
-        }
         __syncwarp();
         pdl_wait();   // (the decision warps are gated by the aux warps' barriers anyway; this orders their V stores after the predecessors)
         if (q.trace && blockIdx.x == 0 && threadIdx.x == 0) q.trace[(0 * 64 + 63) * 8 + 7] = clock64();   // dependency wait over
@@ -504,7 +406,7 @@ __global__ void __launch_bounds__(kWarps * 32, 1) sweep4_kernel(const SweepParam
         const int aw = warp - kDecWarps;
         const int alane = aw * 32 + lane;
         const int n_mt = GnP >> 3;                      // 8-row blocks of fitted values
-        const uint32_t vn_bytes = (uint32_t)((size_t)q.Gn * (TP + kVPad) * 8), raw_bytes = (uint32_t)(2 * (F + 1) * ROW);
+        const uint32_t vn_bytes = (uint32_t)((size_t)q.Gn * TP * 8), raw_bytes = (uint32_t)(2 * (F + 1) * ROW);
         auto produce_vn = [&](int64_t tile, int b) {
             mbar_expect_tx(&vfull[b], vn_bytes);
             tma_2d(sm + L.vn + (size_t)b * L.vn_buf, &mapV, (int)(tile * TP), 0, &vfull[b]);
@@ -788,7 +690,7 @@ static cudaError_t launch4_t(SweepParams& q, int n_prod, int blocks, cudaStream_
     q.n_prod = n_prod;
     if (cudaError_t e = ensure_dynamic_smem((const void*)kern, smem)) return e;
     CUtensorMap mv, msp, mfp, msm, mfm;
-    if (!make_map(&mv, q.Vnext, q.Npad, q.Gn, TP + kVPad, q.Gn) || !make_map(&msp, q.spot_p, q.Npad, 1, TP, 1) ||
+    if (!make_map(&mv, q.Vnext, q.Npad, q.Gn, TP, q.Gn) || !make_map(&msp, q.spot_p, q.Npad, 1, TP, 1) ||
         !make_map(&mfp, q.fac_p, q.Npad, q.F, TP, q.F) || !make_map(&msm, q.spot_m, q.Npad, 1, TP, 1) ||
         !make_map(&mfm, q.fac_m, q.Npad, q.F, TP, q.F))
         return cudaErrorInvalidValue;

@@ -3,8 +3,10 @@
 the valuation on a B200 through the C ABI (include/lsmc_b200.h) instead of pythonnet -> LsmcStorageValuation.Calculate.
 
 What differs from the reference, by necessity:
-  * random numbers: device Philox4x32-10 (antithetic, like the reference's MersenneTwisterGenerator(seed, true),
-    LVP.cs:185-189) instead of MT19937 — seeded results agree with the reference to Monte-Carlo error, not bit-wise;
+  * random numbers: seeded calls draw the reference's own stream (MT19937 + MathNet Normal.Samples + antithetic, as
+    MersenneTwisterGenerator(seed, true) feeds Cmdty.Core's simulator, LVP.cs:185-189; csrc/mt19937.h) on the host and
+    reproduce the reference's seeded golden NPVs; unseeded calls (and SEEDED_RNG = "philox") use the device
+    Philox4x32-10 stream, which agrees with the reference to Monte-Carlo error only;
   * `intrinsic_npv` / `intrinsic_profile` come from the library's host routine lsmc_intrinsic (storage_b200/intrinsic.py),
     the reference's IntrinsicStorageValuation restated (pinned by the reference's golden value 1703773.0757192627);
   * there is no CPU fallback: without liblsmc_b200.so or a B200 the call raises.
@@ -61,32 +63,36 @@ class MultiFactorValuationResults(tp.NamedTuple):
 
 
 def _validate_multi_factor_params(factors, factor_corrs: FactorCorrsType) -> np.ndarray:
-    """multi_factor.py:112-146."""
-    factors_len = len(factors)
-    if factors_len == 0:
+    """The checks of the reference's validator (multi_factor.py:112-146) in the same order and with the same messages — the
+    error strings are what its wrapper tests assert — on the whole matrix at once; the first offender in row-major order is
+    the one reported, as in the reference's element loop."""
+    n = len(factors)
+    if n == 0:
         raise ValueError("factors cannot be empty.")
-    if factors_len == 1 and factor_corrs is None:
-        factor_corrs = np.array([[1.0]])
-    if factors_len == 2 and isinstance(factor_corrs, (float, int)):
-        factor_corrs = np.array([[1.0, float(factor_corrs)], [float(factor_corrs), 1.0]])
-    factor_corrs = np.asarray(factor_corrs)
-    if factor_corrs.ndim != 2:
+    if n == 1 and factor_corrs is None:
+        corrs = np.ones((1, 1))
+    elif n == 2 and isinstance(factor_corrs, (float, int)):
+        corrs = np.array([[1.0, float(factor_corrs)], [float(factor_corrs), 1.0]])
+    else:
+        corrs = np.asarray(factor_corrs)
+    if corrs.ndim != 2:
         raise ValueError("Factor correlation matrix is not 2-dimensional.")
-    if factor_corrs.shape[0] != factor_corrs.shape[1]:
+    if corrs.shape[0] != corrs.shape[1]:
         raise ValueError("Factor correlation matrix is not square.")
-    factor_corrs = factor_corrs.astype(np.float64)
-    for (i, j), corr in np.ndenumerate(factor_corrs):
+    corrs = corrs.astype(np.float64)
+    diagonal = np.eye(corrs.shape[0], dtype=bool)
+    offending = np.where(diagonal, ~np.isclose(corrs, 1.0), ~((corrs >= -1.0) & (corrs <= 1.0)))
+    if offending.any():
+        i, j = (int(v) for v in np.argwhere(offending)[0])
         if i == j:
-            if not np.isclose([corr], [1.0]):
-                raise ValueError("Factor correlation on diagonal position ({i}, {j}) value of {corr} not valid as not "
-                                 "equal to 1.".format(i=i, j=j, corr=corr))
-        elif not -1 <= corr <= 1:
-            raise ValueError("Factor correlation in position ({i}, {j}) value of {corr} not valid as not in the "
-                             "interval [-1, 1]".format(i=i, j=j, corr=corr))
-    if factors_len != factor_corrs.shape[0]:
+            raise ValueError("Factor correlation on diagonal position ({i}, {j}) value of {corr} not valid as not "
+                             "equal to 1.".format(i=i, j=j, corr=corrs[i, j]))
+        raise ValueError("Factor correlation in position ({i}, {j}) value of {corr} not valid as not in the "
+                         "interval [-1, 1]".format(i=i, j=j, corr=corrs[i, j]))
+    if n != corrs.shape[0]:
         raise ValueError("factor_corrs and factors must be of the same length. factor_corrs is of length {} and "
-                         "factors is of length {}.".format(factor_corrs.shape[0], factors_len))
-    return factor_corrs
+                         "factors is of length {}.".format(corrs.shape[0], n))
+    return corrs
 
 
 def _seeds(seed, fwd_sim_seed):
