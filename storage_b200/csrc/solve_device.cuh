@@ -16,11 +16,39 @@ struct GlobalRed {
     __device__ __forceinline__ double operator()(int k, int col) const { return p[(size_t)k * ld + col]; }
 };
 
-inline size_t solve_smem_bytes(int K) { return sizeof(double) * ((size_t)3 * K * K + 2 * K); }
+// Shared memory of a solve, in doubles: A [K][K] (Cholesky factor, lower) | Graw [K][K] | dscale [K] | Tm [K][K] | invd [K] |
+// S [K][K] (the factor in the form the warp substitutions read, see solve_factor) | col [2][K] (published columns).
+inline size_t solve_smem_bytes(int K) { return sizeof(double) * ((size_t)4 * K * K + 4 * K); }
+
+// Element idx of the lower triangle in row-major order (0: (0,0), 1: (1,0), 2: (1,1), ...) -> row; column = idx - row (row + 1) / 2.
+__device__ __forceinline__ int tri_row(int idx) {
+    int i = (int)((sqrtf(8.0f * (float)idx + 1.0f) - 1.0f) * 0.5f);
+    while ((i + 1) * (i + 2) / 2 <= idx) i++;
+    while (i * (i + 1) / 2 > idx) i--;
+    return i;
+}
+
+// The preconditioner T (upper triangular: only that triangle is read) -> shared memory.  Per-problem constant data: tail_kernel
+// calls this before its dependency wait, so the loads overlap the drain of the sweep before it.
+__device__ __forceinline__ void solve_stage_precond(const SolveParams& sp, double* sm) {
+    const int K = sp.K;
+    const double* T = sp.precond;
+    if (sp.accum_mode == 2 || !T) return;
+    double* Tm = sm + 2 * K * K + K;
+    const int n_tri = K * (K + 1) / 2;
+#pragma unroll 8
+    for (int e = threadIdx.x; e < n_tri; e += blockDim.x) {
+        const int m = tri_row(e), k = e - m * (m + 1) / 2;   // k <= m
+        Tm[k * K + m] = __ldg(T + k * K + m);
+    }
+}
 
 // Gram matrix -> shared memory, equilibration, preconditioner.  Returns false in the current-period mode (means, no system).
+// Leaves Graw, dscale, dropped (and Tm unless the caller staged it already); the scaled matrix D G D is formed by solve_factor
+// in registers.
 template <class Red>
-__device__ __forceinline__ bool solve_stage(const SolveParams& sp, const Red& red, double* sm, int* dropped, const int col0, const int col_step) {
+__device__ __forceinline__ bool solve_stage(const SolveParams& sp, const Red& red, double* sm, int* dropped, const int col0, const int col_step,
+                                            const bool precond_staged = false) {
     const int K = sp.K, G = sp.G, tid = threadIdx.x;
     if (sp.accum_mode == 2) {   // current period: continuation = mean over sims (LSV.cs:171-182)
         for (int i = col0 + tid * col_step; i < G; i += blockDim.x * col_step) {
@@ -30,22 +58,22 @@ __device__ __forceinline__ bool solve_stage(const SolveParams& sp, const Red& re
         }
         return false;
     }
-    double* A = sm;                 // [K][K] scaled Gram -> Cholesky factor (lower)
+    double* A = sm;                 // [K][K] Cholesky factor (lower), written by solve_factor
     double* Graw = A + K * K;       // [K][K] unscaled Gram
     double* dscale = Graw + K * K;  // [K]
-    double* Tm = dscale + K;        // [K][K] preconditioner (when present)
     const int gcol = 8 * sp.NT;
     const double* T = sp.precond;
-#pragma unroll 4   // independent L2 loads: several in flight per thread (K = 56: 25 elements per thread, 22 us -> a few)
-    for (int e = tid; e < K * K; e += blockDim.x) {
-        int r = e / K, c = e % K;
-        // symmetrise: the two triangles come from different DMMA tiles and may differ in the last bit
-        Graw[e] = 0.5 * (red(r, gcol + c) + red(c, gcol + r));
+    const int n_tri = K * (K + 1) / 2;
+    // symmetrise: the two triangles come from different DMMA tiles and may differ in the last bit.  One pair of loads per
+    // element of the lower triangle, eight elements (sixteen L2 loads) in flight per thread.
+#pragma unroll 8
+    for (int e = tid; e < n_tri; e += blockDim.x) {
+        const int r = tri_row(e), c = e - r * (r + 1) / 2;
+        const double v = 0.5 * (red(r, gcol + c) + red(c, gcol + r));
+        Graw[r * K + c] = v;
+        Graw[c * K + r] = v;
     }
-    if (T) {
-#pragma unroll 4
-        for (int e = tid; e < K * K; e += blockDim.x) Tm[e] = T[e];
-    }
+    if (!precond_staged) solve_stage_precond(sp, sm);
     __syncthreads();
     for (int k = tid; k < K; k += blockDim.x) {
         const double gkk = Graw[k * K + k];
@@ -54,51 +82,86 @@ __device__ __forceinline__ bool solve_stage(const SolveParams& sp, const Red& re
         dropped[k] = (gkk > 0.0 && !flagged) ? 0 : 1;
     }
     __syncthreads();
-    for (int e = tid; e < K * K; e += blockDim.x) {
-        int r = e / K, c = e % K;
-        A[e] = Graw[e] * dscale[r] * dscale[c];
-    }
-    __syncthreads();
     return true;
 }
 
-// Cholesky of the staged, scaled Gram matrix by the whole CTA + reciprocals of the diagonal (CTA-wide call).
-// Right-looking with the scaling deferred: at column j every thread reads the pivot itself and applies
-//     A[i][k] -= A[i][j] A[k][j] / pivot          (j < k <= i)
-// to its share of the trailing triangle — the reads are in column j, the writes in the columns right of it, so one barrier
-// per column suffices and nobody waits for a thread that takes a square root; L = A scaled by 1 / sqrt(pivot) comes in one
-// pass at the end.  (The previous form — warp 0 alone, sqrt and divisions serial on lane 0, three warp barriers per column —
-// took 5.8 us at K = 10 and 104 us at K = 56: tail trace in profiles/.)
+// Cholesky of the staged Gram matrix, equilibrated on the fly, by the whole CTA + reciprocals of the diagonal (CTA-wide call).
+// Right-looking with the scaling deferred:
+//     a[i][k] -= (a[i][j] / pivot_j) a[k][j]          (j < k <= i)
+// Every thread keeps its E elements of the lower triangle (dealt row-major, round robin) in REGISTERS for the whole
+// factorisation; at column j the owners of that column publish it — it is final — into one of two K-vectors in shared memory,
+// one barrier, and every thread updates its elements right of the column from two shared loads each.  L = a scaled by
+// 1 / sqrt(pivot) is written once at the end, as A (lower triangle, with its diagonal) for the thread-per-right-hand-side
+// solver and as S for the warp solver: S[j][k] = l_jk / l_jj left of the diagonal (row j of the backward substitution) and
+// S[j][k] = l_kj / l_jj right of it (column j of the forward substitution), so that both substitutions read ROW j — lanes on
+// consecutive addresses.  Same operations on the same values as the shared-memory form it replaces (which walked the trailing
+// triangle with two nested strided loops: 0.83 us per column at K = 56), element by element.
+template <int E>
 __device__ __forceinline__ void solve_factor(const SolveParams& sp, double* sm, int* dropped) {
     const int K = sp.K, tid = threadIdx.x, nthr = blockDim.x;
     double* A = sm;
-    double* Tm = A + 2 * K * K + K;
-    double* invd = Tm + K * K;      // [K] reciprocals of the factor's diagonal: the substitutions multiply instead of dividing
-    const int ti = tid >> 4, tk = tid & 15, ni = nthr >> 4;   // blockDim.x is a multiple of 32
+    const double* Graw = A + K * K;
+    const double* dscale = Graw + K * K;
+    double* invd = A + 3 * K * K + K;   // [K] reciprocals of the factor's diagonal: the substitutions multiply instead of dividing
+    double* S = invd + K;
+    double* col = S + K * K;
+    const int n_tri = K * (K + 1) / 2;
+    double a[E];
+    int ik[E];   // row | (column + 1) << 8; 0 = no element (row 0, "column -1": never published, never updated)
+#pragma unroll
+    for (int e = 0; e < E; e++) {
+        const int idx = tid + e * nthr;
+        a[e] = 0.0; ik[e] = 0;
+        if (idx < n_tri) {
+            const int i = tri_row(idx), k = idx - i * (i + 1) / 2;
+            ik[e] = i | ((k + 1) << 8);
+            a[e] = Graw[i * K + k] * dscale[i] * dscale[k];
+        }
+    }
     for (int j = 0; j < K; j++) {
-        const double piv = A[j * K + j];
+        double* cb = col + (j & 1) * K;
+#pragma unroll
+        for (int e = 0; e < E; e++) if ((ik[e] >> 8) == j + 1) cb[ik[e] & 255] = a[e];
+        __syncthreads();   // (two buffers: the column after next is published only after everybody has passed the next barrier)
+        const double piv = cb[j];
         const bool dj = dropped[j] != 0 || !(piv > sp.pivot_tol);
         const double rinv = dj ? 0.0 : __drcp_rn(piv);
-        for (int i = j + 1 + ti; i < K; i += ni) {
-            const double aij = A[i * K + j] * rinv;
-            for (int k = j + 1 + tk; k <= i; k += 16) A[i * K + k] = fma(-aij, A[k * K + j], A[i * K + k]);
+        // branch free: every element loads its two column entries (a finished or absent element reads valid addresses and keeps
+        // its value) — with a branch per element the seventeen updates of a thread ran one after the other, 1 us per column
+        const double* cbm1 = cb - 1;
+#pragma unroll
+        for (int e = 0; e < E; e++) {
+            const int i = ik[e] & 255, kp = ik[e] >> 8;
+            const double ci = cb[i], ck = cbm1[kp];
+            const double upd = fma(-(ci * rinv), ck, a[e]);
+            a[e] = kp > j + 1 ? upd : a[e];
         }
-        __syncthreads();
     }
-    // scaling in two passes: rs_j = 1 / sqrt(pivot_j) (0 for a dropped column, which becomes the unit column), then
-    // l_ij = a_ij rs_j, l_jj = pivot_j rs_j, 1 / l_jj = rs_j
-    for (int j = tid; j < K; j += nthr) {
-        const double piv = A[j * K + j];
-        const bool dj = dropped[j] != 0 || !(piv > sp.pivot_tol);
-        dropped[j] = dj ? 1 : 0;
-        invd[j] = dj ? 0.0 : rsqrt(piv);
+    // scaling: rs_j = 1 / sqrt(pivot_j) (0 for a dropped column, which becomes the unit column), l_ij = a_ij rs_j,
+    // l_jj = pivot_j rs_j, 1 / l_jj = rs_j
+#pragma unroll
+    for (int e = 0; e < E; e++) {
+        const int i = ik[e] & 255, k = (ik[e] >> 8) - 1;
+        if (i == k) {
+            const bool dj = dropped[i] != 0 || !(a[e] > sp.pivot_tol);
+            dropped[i] = dj ? 1 : 0;
+            invd[i] = dj ? 0.0 : rsqrt(a[e]);
+        }
     }
     __syncthreads();
-    for (int e = tid; e < K * K; e += nthr) {
-        const int i = e / K, j = e - i * K;
-        if (j > i) continue;
-        const double rs = invd[j];
-        A[e] = (i == j) ? (rs == 0.0 ? 1.0 : A[e] * rs) : A[e] * rs;
+#pragma unroll
+    for (int e = 0; e < E; e++) {
+        const int i = ik[e] & 255, k = (ik[e] >> 8) - 1;
+        if (k >= 0) {
+            const double rs = invd[k];
+            const double l = (i == k && rs == 0.0) ? 1.0 : a[e] * rs;
+            A[i * K + k] = l;
+            if (i != k) {
+                const double ri = invd[i];
+                S[i * K + k] = l * (ri == 0.0 ? 1.0 : ri);
+                S[k * K + i] = l * (rs == 0.0 ? 1.0 : rs);
+            }
+        }
     }
     __syncthreads();
     for (int j = tid; j < K; j += nthr) if (invd[j] == 0.0) invd[j] = 1.0;
@@ -120,7 +183,7 @@ __device__ __forceinline__ void solve_cta(const SolveParams& sp, const Red& red,
     double r0[KT];
 #pragma unroll
     for (int k = 0; k < KT; k++) r0[k] = (k < K && i_first < G) ? red(k, i_first) : 0.0;
-    solve_factor(sp, sm, dropped);
+    solve_factor<(KT * (KT + 1) / 2 + 127) / 128>(sp, sm, dropped);   // CTAs of at least 128 threads
     // each thread: one right-hand side at a time, vectors in registers (KT = compile-time bound of K)
     for (int i = i_first; i < G; i += blockDim.x * col_step) {
         double x[KT], r[KT], y[KT], rhs[KT];
@@ -186,8 +249,8 @@ __device__ __forceinline__ void solve_cta(const SolveParams& sp, const Red& red,
 // col0 + w * col_step, col0 + (w + nwarps) * col_step, ...
 template <int R, class Red>   // R = rows per lane: 1 (K <= 32) or 2 (K <= 64)
 __device__ __forceinline__ void solve_cta_warps(const SolveParams& sp, const Red& red, double* sm, int* dropped, const int col0, const int col_step,
-                                                long long* tr = nullptr) {
-    if (!solve_stage(sp, red, sm, dropped, col0, col_step)) return;
+                                                long long* tr = nullptr, const bool precond_staged = false) {
+    if (!solve_stage(sp, red, sm, dropped, col0, col_step, precond_staged)) return;
     if (tr) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(tr[3]));
     const int K = sp.K, G = sp.G, lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
     const double* A = sm;
@@ -195,12 +258,13 @@ __device__ __forceinline__ void solve_cta_warps(const SolveParams& sp, const Red
     const double* dscale = Graw + K * K;
     const double* Tm = dscale + K;
     const double* invd = Tm + K * K;
+    const double* S = invd + K;     // rows of the factor scaled by 1 / l_jj, both triangles (solve_factor)
     const bool hasT = sp.precond != nullptr;
     const int i_first = col0 + warp * col_step;
     double rhs[R];
 #pragma unroll
     for (int q = 0; q < R; q++) { const int k = lane + 32 * q; rhs[q] = (k < K && i_first < G) ? red(k, i_first) : 0.0; }
-    solve_factor(sp, sm, dropped);
+    solve_factor<(32 * R * (32 * R + 1) / 2 + 127) / 128>(sp, sm, dropped);   // CTAs of at least 128 threads
     if (tr) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(tr[4]));
     for (int i = i_first; i < G; i += nwarps * col_step) {
         if (i != i_first) {
@@ -229,11 +293,10 @@ __device__ __forceinline__ void solve_cta_warps(const SolveParams& sp, const Red
 #pragma unroll 4
                 for (int j = 32 * qj; j < min(K, 32 * qj + 32); j++) {
                     const double zj = __shfl_sync(0xffffffffu, dr[qj] ? 0.0 : b[qj], j & 31);
-                    const double ivj = invd[j];
 #pragma unroll
                     for (int q = 0; q < R; q++) {
                         const int k = lane + 32 * q;
-                        const double lkj = (k > j && k < K) ? A[k * K + j] * ivj : 0.0;
+                        const double lkj = (k > j && k < K) ? S[j * K + k] : 0.0;   // l_kj / l_jj
                         b[q] = fma(-lkj, zj, b[q]);
                     }
                 }
@@ -246,11 +309,10 @@ __device__ __forceinline__ void solve_cta_warps(const SolveParams& sp, const Red
 #pragma unroll 4
                 for (int j = min(K, 32 * qj + 32) - 1; j >= 32 * qj; j--) {
                     const double wj = __shfl_sync(0xffffffffu, dr[qj] ? 0.0 : y[qj], j & 31);
-                    const double ivj = invd[j];
 #pragma unroll
                     for (int q = 0; q < R; q++) {
                         const int k = lane + 32 * q;
-                        const double ljk = (k < j) ? A[j * K + k] * ivj : 0.0;
+                        const double ljk = (k < j) ? S[j * K + k] : 0.0;   // l_jk / l_jj
                         y[q] = fma(-ljk, wj, y[q]);
                     }
                 }

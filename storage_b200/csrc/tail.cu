@@ -83,6 +83,7 @@ __global__ void __launch_bounds__(kTailThreads) tail_kernel(const TailParams tp)
     extern __shared__ double tsm[];
     __shared__ int dropped[64];
     pdl_launch_dependents();   // PDL: the next sweep's CTAs set themselves up while this kernel runs ...
+    if (tp.do_solve) solve_stage_precond(tp.solve, tsm);   // (per-problem constant, written before the first sweep: safe ahead of the wait)
     pdl_wait();                // ... and this one starts the moment the sweep before it has completed
     long long* tr = (tp.trace && blockIdx.x == 0 && threadIdx.x == 0) ? tp.trace : nullptr;
     if (tr) tr[0] = gtimer();
@@ -124,7 +125,7 @@ __global__ void __launch_bounds__(kTailThreads) tail_kernel(const TailParams tp)
     // ---- 3: solve ----
     // (A register-resident variant — rows of L, L^T, T per lane, fully unrolled for K <= 16 — was measured and dropped: 34 us
     //  against 21 us; a kernel that runs its straight-line code once per launch pays for every instruction fetch.)
-    if (tp.do_solve) solve_cta_warps<R>(tp.solve, red, tsm, dropped, blockIdx.x, gridDim.x, tr);
+    if (tp.do_solve) solve_cta_warps<R>(tp.solve, red, tsm, dropped, blockIdx.x, gridDim.x, tr, true);
     if (tr) tr[6] = gtimer();
 }
 
