@@ -6,6 +6,8 @@
 #include "../../include/lsmc_b200.h"
 #include "lsmc_device.cuh"
 
+struct CUtensorMap_st;   // <cuda.h>: CUtensorMap
+
 namespace lsmc {
 
 struct SweepConfig {
@@ -20,6 +22,7 @@ struct SweepConfig {
 struct SolveParams {
     const double* reduced;   // [8*MT][ncols]
     int ncols, K, G, NT, ldb, accum_mode;
+    int gram_lower_blocks;   // 1: of X~^T X~ only the blocks (rows 8m.., columns 8kb..) with m <= kb are filled (general sweep)
     int64_t n_global;
     double pivot_tol;
     const double* precond;   // T [K][K] + flags [K] of the regressed period
@@ -44,6 +47,8 @@ cudaError_t ensure_dynamic_smem(const void* kernel, size_t bytes);
 // Launch with programmatic stream serialisation (lsmc_device.cuh pdl_wait / pdl_launch_dependents).  LSMC_PDL=0 in the
 // environment falls back to plain stream order (development).
 bool pdl_enabled();
+// TMA descriptor of an FP64 panel [rows][Npad]: box = TP paths x box_rows rows (sweep4.cu).  False when the driver lacks the encoder.
+bool make_panel_map(CUtensorMap_st* map, const double* base, int64_t Npad, int rows, int TP, int box_rows);
 template <class... KArgs, class... Args>
 inline cudaError_t launch_pdl(bool pdl, void (*kern)(KArgs...), int blocks, int threads, size_t smem, cudaStream_t stream, Args&&... args) {
     cudaLaunchConfig_t cfg{};

@@ -677,7 +677,7 @@ void backward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
         const bool use4 = c->TP4 != 0 && sweep4_covers(q);
         DevBuf<long long> trace_buf;
         const char* trace_path = getenv("LSMC_TRACE");   // development: phase timestamps of one mid-horizon sweep
-        const bool trace_now = trace_path && use4 && p == P / 2;
+        const bool trace_now = trace_path && p == P / 2;
         if (trace_now) { trace_buf.alloc(16 * 64 * 8); CUDA_CHECK(cudaMemsetAsync(trace_buf.p, 0, 16 * 64 * 8 * sizeof(long long), s)); q.trace = trace_buf.p; }
         const int n_parts = use4 ? c->sweep4_blocks : c->sweep_blocks;
         if (use4) CUDA_CHECK(launch_sweep4(q, c->TP4, (int)pl.basis.ops.size(), c->sweep4_blocks, s));
@@ -697,6 +697,7 @@ void backward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
         SolveParams sp{};
         sp.reduced = c->reduced.p; sp.ncols = q.ncols; sp.K = pl.K; sp.G = q.G; sp.NT = (q.G + 7) / 8; sp.ldb = c->ldb;
         sp.accum_mode = q.accum_mode; sp.n_global = c->Nglobal; sp.pivot_tol = 1e-13;
+        sp.gram_lower_blocks = use4 ? 0 : 1;
         sp.precond = q.accum_mode == 1 ? q.precond : nullptr;
         sp.beta = p > 0 ? c->beta_all.p + (size_t)(p - 1) * c->beta_stride() : nullptr;
         if (c->use_tail && c->peer.ready) {

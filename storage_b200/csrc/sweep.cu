@@ -9,13 +9,16 @@
 //   F0 basis monomials of both periods from the raw rows (all threads, one (basis, path) element each)
 //   F1 x~ = T^T x_{p-1} (preconditioned regressors) and the fitted continuation values C^[l][n] = beta_l . x_p[n]
 //      for every next-grid row l on the FP64 tensor pipe (DMMA 8x8x4: A = beta, B = X_p^T) -> shared memory
-//   D  lane (g,t) of a decision item owns grid row i = 8j+g and, per iteration, the two paths 8u+2t, 8u+2t+1
+//   D  every warp first takes its share of the 8 x 8 blocks of X~^T X~ (lower block triangle, dealt round robin); then
+//      lane (g,t) of a decision item owns grid row i = 8j+g and, per iteration, the two paths 8u+2t, 8u+2t+1
 //      (128-bit shared loads): max over the bang-bang decisions of immediate + interpolated C^, realised value from
 //      interpolated V_next, store V[i][n] (128-bit), and feed the value straight from registers as the B operand
-//      of the DMMA that accumulates X~_{p-1}^T V; trailing items accumulate X~^T X~.
+//      of the DMMA that accumulates X~_{p-1}^T V.
 // All arithmetic that decides is individually rounded (__dmul_rn/__dadd_rn) in the reference's order: given the same
 // coefficients the value surface is bit-identical to the oracle's.  FP64 scalar and DMMA share one pipe on B200
 // (scripts/probe_fp64.cu: 36 TFLOP/s either way, not additive), which — not HBM — is what bounds this kernel.
+#include <cuda.h>
+
 #include "kernels.h"
 
 namespace lsmc {
@@ -44,10 +47,17 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
+// 2-D tensor copy global -> shared through a TMA descriptor: the whole V_next tile in one instruction (a bulk copy per row —
+// a hundred 192-byte copies per tile — kept the producer warp issuing for most of a tile's time).
+__device__ __forceinline__ void tma_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+
 __device__ __forceinline__ double2 lds128(const double* p) { return *reinterpret_cast<const double2*>(p); }
 
 #ifndef LSMC_DECIDE_UNROLL
-#define LSMC_DECIDE_UNROLL 1
+#define LSMC_DECIDE_UNROLL 3
 #endif
 constexpr int kDecideUnroll = LSMC_DECIDE_UNROLL;
 constexpr int kSweepWarps = 16;
@@ -72,10 +82,10 @@ __host__ __device__ inline SweepSmem sweep_layout(int TP, int Gn, int K, int F, 
     L.raw = o;   o += (size_t)nbuf * L.raw_rows * L.LD;      // raw regressors: spot_p, fac_p[F], spot_{p-1}, fac_{p-1}[F]
     L.c = o;     o += (size_t)L.GnP * L.LD;                  // fitted continuation values
     L.xp = o;    o += (size_t)L.Kp4 * L.LDX;                 // basis rows of period p (rows >= K stay zero)
-    L.xm = o;    o += (size_t)K * L.LD;                      // raw basis rows of period p-1
+    L.xm = o;    o += (size_t)L.Kp4 * L.LDX;                 // basis rows of period p-1 (rows >= K stay zero)
     L.xt = o;    o += (size_t)8 * MT * L.LD;                 // preconditioned rows x~ (rows >= K stay zero)
     L.beta = o;  o += (size_t)L.GnP * L.LDB;
-    L.t = o;     o += (size_t)K * K;
+    L.t = o;     o += (size_t)L.Kp4 * (8 * MT + 4);          // preconditioner, row stride 8 MT + 4 (rows / columns >= K stay zero)
     L.nodes = o; o += (size_t)2 * n_scratch * L.LD;              // product nodes that are not basis functions, both periods
     L.cst = o;   o += (size_t)2 * L.LD;                          // row 0 zeros, row 1 ones (zero beyond the last path)
     o = (o + 1) & ~(size_t)1;
@@ -114,7 +124,7 @@ __device__ __forceinline__ void decide_item(const RowTable& R, const double* __r
     const double* pV = vn + 2 * t;
     const double* pX = sXT + (size_t)g * LD + 2 * t;
     double* out = vrow + 2 * t;
-#pragma unroll (kDecideUnroll)   // rolled: see sweep4.cu LSMC_STEP_UNROLL
+#pragma unroll (kDecideUnroll)   // 3: the whole 24-path tile of the K > 16 shapes straight-line (no spills there; 1.357 -> 1.320 ms at C4)
     for (int u = 0; u < TP / 8; u++) {
         double v[2] = {0.0, 0.0};
         if (R.row_ok) {
@@ -237,8 +247,8 @@ __device__ __forceinline__ void terminal_item(const SweepParams& q, const RowTab
 }  // namespace
 
 template <int TP, int MT, int NTW>
-__global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams q, int nbuf) {
-    extern __shared__ __align__(16) double smem[];
+__global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams q, int nbuf, const __grid_constant__ CUtensorMap mapV) {
+    extern __shared__ __align__(128) double smem[];
     pdl_launch_dependents();   // PDL: see lsmc_device.cuh
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, t = lane & 3;
@@ -247,6 +257,7 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
     const int n_rowops = bd->n_rowops, n_scr = bd->n_scratch;
     const SweepSmem L = sweep_layout(TP, q.Gn, K, F, MT, nbuf, n_scr, n_rowops);
     constexpr int LD = TP, LDX = TP + 4;
+    constexpr int LDT = 8 * MT + 4;   // strides = 4 mod 8 doubles: the four k-rows of a DMMA operand fall into distinct bank groups
     const int LDB = L.LDB, GnP = L.GnP, Kp4 = L.Kp4;
     double* const sVn = smem + L.vn;
     double* const sRaw = smem + L.raw;
@@ -261,7 +272,7 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
     __shared__ int16_t sWaveEnd[kMaxRowOps];
 
     const int NT = (q.G + 7) >> 3;                        // decision items (8 grid rows each)
-    const int n_items = q.accum_mode ? NT + MT : NT;      // + X~^T X~ items
+    const int n_items = NT;
     const int64_t n_tiles = (q.N + TP - 1) / TP;
     const bool need_sp = !q.spot_is_const;                          // spot of period p (else the deterministic price)
     const bool need_fp = q.mode == 0 && q.cont_mode == 0;           // basis of period p for the fitted values
@@ -283,7 +294,7 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
         auto offset = [&](int region, int row) -> int {
             if (region == 0) return (int)(L.cst + (size_t)row * LD);
             if (region == 1) return (int)(L.raw + (size_t)(sel * (F + 1) + row) * LD);
-            if (region == 2) return sel ? (int)(L.xm + (size_t)row * LD) : (int)(L.xp + (size_t)row * LDX);
+            if (region == 2) return (int)((sel ? L.xm : L.xp) + (size_t)row * LDX);
             return (int)(L.nodes + (size_t)(sel * n_scr + row) * LD);
         };
         sOp4[2 * o0 + sel * (o1 - o0) + (o - o0)] =
@@ -300,7 +311,7 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
             sBeta[(size_t)l * LDB + k] = __ldg(q.beta + (size_t)l * q.ldb + k);
         }
     }
-    if (need_m) for (int i = tid; i < K * K; i += blockDim.x) sT[i] = __ldg(q.precond + i);
+    if (need_m) for (int i = tid; i < K * K; i += blockDim.x) sT[(i / K) * LDT + i % K] = __ldg(q.precond + i);
     if (tid == 0) {
         mbar_init(&s_full[0], 1);
         mbar_init(&s_full[1], 1);
@@ -310,6 +321,20 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
     // ---- decision tables -> registers ----
     RowTable tab[NTW];
     double acc[NTW][MT][2];
+    // X~^T X~: the MT (MT + 1) / 2 blocks (kb, m), m <= kb, of the lower block triangle — block (m, kb) is its transpose —
+    // dealt over the fifteen workers (the producer warp needs most of the phase to issue its copies); block
+    // b = kb (kb + 1) / 2 + m goes to worker b % 15, slot b / 15
+    constexpr int kGramBlocks = MT * (MT + 1) / 2, GB = (kGramBlocks + kWorkers - 1) / kWorkers;
+    double gacc[GB][2];
+    int gblk[GB];   // kb << 8 | m, -1: none
+#pragma unroll
+    for (int sl = 0; sl < GB; sl++) {
+        gacc[sl][0] = gacc[sl][1] = 0.0;
+        const int bidx = warp + sl * kWorkers;
+        int kb = 0;
+        while ((kb + 1) * (kb + 2) / 2 <= bidx) kb++;
+        gblk[sl] = (q.accum_mode && warp < kWorkers && bidx < kGramBlocks) ? ((kb << 8) | (bidx - kb * (kb + 1) / 2)) : -1;
+    }
 #pragma unroll
     for (int jj = 0; jj < NTW; jj++) {
 #pragma unroll
@@ -351,10 +376,7 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
         if (nrows == 0) return;
         if (lane == 0) mbar_expect_tx(&s_full[b], (uint32_t)nrows * row_bytes);
         __syncwarp();
-        if (q.mode == 0) {
-            double* dst = sVn + (size_t)b * GnP * LD;
-            for (int r = lane; r < q.Gn; r += 32) bulk_g2s(dst + (size_t)r * LD, q.Vnext + (size_t)r * q.Npad + n0, row_bytes, &s_full[b]);
-        }
+        if (q.mode == 0 && lane == 0) tma_2d(sVn + (size_t)b * GnP * LD, &mapV, (int)n0, 0, &s_full[b]);   // Gn rows x TP paths, row pitch LD = TP
         if (lane < 2 * (F + 1)) {
             const int r = lane;
             const double* src = nullptr;
@@ -376,6 +398,9 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
         const double* vn = sVn + (size_t)b * GnP * LD;
         double* raw = sRaw + (size_t)b * L.raw_rows * LD;
         const double* sS = raw;   // row 0: spot of period p
+        // development (LSMC_TRACE): phase timestamps of CTA 0, one row per warp and tile
+        long long* tr = (q.trace && blockIdx.x == 0 && it < 64 && lane == 0) ? q.trace + ((size_t)warp * 64 + it) * 8 : nullptr;
+        if (tr) tr[0] = clock64();
 
         // ================= phase F0: basis monomials of both periods from the raw rows =================
         if (any_copy) mbar_wait(&s_full[b], (uint32_t)((it / nbuf) & 1));   // this tile's rows have landed
@@ -408,31 +433,69 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
             }
         }
 
+        if (tr) tr[1] = clock64();
         // ================= phase F1: preconditioned regressors + fitted continuation values =================
-        if (q.accum_mode == 1) {
-            // x~ = T^T x_{p-1} on the FP64 tensor pipe: D[j][path] = sum_i T[i][j] x[i][path]; one (row block, path block) per warp step
-            constexpr int NNT = TP / 8;
-            for (int item = warp; item < MT * NNT; item += kSweepWarps) {
+        // Work of this phase: NF fit items (8 next-grid rows x TP paths, TP / 8 DMMA per k-step) and NX x~ items (8 basis rows x
+        // 8 paths, one DMMA per k-step), both on the FP64 tensor pipe.  Fit item f goes to warp f % 16; the warps left with one fit
+        // item fewer take TP / 8 x~ items each first (the same number of DMMA), the rest is dealt round robin.
+        constexpr int NNT = TP / 8;
+        const int NF = (q.mode == 0 && q.cont_mode == 0) ? (GnP >> 3) : 0;
+        const int NX = q.accum_mode == 1 ? MT * NNT : 0;
+        if (NX) {
+            // x~ = T^T x_{p-1}: D[j][path] = sum_i T[i][j] x[i][path]; the k-steps alternate between two accumulator pairs so that
+            // two DMMA chains are in flight per item
+            auto xt_item = [&](const int item) {
                 const int m = item / NNT, nt = item - m * NNT, j = 8 * m + g;
-                double c0 = 0.0, c1 = 0.0;
-                for (int ks = 0; ks < Kp4; ks += 4) {
-                    const int i = ks + t;
-                    const double av = (i < K && j < K) ? sT[i * K + j] : 0.0;
-                    const double bv = (i < K) ? sXM[(size_t)i * LD + 8 * nt + g] : 0.0;
-                    dmma8x8x4(c0, c1, av, bv);
+                double c0 = 0.0, c1 = 0.0, d0 = 0.0, d1 = 0.0;
+                auto operands = [&](const int ks, double& av, double& bv) {   // (zero rows / columns beyond K)
+                    av = sT[(ks + t) * LDT + j];
+                    bv = sXM[(size_t)(ks + t) * LDX + 8 * nt + g];
+                };
+                int ks = 0;
+#pragma unroll 2   // operands of the next pair of k-steps in flight while this pair's DMMA issue
+                for (; ks + 4 < Kp4; ks += 8) {
+                    double a0, b0, a1, b1;
+                    operands(ks, a0, b0);
+                    operands(ks + 4, a1, b1);
+                    dmma8x8x4(c0, c1, a0, b0);
+                    dmma8x8x4(d0, d1, a1, b1);
                 }
-                *reinterpret_cast<double2*>(sXT + (size_t)j * LD + 8 * nt + 2 * t) = make_double2(c0, c1);
-            }
+                if (ks < Kp4) {
+                    double a0, b0;
+                    operands(ks, a0, b0);
+                    dmma8x8x4(c0, c1, a0, b0);
+                }
+                *reinterpret_cast<double2*>(sXT + (size_t)j * LD + 8 * nt + 2 * t) = make_double2(c0 + d0, c1 + d1);
+            };
+            // all TP / 8 path blocks of one row block at once, like a fit item: the T fragment is loaded once per k-step
+            auto xt_row_item = [&](const int m) {
+                const double* trow = sT + t * LDT + 8 * m + g;
+                const double* xcol = sXM + (size_t)t * LDX + g;
+                double cf[NNT][2];
+#pragma unroll
+                for (int nt = 0; nt < NNT; nt++) cf[nt][0] = cf[nt][1] = 0.0;
+#pragma unroll 2
+                for (int ks = 0; ks < Kp4; ks += 4) {
+                    const double av = trow[ks * LDT];
+#pragma unroll
+                    for (int nt = 0; nt < NNT; nt++) dmma8x8x4(cf[nt][0], cf[nt][1], av, xcol[(size_t)ks * LDX + 8 * nt]);
+                }
+#pragma unroll
+                for (int nt = 0; nt < NNT; nt++) *reinterpret_cast<double2*>(sXT + (size_t)(8 * m + g) * LD + 8 * nt + 2 * t) = make_double2(cf[nt][0], cf[nt][1]);
+            };
+            const int n_hi = NF ? NF - ((NF - 1) / kSweepWarps) * kSweepWarps : kSweepWarps;   // warps with the larger number of fit items
+            const int n_first = min(MT, kSweepWarps - n_hi) * NNT;                             // x~ items taken as whole row blocks
+            if (warp >= n_hi && warp - n_hi < MT) xt_row_item(warp - n_hi);
+            for (int e = n_first + warp; e < NX; e += kSweepWarps) xt_item(e);
         } else if (q.accum_mode == 2) {
             for (int path = tid; path < TP; path += blockDim.x) sXT[path] = (n0 + path < q.N) ? 1.0 : 0.0;
         }
+        if (tr) tr[6] = clock64();
         if (q.mode == 0) {
             if (q.cont_mode == 0) {
                 // one block of 8 next-grid rows per warp step, all TP / 8 path blocks at once: the coefficient fragment is loaded
                 // once per k-step and feeds independent accumulator chains
-                constexpr int NNT = TP / 8;
-                const int NTn = GnP >> 3;
-                for (int mt = warp; mt < NTn; mt += kSweepWarps) {
+                for (int mt = warp; mt < NF; mt += kSweepWarps) {
                     const double* brow = sBeta + (size_t)(8 * mt + g) * LDB + t;
                     const double* xcol = sXP + (size_t)t * LDX + g;
                     double cf[NNT][2];
@@ -455,18 +518,34 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
                 }
             }
         }
+        if (tr) tr[2] = clock64();
         __syncthreads();
+        if (tr) tr[3] = clock64();
 
         // ================= phase D: decisions + normal-equation accumulation; producer prefetches =================
         const int64_t next = tile + gridDim.x;
-        if (warp == kWorkers) {
-            if (nbuf == 2 && next < n_tiles) produce(next, b ^ 1);
-        } else {
+        if (warp == kWorkers && nbuf == 2 && next < n_tiles) produce(next, b ^ 1);
+        if (accum) {
+            // this warp's blocks of X~^T X~ (B operand = x~ itself); the slots' DMMA chains are independent
+#pragma unroll
+            for (int u = 0; u < TP / 8; u++) {
+#pragma unroll
+                for (int sl = 0; sl < GB; sl++) {
+                    if (gblk[sl] >= 0) {
+                        const double2 b2 = lds128(sXT + (size_t)(8 * (gblk[sl] >> 8) + g) * LD + 2 * t + 8 * u);
+                        const double2 a2 = lds128(sXT + (size_t)(8 * (gblk[sl] & 255) + g) * LD + 2 * t + 8 * u);
+                        dmma8x8x4(gacc[sl][0], gacc[sl][1], a2.x, b2.x);
+                        dmma8x8x4(gacc[sl][0], gacc[sl][1], a2.y, b2.y);
+                    }
+                }
+            }
+        }
+        if (warp < kWorkers) {
 #pragma unroll
             for (int jj = 0; jj < NTW; jj++) {
                 const int j = warp + jj * kWorkers;
                 if (j >= n_items) break;
-                if (j < NT) {
+                {
                     const RowTable& R = tab[jj];
                     const int i = 8 * j + g;
                     double* vrow = q.Vout + (size_t)(R.row_ok ? i : 0) * q.Npad + n0;
@@ -478,30 +557,30 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
 #undef VARIANT
                         default: decide_item_generic<TP, MT>(q, R, i, sC, vn, sS, sXT, vrow, accum, g, t, acc[jj]); break;
                     }
-                } else {
-                    const int kb = 8 * (j - NT) + g;   // X~^T X~: B operand = x~ itself
-                    const double* pb = sXT + (size_t)kb * LD + 2 * t;
-                    const double* pa = sXT + (size_t)g * LD + 2 * t;
-#pragma unroll
-                    for (int u = 0; u < TP / 8; u++) {
-                        const double2 b2 = lds128(pb + 8 * u);
-#pragma unroll
-                        for (int m = 0; m < MT; m++) {
-                            const double2 a2 = lds128(pa + (size_t)8 * m * LD + 8 * u);
-                            dmma8x8x4(acc[jj][m][0], acc[jj][m][1], a2.x, b2.x);
-                            dmma8x8x4(acc[jj][m][0], acc[jj][m][1], a2.y, b2.y);
-                        }
-                    }
                 }
             }
         }
+        if (tr) tr[4] = clock64();
         __syncthreads();
+        if (tr) tr[5] = clock64();
         if (nbuf == 1) {
             if (warp == kWorkers && next < n_tiles) produce(next, 0);
         }
     }
 
     // ---- per-CTA partial: partial[cta][k][col], k = 8m+g, col = 8j+2t ----
+    if (q.accum_mode) {
+        // X~^T X~: block (kb, m) holds rows 8m.. of the columns of basis block kb; its mirror image is left to the solver
+        // (SolveParams::gram_lower_blocks) and written as zeros so that the reduction never sums stale memory
+        double* out = q.partial + (size_t)blockIdx.x * (8 * MT) * q.ncols;
+#pragma unroll
+        for (int sl = 0; sl < GB; sl++) {
+            if (gblk[sl] < 0) continue;
+            const int kb = gblk[sl] >> 8, m = gblk[sl] & 255;
+            *reinterpret_cast<double2*>(out + (size_t)(8 * m + g) * q.ncols + 8 * (NT + kb) + 2 * t) = make_double2(gacc[sl][0], gacc[sl][1]);
+            if (kb != m) *reinterpret_cast<double2*>(out + (size_t)(8 * kb + g) * q.ncols + 8 * (NT + m) + 2 * t) = make_double2(0.0, 0.0);
+        }
+    }
     if (q.accum_mode && warp < kWorkers) {
         double* out = q.partial + (size_t)blockIdx.x * (8 * MT) * q.ncols;
 #pragma unroll
@@ -536,7 +615,9 @@ template <int TP, int MT, int NTW>
 static cudaError_t launch_sweep_t(const SweepParams& q, int blocks, size_t smem, int nbuf, cudaStream_t stream) {
     auto kern = sweep_kernel<TP, MT, NTW>;
     if (cudaError_t e = ensure_dynamic_smem((const void*)kern, smem)) return e;
-    return launch_pdl(q.pdl != 0, kern, blocks, kSweepWarps * 32, smem, stream, q, nbuf);
+    CUtensorMap mv{};
+    if (q.mode == 0 && !make_panel_map(&mv, q.Vnext, q.Npad, q.Gn, TP, q.Gn)) return cudaErrorInvalidValue;
+    return launch_pdl(q.pdl != 0, kern, blocks, kSweepWarps * 32, smem, stream, q, nbuf, mv);
 }
 
 template <int TP>
@@ -560,9 +641,8 @@ int sweep_max_items() { return 2 * kWorkers; }
 cudaError_t launch_sweep(SweepParams& q, const SweepConfig& cfg, cudaStream_t stream) {
     const int MT = cfg.MT;
     const int NT = (q.G + 7) / 8;
-    const int n_items = q.accum_mode ? NT + MT : NT;
-    if (n_items > 2 * kWorkers) return cudaErrorInvalidValue;
-    const int NTW = n_items <= kWorkers ? 1 : 2;
+    if (NT + (q.accum_mode ? MT : 0) > 2 * kWorkers) return cudaErrorInvalidValue;   // (the bound lsmc_set_problem checks: sweep_max_items)
+    const int NTW = NT <= kWorkers ? 1 : 2;
     q.ncols = 8 * (NT + MT);
     const size_t smem = layout_bytes(cfg.TP, q.Gn, q.K, q.F, MT, cfg.nbuf, cfg.n_scratch, cfg.n_rowops);
     if (cfg.TP == 56) return launch_sweep_tp<56>(q, MT, NTW, cfg.blocks, smem, cfg.nbuf, stream);

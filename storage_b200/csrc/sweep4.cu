@@ -661,7 +661,7 @@ static EncodeTiledFn encode_tiled_fn() {
 }
 
 // [rows][Npad] FP64 panel, box = TP paths x box_rows rows.
-static bool make_map(CUtensorMap* map, const double* base, int64_t Npad, int rows, int TP, int box_rows) {
+bool make_panel_map(CUtensorMap_st* map, const double* base, int64_t Npad, int rows, int TP, int box_rows) {
     EncodeTiledFn enc = encode_tiled_fn();
     if (!enc) return false;
     const cuuint64_t dims[2] = {(cuuint64_t)Npad, (cuuint64_t)rows};
@@ -690,9 +690,9 @@ static cudaError_t launch4_t(SweepParams& q, int n_prod, int blocks, cudaStream_
     q.n_prod = n_prod;
     if (cudaError_t e = ensure_dynamic_smem((const void*)kern, smem)) return e;
     CUtensorMap mv, msp, mfp, msm, mfm;
-    if (!make_map(&mv, q.Vnext, q.Npad, q.Gn, TP, q.Gn) || !make_map(&msp, q.spot_p, q.Npad, 1, TP, 1) ||
-        !make_map(&mfp, q.fac_p, q.Npad, q.F, TP, q.F) || !make_map(&msm, q.spot_m, q.Npad, 1, TP, 1) ||
-        !make_map(&mfm, q.fac_m, q.Npad, q.F, TP, q.F))
+    if (!make_panel_map(&mv, q.Vnext, q.Npad, q.Gn, TP, q.Gn) || !make_panel_map(&msp, q.spot_p, q.Npad, 1, TP, 1) ||
+        !make_panel_map(&mfp, q.fac_p, q.Npad, q.F, TP, q.F) || !make_panel_map(&msm, q.spot_m, q.Npad, 1, TP, 1) ||
+        !make_panel_map(&mfm, q.fac_m, q.Npad, q.F, TP, q.F))
         return cudaErrorInvalidValue;
     return launch_pdl(q.pdl != 0, kern, blocks, kWarps * 32, smem, stream, q, mv, msp, mfp, msm, mfm);
 }
