@@ -19,3 +19,7 @@ for w in range(16):
     tot.append(tile.mean())
     print("%4d | %5.0f | %5.0f | %5.0f | %5.0f | %5.0f | %5.0f | %5.0f" % (w, f0.mean(), xt.mean(), fit.mean(), bar1.mean(), d.mean(), bar2.mean(), tile.mean()))
 print("clocks per tile: %.0f" % np.mean(tot))
+if t[13:, ok, 7].any():   # warps 13..15: next tile's rows landed (after the start of the decision phase) and its basis program done
+    for w in (13, 14, 15):
+        r = t[w][ok]
+        print("warp %d: decision phase start -> next tile landed %.0f, basis program of the next tile %.0f" % (w, (r[:, 7] - r[:, 3]).mean(), (r[:, 4] - r[:, 7]).mean()))

@@ -54,6 +54,15 @@ __device__ __forceinline__ void tma_2d(void* dst, const CUtensorMap* map, int c0
                  ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
 }
 
+// Shared-space accesses by 32-bit address (the basis program indexes the whole carve-up with offsets from its op table)
+__device__ __forceinline__ double lds64_at(uint32_t a) { double v; asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a)); return v; }
+__device__ __forceinline__ void sts64_at(uint32_t a, double v) { asm volatile("st.shared.f64 [%0], %1;" ::"r"(a), "d"(v) : "memory"); }
+__device__ __forceinline__ int4 lds128i_at(uint32_t a) {
+    int4 v;
+    asm volatile("ld.shared.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
+    return v;
+}
+
 __device__ __forceinline__ double2 lds128(const double* p) { return *reinterpret_cast<const double2*>(p); }
 
 #ifndef LSMC_DECIDE_UNROLL
@@ -389,6 +398,57 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
     };
     const bool any_copy = q.mode == 0 || need_sp || need_m;
 
+    // ---- phase F0 as a routine of `nth` cooperating threads (this thread is number `tix`; `sync` is their barrier): masks the
+    //      columns beyond the last path, then runs the basis program on tile buffer bb.
+    //      The basis program (host_plan.cpp compile_basis: left-to-right product chains, spot first, factors ascending, shared
+    //      prefixes computed once — the order BasisFunctions.cs:92-132 and the oracle multiply in), one multiply per element,
+    //      wave by wave; a node that is a basis function lands in its design-matrix row. ----
+    auto basis_rows = [&](const int bb, const int64_t tn0, const int tix, const int nth, auto sync) {
+        const int rb = bb * L.raw_rows * LD;
+        if (tn0 + TP > q.N) {   // the last tile: columns beyond the last path must contribute nothing
+            for (int path = tix; path < TP; path += nth) if (tn0 + path >= q.N) smem[L.cst + LD + path] = 0.0;
+            for (int e = tix; e < L.raw_rows * TP; e += nth) {
+                const int r = e / TP, path = e - r * TP;
+                if (tn0 + path >= q.N) sRaw[rb + (size_t)r * LD + path] = 0.0;
+            }
+            sync();
+        }
+        int o0 = 0;
+        for (int w = 0; w < n_waves; w++) {
+            const int o1 = sWaveEnd[w], nw = o1 - o0;
+            const int lo = need_fp ? 0 : nw, hi = need_m ? 2 * nw : nw;
+            const uint32_t ops_a = smem_u32(sOp4 + 2 * o0 + lo), sm_a = smem_u32(smem);
+            // four elements per step, all their loads ahead of the stores (the elements of a wave are independent, which the
+            // compiler cannot know: one element per step ran at one shared-memory round trip after the other)
+            constexpr int U = 4;
+            const int n_el = (hi - lo) * TP;
+            for (int e0 = tix; e0 < n_el; e0 += U * nth) {
+                double va[U], vb[U];
+                int4 op[U];
+                int path[U];
+                // (an element beyond the end repeats the wave's first one: same value stored twice, no branches)
+#pragma unroll
+                for (int u = 0; u < U; u++) {
+                    const int e = e0 + u * nth < n_el ? e0 + u * nth : 0;
+                    const int idx = e / TP;
+                    path[u] = e - idx * TP;
+                    op[u] = lds128i_at(ops_a + 16 * idx);
+                }
+#pragma unroll
+                for (int u = 0; u < U; u++) {
+                    va[u] = lds64_at(sm_a + 8 * (op[u].x + ((op[u].w & 1) ? rb : 0) + path[u]));
+                    vb[u] = lds64_at(sm_a + 8 * (op[u].y + ((op[u].w & 2) ? rb : 0) + path[u]));
+                }
+#pragma unroll
+                for (int u = 0; u < U; u++) sts64_at(sm_a + 8 * (op[u].z + path[u]), mul_rn(va[u], vb[u]));
+            }
+            o0 = o1;
+            sync();
+        }
+    };
+    constexpr int kAuxFirst = 13;   // warps 13, 14 (workers without a decision item when the grid has <= 104 rows) and the producer
+    const bool overlap_f0 = nbuf == 2 && NT <= kAuxFirst;
+
     int64_t tile = blockIdx.x;
     if (warp == kWorkers && tile < n_tiles) produce(tile, 0);
 
@@ -404,34 +464,12 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
 
         // ================= phase F0: basis monomials of both periods from the raw rows =================
         if (any_copy) mbar_wait(&s_full[b], (uint32_t)((it / nbuf) & 1));   // this tile's rows have landed
-        if (n0 + TP > q.N) {   // the last tile: columns beyond the last path must contribute nothing
-            for (int path = tid; path < TP; path += blockDim.x) if (n0 + path >= q.N) smem[L.cst + LD + path] = 0.0;
-            for (int e = tid; e < L.raw_rows * TP; e += blockDim.x) {
-                const int r = e / TP, path = e - r * TP;
-                if (n0 + path >= q.N) raw[(size_t)r * LD + path] = 0.0;
-            }
-            __syncthreads();
-        }
-        {
-            // The basis program (host_plan.cpp compile_basis: left-to-right product chains, spot first, factors ascending, shared
-            // prefixes computed once — the order BasisFunctions.cs:92-132 and the oracle multiply in), one multiply per element,
-            // wave by wave; a node that is a basis function lands in its design-matrix row.
-            const int rb = b * L.raw_rows * LD;
-            int o0 = 0;
-            for (int w = 0; w < n_waves; w++) {
-                const int o1 = sWaveEnd[w], nw = o1 - o0;
-                const int lo = need_fp ? 0 : nw, hi = need_m ? 2 * nw : nw;
-                const int4* ops = sOp4 + 2 * o0 + lo;
-                for (int e = tid; e < (hi - lo) * TP; e += blockDim.x) {
-                    const int idx = e / TP, path = e - idx * TP;
-                    const int4 op = ops[idx];
-                    const double va = smem[op.x + ((op.w & 1) ? rb : 0) + path], vb = smem[op.y + ((op.w & 2) ? rb : 0) + path];
-                    smem[op.z + path] = mul_rn(va, vb);
-                }
-                o0 = o1;
-                __syncthreads();
-            }
-        }
+        // the other buffer was last read in the previous tile's decision phase: the next tile's copies start now — a V_next tile of
+        // a hundred 192-byte rows takes the TMA unit about 4 000 clocks — and have landed when the decision phase begins
+        if (warp == kWorkers && nbuf == 2 && tile + gridDim.x < n_tiles) produce(tile + gridDim.x, b ^ 1);
+        // (with two tile buffers the basis rows of every tile but a CTA's first were computed during the previous tile's decision
+        //  phase, by the three warps that have no decision item — see phase D)
+        if (!overlap_f0 || it == 0) basis_rows(b, n0, tid, (int)blockDim.x, [] { __syncthreads(); });
 
         if (tr) tr[1] = clock64();
         // ================= phase F1: preconditioned regressors + fitted continuation values =================
@@ -483,10 +521,15 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
 #pragma unroll
                 for (int nt = 0; nt < NNT; nt++) *reinterpret_cast<double2*>(sXT + (size_t)(8 * m + g) * LD + 8 * nt + 2 * t) = make_double2(cf[nt][0], cf[nt][1]);
             };
+            // the workers (the producer warp is busy issuing the next tile's copies) left with one fit item fewer take two whole row
+            // blocks each; the rest goes round robin over the workers
             const int n_hi = NF ? NF - ((NF - 1) / kSweepWarps) * kSweepWarps : kSweepWarps;   // warps with the larger number of fit items
-            const int n_first = min(MT, kSweepWarps - n_hi) * NNT;                             // x~ items taken as whole row blocks
-            if (warp >= n_hi && warp - n_hi < MT) xt_row_item(warp - n_hi);
-            for (int e = n_first + warp; e < NX; e += kSweepWarps) xt_item(e);
+            const int n_lo = max(0, kWorkers - n_hi);
+            const int n_rows = min(MT, 2 * n_lo);                                             // row blocks taken whole
+            if (warp >= n_hi && warp < kWorkers)
+                for (int m = warp - n_hi; m < n_rows; m += n_lo) xt_row_item(m);
+            if (warp < kWorkers)
+                for (int e = n_rows * NNT + warp; e < NX; e += kWorkers) xt_item(e);
         } else if (q.accum_mode == 2) {
             for (int path = tid; path < TP; path += blockDim.x) sXT[path] = (n0 + path < q.N) ? 1.0 : 0.0;
         }
@@ -524,7 +567,6 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
 
         // ================= phase D: decisions + normal-equation accumulation; producer prefetches =================
         const int64_t next = tile + gridDim.x;
-        if (warp == kWorkers && nbuf == 2 && next < n_tiles) produce(next, b ^ 1);
         if (accum) {
             // this warp's blocks of X~^T X~ (B operand = x~ itself); the slots' DMMA chains are independent
 #pragma unroll
@@ -539,6 +581,13 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
                     }
                 }
             }
+        }
+        if (overlap_f0 && warp >= kAuxFirst && next < n_tiles) {
+            // the next tile's rows are on their way: as soon as they have landed, warps 13..15 run its basis program — the basis
+            // rows, product nodes and the constant rows are not read during this phase
+            if (any_copy) mbar_wait(&s_full[b ^ 1], (uint32_t)(((it + 1) >> 1) & 1));
+            if (tr) tr[7] = clock64();
+            basis_rows(b ^ 1, next * TP, tid - kAuxFirst * 32, (kSweepWarps - kAuxFirst) * 32, [] { asm volatile("bar.sync 1, 96;" ::: "memory"); });
         }
         if (warp < kWorkers) {
 #pragma unroll
