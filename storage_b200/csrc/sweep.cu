@@ -92,7 +92,7 @@ __host__ __device__ inline SweepSmem sweep_layout(int TP, int Gn, int K, int F, 
     L.c = o;     o += (size_t)L.GnP * L.LD;                  // fitted continuation values
     L.xp = o;    o += (size_t)L.Kp4 * L.LDX;                 // basis rows of period p (rows >= K stay zero)
     L.xm = o;    o += (size_t)L.Kp4 * L.LDX;                 // basis rows of period p-1 (rows >= K stay zero)
-    L.xt = o;    o += (size_t)8 * MT * L.LD;                 // preconditioned rows x~ (rows >= K stay zero)
+    L.xt = o;    o += (size_t)nbuf * 8 * MT * L.LD;          // preconditioned rows x~ (rows >= K stay zero), one set per tile buffer
     L.beta = o;  o += (size_t)L.GnP * L.LDB;
     L.t = o;     o += (size_t)L.Kp4 * (8 * MT + 4);          // preconditioner, row stride 8 MT + 4 (rows / columns >= K stay zero)
     L.nodes = o; o += (size_t)2 * n_scratch * L.LD;              // product nodes that are not basis functions, both periods
@@ -273,7 +273,7 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
     double* const sC = smem + L.c;
     double* const sXP = smem + L.xp;
     double* const sXM = smem + L.xm;
-    double* const sXT = smem + L.xt;
+    double* const sXT0 = smem + L.xt;
     double* const sBeta = smem + L.beta;
     double* const sT = smem + L.t;
     int4* const sOp4 = reinterpret_cast<int4*>(smem + L.ops);
@@ -446,6 +446,48 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
             sync();
         }
     };
+    constexpr int NNT = TP / 8;
+    // x~ = T^T x_{p-1}: D[j][path] = sum_i T[i][j] x[i][path]; the k-steps alternate between two accumulator pairs so that
+    // two DMMA chains are in flight per item
+    auto xt_item = [&](double* xt, const int item) {
+        const int m = item / NNT, nt = item - m * NNT, j = 8 * m + g;
+        double c0 = 0.0, c1 = 0.0, d0 = 0.0, d1 = 0.0;
+        auto operands = [&](const int ks, double& av, double& bv) {   // (zero rows / columns beyond K)
+            av = sT[(ks + t) * LDT + j];
+            bv = sXM[(size_t)(ks + t) * LDX + 8 * nt + g];
+        };
+        int ks = 0;
+#pragma unroll 2   // operands of the next pair of k-steps in flight while this pair's DMMA issue
+        for (; ks + 4 < Kp4; ks += 8) {
+            double a0, b0, a1, b1;
+            operands(ks, a0, b0);
+            operands(ks + 4, a1, b1);
+            dmma8x8x4(c0, c1, a0, b0);
+            dmma8x8x4(d0, d1, a1, b1);
+        }
+        if (ks < Kp4) {
+            double a0, b0;
+            operands(ks, a0, b0);
+            dmma8x8x4(c0, c1, a0, b0);
+        }
+        *reinterpret_cast<double2*>(xt + (size_t)j * LD + 8 * nt + 2 * t) = make_double2(c0 + d0, c1 + d1);
+    };
+    // all TP / 8 path blocks of one row block at once, like a fit item: the T fragment is loaded once per k-step
+    auto xt_row_item = [&](double* xt, const int m) {
+        const double* trow = sT + t * LDT + 8 * m + g;
+        const double* xcol = sXM + (size_t)t * LDX + g;
+        double cf[NNT][2];
+#pragma unroll
+        for (int nt = 0; nt < NNT; nt++) cf[nt][0] = cf[nt][1] = 0.0;
+#pragma unroll 2
+        for (int ks = 0; ks < Kp4; ks += 4) {
+            const double av = trow[ks * LDT];
+#pragma unroll
+            for (int nt = 0; nt < NNT; nt++) dmma8x8x4(cf[nt][0], cf[nt][1], av, xcol[(size_t)ks * LDX + 8 * nt]);
+        }
+#pragma unroll
+        for (int nt = 0; nt < NNT; nt++) *reinterpret_cast<double2*>(xt + (size_t)(8 * m + g) * LD + 8 * nt + 2 * t) = make_double2(cf[nt][0], cf[nt][1]);
+    };
     constexpr int kAuxFirst = 13;   // warps 13, 14 (workers without a decision item when the grid has <= 104 rows) and the producer
     const bool overlap_f0 = nbuf == 2 && NT <= kAuxFirst;
 
@@ -458,6 +500,7 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
         const double* vn = sVn + (size_t)b * GnP * LD;
         double* raw = sRaw + (size_t)b * L.raw_rows * LD;
         const double* sS = raw;   // row 0: spot of period p
+        double* const sXT = sXT0 + ((overlap_f0 && (it & 1)) ? (size_t)8 * MT * LD : 0);   // x~ of this tile
         // development (LSMC_TRACE): phase timestamps of CTA 0, one row per warp and tile
         long long* tr = (q.trace && blockIdx.x == 0 && it < 64 && lane == 0) ? q.trace + ((size_t)warp * 64 + it) * 8 : nullptr;
         if (tr) tr[0] = clock64();
@@ -476,60 +519,18 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
         // Work of this phase: NF fit items (8 next-grid rows x TP paths, TP / 8 DMMA per k-step) and NX x~ items (8 basis rows x
         // 8 paths, one DMMA per k-step), both on the FP64 tensor pipe.  Fit item f goes to warp f % 16; the warps left with one fit
         // item fewer take TP / 8 x~ items each first (the same number of DMMA), the rest is dealt round robin.
-        constexpr int NNT = TP / 8;
         const int NF = (q.mode == 0 && q.cont_mode == 0) ? (GnP >> 3) : 0;
         const int NX = q.accum_mode == 1 ? MT * NNT : 0;
-        if (NX) {
-            // x~ = T^T x_{p-1}: D[j][path] = sum_i T[i][j] x[i][path]; the k-steps alternate between two accumulator pairs so that
-            // two DMMA chains are in flight per item
-            auto xt_item = [&](const int item) {
-                const int m = item / NNT, nt = item - m * NNT, j = 8 * m + g;
-                double c0 = 0.0, c1 = 0.0, d0 = 0.0, d1 = 0.0;
-                auto operands = [&](const int ks, double& av, double& bv) {   // (zero rows / columns beyond K)
-                    av = sT[(ks + t) * LDT + j];
-                    bv = sXM[(size_t)(ks + t) * LDX + 8 * nt + g];
-                };
-                int ks = 0;
-#pragma unroll 2   // operands of the next pair of k-steps in flight while this pair's DMMA issue
-                for (; ks + 4 < Kp4; ks += 8) {
-                    double a0, b0, a1, b1;
-                    operands(ks, a0, b0);
-                    operands(ks + 4, a1, b1);
-                    dmma8x8x4(c0, c1, a0, b0);
-                    dmma8x8x4(d0, d1, a1, b1);
-                }
-                if (ks < Kp4) {
-                    double a0, b0;
-                    operands(ks, a0, b0);
-                    dmma8x8x4(c0, c1, a0, b0);
-                }
-                *reinterpret_cast<double2*>(sXT + (size_t)j * LD + 8 * nt + 2 * t) = make_double2(c0 + d0, c1 + d1);
-            };
-            // all TP / 8 path blocks of one row block at once, like a fit item: the T fragment is loaded once per k-step
-            auto xt_row_item = [&](const int m) {
-                const double* trow = sT + t * LDT + 8 * m + g;
-                const double* xcol = sXM + (size_t)t * LDX + g;
-                double cf[NNT][2];
-#pragma unroll
-                for (int nt = 0; nt < NNT; nt++) cf[nt][0] = cf[nt][1] = 0.0;
-#pragma unroll 2
-                for (int ks = 0; ks < Kp4; ks += 4) {
-                    const double av = trow[ks * LDT];
-#pragma unroll
-                    for (int nt = 0; nt < NNT; nt++) dmma8x8x4(cf[nt][0], cf[nt][1], av, xcol[(size_t)ks * LDX + 8 * nt]);
-                }
-#pragma unroll
-                for (int nt = 0; nt < NNT; nt++) *reinterpret_cast<double2*>(sXT + (size_t)(8 * m + g) * LD + 8 * nt + 2 * t) = make_double2(cf[nt][0], cf[nt][1]);
-            };
+        if (NX && (!overlap_f0 || it == 0)) {   // (with two tile buffers: done during the previous tile's decision phase)
             // the workers (the producer warp is busy issuing the next tile's copies) left with one fit item fewer take two whole row
             // blocks each; the rest goes round robin over the workers
             const int n_hi = NF ? NF - ((NF - 1) / kSweepWarps) * kSweepWarps : kSweepWarps;   // warps with the larger number of fit items
             const int n_lo = max(0, kWorkers - n_hi);
             const int n_rows = min(MT, 2 * n_lo);                                             // row blocks taken whole
             if (warp >= n_hi && warp < kWorkers)
-                for (int m = warp - n_hi; m < n_rows; m += n_lo) xt_row_item(m);
+                for (int m = warp - n_hi; m < n_rows; m += n_lo) xt_row_item(sXT, m);
             if (warp < kWorkers)
-                for (int e = n_rows * NNT + warp; e < NX; e += kWorkers) xt_item(e);
+                for (int e = n_rows * NNT + warp; e < NX; e += kWorkers) xt_item(sXT, e);
         } else if (q.accum_mode == 2) {
             for (int path = tid; path < TP; path += blockDim.x) sXT[path] = (n0 + path < q.N) ? 1.0 : 0.0;
         }
@@ -588,6 +589,13 @@ __global__ void __launch_bounds__(kSweepWarps * 32, 1) sweep_kernel(SweepParams 
             if (any_copy) mbar_wait(&s_full[b ^ 1], (uint32_t)(((it + 1) >> 1) & 1));
             if (tr) tr[7] = clock64();
             basis_rows(b ^ 1, next * TP, tid - kAuxFirst * 32, (kSweepWarps - kAuxFirst) * 32, [] { asm volatile("bar.sync 1, 96;" ::: "memory"); });
+            if (q.accum_mode == 1) {
+                // ... and its preconditioned regressors, into the other x~ buffer: whole row blocks first, the rest as single items
+                double* const xt_next = sXT0 + ((it & 1) ? 0 : (size_t)8 * MT * LD);
+                constexpr int kAux = kSweepWarps - kAuxFirst, R = MT - MT % kAux;
+                for (int m = warp - kAuxFirst; m < R; m += kAux) xt_row_item(xt_next, m);
+                for (int e = R * NNT + warp - kAuxFirst; e < MT * NNT; e += kAux) xt_item(xt_next, e);
+            }
         }
         if (warp < kWorkers) {
 #pragma unroll
