@@ -635,7 +635,15 @@ void backward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
         q.ldb = c->ldb;
         q.basis = c->basis.p;
         q.partial = c->partial.p;
-        q.pdl = (c->use_pdl && pdl_enabled()) ? 1 : 0;
+        // Programmatic dependent launch, per edge of the loop (measured on one B200, bench.py, us per period outside the sweep):
+        //   tail -> sweep (the sweep's set-up overlaps the tail): C3 19.7 -> 9.6, C3 at 125k paths 19.3 -> 8.7 — kept for problems on
+        //   the pipelined sweep; C4 (general sweep, 190 KB of shared memory per CTA) 90.8 -> 107.4 — off there;
+        //   sweep -> tail (the tail's CTAs start as the sweep's CTAs leave): C3 9.6 -> 17.1, C4 107 -> 166 — off everywhere.
+        // LSMC_PDL_EDGES (development): bit 0 tail -> sweep, bit 1 sweep -> tail, bit 2 also with the general sweep.
+        static const int pdl_edges = [] { const char* e = getenv("LSMC_PDL_EDGES"); return e ? atoi(e) : 1; }();
+        const bool pdl_on = c->use_pdl && pdl_enabled() && (c->TP4 != 0 || (pdl_edges & 4));
+        q.pdl = (pdl_on && (pdl_edges & 1)) ? 1 : 0;
+        const int pdl_tail = (pdl_on && (pdl_edges & 2)) ? 1 : 0;
         const bool is_current = (p == 0 && s0 == 1);
         double* vout = c->keep_values ? c->Vall.p + (size_t)p * pl.max_grid * Np : c->V(cur ^ 1);
         const double* vnext = c->keep_values ? c->Vall.p + (size_t)(p + 1) * pl.max_grid * Np : c->V(cur);
@@ -706,7 +714,7 @@ void backward(lsmc_ctx* c, lsmc_progress_cb cb, void* user) {
             tp.solve = sp; tp.partial = c->partial.p; tp.n_parts = n_parts; tp.n_elem = n_elem;
             tp.do_solve = p > 0 ? 1 : 0;
             tp.total_out = c->reduced.p; tp.n_out = 1;   // element 0 at p == 0: sum of the start-inventory values (backward NPV)
-            tp.peers = c->peer.view; tp.error_flag = c->error_flag.p; tp.pdl = q.pdl;
+            tp.peers = c->peer.view; tp.error_flag = c->error_flag.p; tp.pdl = pdl_tail;
             const int blocks = tail_blocks(n_elem, q.G, c->num_sms);
             c->peer.next(blocks, &tp.parity, &tp.target, &tp.local_target);
             static const bool tail_trace = getenv("LSMC_TAIL_TRACE") != nullptr;   // development: phase stamps of one mid-horizon tail

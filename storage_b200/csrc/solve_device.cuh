@@ -69,8 +69,10 @@ __device__ __forceinline__ bool solve_stage(const SolveParams& sp, const Red& re
 #pragma unroll 8
     for (int e = tid; e < n_tri; e += blockDim.x) {
         const int r = tri_row(e), c = e - r * (r + 1) / 2;
-        // (c <= r; with gram_lower_blocks only rows of basis block <= column block are filled: (c, r), and (r, c) inside a block)
-        const double v = (sp.gram_lower_blocks && (r >> 3) != (c >> 3)) ? red(c, gcol + r) : 0.5 * (red(r, gcol + c) + red(c, gcol + r));
+        // (c <= r; with gram_lower_blocks only the blocks with basis block <= column block are filled and their mirror images hold
+        //  zeros: (c, r) then carries the whole entry.  Both loads unconditional: sixteen in flight per thread)
+        const double w = (sp.gram_lower_blocks && (r >> 3) != (c >> 3)) ? 1.0 : 0.5;
+        const double v = w * (red(r, gcol + c) + red(c, gcol + r));
         Graw[r * K + c] = v;
         Graw[c * K + r] = v;
     }
