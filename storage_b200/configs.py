@@ -35,11 +35,12 @@ def _ratchet_storage(start, end, years=1, **kw):   # README.md:100-125 shape
     return CmdtyStorage('D', start, end, 0.1, 0.25, ratchets=ratchets, ratchet_interp=RatchetInterp.LINEAR, **kw)
 
 
-def build_config(name, num_sims=None, start_inventory=None, basis=None, end=None, storage=None):
+def build_config(name, num_sims=None, start_inventory=None, basis=None, end=None, storage=None, grid_points=None):
     """Returns a flattened Problem for config 'c1'..'c5' (BASELINE.json configs[0..4]).
 
-    `basis`, `end` and `storage` override the config's basis-function string, storage end date and storage object
-    (parity-test variants of the named shapes: other K, shorter horizons, other constraint kinds)."""
+    `basis`, `end`, `storage` and `grid_points` override the config's basis-function string, storage end date, storage object
+    and number of inventory grid points (parity-test variants of the named shapes: other K, shorter horizons, other constraint
+    kinds, grids beyond the pipelined sweep's 104 rows)."""
     name = name.lower()
     basis_override, end_override, storage_override = basis, end, storage
     if name == 'c1':    # README simple storage, three-factor seasonal, 1k paths
@@ -108,7 +109,7 @@ def build_config(name, num_sims=None, start_inventory=None, basis=None, end=None
     # 1e-10 (LVP.cs:86); the synthetic configs use 1e-9.
     tol = 1e-9
     return flatten_problem(st, val_period, inv, fwd, rates, _settle_20th_next_month, factors, corrs, N, basis, True,
-                           numerical_tolerance=tol)
+                           numerical_tolerance=tol, **({} if grid_points is None else {"num_inventory_grid_points": grid_points}))
 
 
 def full_polynomial_basis(num_factors, degree):

@@ -105,6 +105,10 @@ FIVE_FACTOR_K16 = ("1 + x0 + x1 + x2 + x3 + x4 + x0**2 + x1**2 + x2**2 + x3**2 +
 CASES = {
     "c4_five_factor_k56": lambda: build_config("c4", num_sims=512),                              # K > 32: sweep_kernel MT=8, solve_kernel<64>, forward_kernel<64>
     "c3_cubic_basis_k20": lambda: build_config("c3", num_sims=640, basis=full_polynomial_basis(3, 3)),   # 16 < K <= 32: MT=4
+    # grids beyond 104 rows: the general sweep for every period, two rounds of decision items per tile (and, with K > 16, the
+    # basis program / x~ not overlapped: the three warps it would run on own decision items)
+    "c3_fine_grid_130": lambda: build_config("c3", num_sims=512, end="2021-08-01", grid_points=130),
+    "c3_cubic_basis_k20_grid_120": lambda: build_config("c3", num_sims=512, end="2021-07-01", basis=full_polynomial_basis(3, 3), grid_points=120),
     "c4_five_factor_k16_tp40": lambda: build_config("c4", num_sims=600, end="2021-07-01", basis=FIVE_FACTOR_K16),
     "reference_fixture_step_ratchets": lambda: reference_problem(storage=step_ratchet_storage(), num_sims=768, numerical_tolerance=1e-9),
     "inventory_cost": lambda: reference_problem(storage=inventory_cost_storage(), num_sims=512),
