@@ -21,7 +21,7 @@ struct GlobalRed {
 inline size_t solve_smem_bytes(int K) { return sizeof(double) * ((size_t)4 * K * K + 4 * K); }
 
 // Element idx of the lower triangle in row-major order (0: (0,0), 1: (1,0), 2: (1,1), ...) -> row; column = idx - row (row + 1) / 2.
-__device__ __forceinline__ int tri_row(int idx) {
+static __device__ __noinline__ int tri_row(int idx) {   // (one copy: the tail kernel runs its code once per launch, from a cold instruction cache)
     int i = (int)((sqrtf(8.0f * (float)idx + 1.0f) - 1.0f) * 0.5f);
     while ((i + 1) * (i + 2) / 2 <= idx) i++;
     while (i * (i + 1) / 2 > idx) i--;
