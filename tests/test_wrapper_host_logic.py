@@ -64,3 +64,12 @@ def test_three_factor_seasonal_parameterisation(freq, start, end):
     if freq == "D":   # peak on 1 February, trough half a year later
         assert season[pd.Period("2020-02-01", freq="D")] == pytest.approx(0.095 * math.cos(2 * math.pi * 365.0 / 365.25), abs=1e-15)
         assert season.max() <= 0.095 and season.min() >= -0.095
+
+
+def test_build_config_grid_points_override_sets_the_grid_spacing():
+    """configs.build_config(grid_points=n): the parity cases with inventory grids beyond the pipelined sweep's 104 rows."""
+    from storage_b200.configs import build_config
+    coarse = build_config("c3", num_sims=8, end="2021-06-01")
+    fine = build_config("c3", num_sims=8, end="2021-06-01", grid_points=130)
+    assert coarse.grid_spacing == pytest.approx(fine.grid_spacing * 129.0 / 99.0, rel=1e-12)
+    assert fine.n_periods == coarse.n_periods and fine.n_basis == coarse.n_basis
